@@ -1,0 +1,37 @@
+# Build everything in-tree for sm_100a (B200). No GPU is needed to build.
+#   make            -> build/libb200knn.so + executables under build/
+#   make lib        -> only the shared library (what Python loads)
+#   make sass       -> profiles/sass/*.sass listings of the hot kernels
+NVCC      ?= /usr/local/cuda/bin/nvcc
+CXX       ?= g++
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS   := $(ARCH) -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-ffp-contract=off -Xptxas -v \
+             --fmad=false -prec-sqrt=true -prec-div=true -Iinclude -Icsrc
+CXXFLAGS  := -O2 -std=c++17 -fPIC -ffp-contract=off -mfma -pthread -Iinclude -Icsrc
+BUILD     := build
+
+CU_SRCS   := csrc/radix_sort.cu csrc/build.cu csrc/query.cu csrc/api.cu
+CU_OBJS   := $(patsubst csrc/%.cu,$(BUILD)/%.o,$(CU_SRCS))
+CPP_OBJS  := $(BUILD)/cpu_engine.o
+
+LIB       := $(BUILD)/libb200knn.so
+
+all: lib
+
+lib: $(LIB)
+
+$(BUILD)/%.o: csrc/%.cu csrc/*.h csrc/*.cuh include/b200knn.h
+	@mkdir -p $(BUILD)
+	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(BUILD)/$*.ptxas.log || (cat $(BUILD)/$*.ptxas.log; false)
+
+$(BUILD)/%.o: csrc/%.cpp csrc/*.h include/b200knn.h
+	@mkdir -p $(BUILD)
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+
+$(LIB): $(CU_OBJS) $(CPP_OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart static -lpthread
+
+clean:
+	rm -rf $(BUILD)
+
+.PHONY: all lib clean

@@ -1,0 +1,225 @@
+#!/usr/bin/env python
+"""Headline benchmark: kNN queries/sec at N = 256 M float3, k = 100 (BASELINE.json), 1..8 B200.
+
+    python bench.py --gpus 1 --steps 3 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29500 bench.py --gpus 8 --steps 3 --warmup 3
+    python bench.py --impl reference ...        # the unmodified reference (baseline/_ref)
+
+One "step" = one complete all-kNN pass over the whole point set, exactly the work the reference
+does per run after its file read: spatial index build + all queries + k-th-distance extraction.
+Total N is fixed as GPUs are added (strong scaling). Synthetic uniform-random points, fp32.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+BASELINE_N = 256 * 1024 * 1024
+BASELINE_K = 100
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period_s: float = 0.1):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period_s
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # NVML missing: report it, do not fake numbers
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8)): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40)): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20)): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4)): "sw_power_cap",
+        }
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                bits = get_reasons(self.h)
+                for bit, name in names.items():
+                    if bits & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(self.period)
+
+    def finish(self) -> dict:
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "nvml unavailable"}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def run_reference(args) -> int:
+    from baseline.run_reference import bench_reference
+    return bench_reference(args)
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=int(os.environ.get("B200KNN_BENCH_N", BASELINE_N)),
+                    help="TOTAL number of points over all GPUs")
+    ap.add_argument("--k", type=int, default=BASELINE_K)
+    ap.add_argument("--transport", default="fused", choices=["fused", "nccl"],
+                    help="multi-GPU ring transport: in-kernel NVLink hand-off (product) or NCCL send/recv (baseline)")
+    ap.add_argument("--chunk-groups", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if rank == 0:
+            print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; launch with torchrun --nproc-per-node {args.gpus}",
+                  file=sys.stderr)
+        return 2
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from mpi_cuda_largescaleknn_b200.ops._lib import lib
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
+    from mpi_cuda_largescaleknn_b200.parallel.ring import FusedRing, NcclRingBaseline
+    from mpi_cuda_largescaleknn_b200.utils.generators import torch_uniform
+
+    N, k = args.n, args.k
+    begin, end = N * rank // world, N * (rank + 1) // world
+    n_local = end - begin
+    x_dev = torch_uniform(n_local, dev, seed=1234 + rank)
+    out_dev = torch.empty(n_local, dtype=torch.float32, device=dev)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def one_step(points):
+        idx = KnnIndex(points, id_offset=0)
+        if world == 1:
+            idx.knn_self(k, out=out_dev)
+        else:
+            cls = FusedRing if args.transport == "fused" else NcclRingBaseline
+            ring = cls(idx, k, groups_per_chunk=args.chunk_groups)
+            ring.run(out=out_dev)
+            if hasattr(ring, "close"):
+                ring.close()
+        idx.close()
+
+    def timed(fn, steps):
+        """K steps bracketed by barrier+sync, CUDA events on the launching stream, max over ranks."""
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        sync_all()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(args.warmup):
+        one_step(x_dev)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = lib().b200knn_launch_count()
+    total_ms = timed(lambda: one_step(x_dev), args.steps)
+    launches = int(lib().b200knn_launch_count() - launches0)
+    clocks = sampler.finish()
+    ms_per_step = total_ms / args.steps
+    value = N / (ms_per_step * 1e-3)
+
+    e2e = None
+    if not args.no_e2e:
+        # End to end through the public API: inputs start in pinned host memory every step, the
+        # result is read back to the host every step.
+        x_host = torch.empty((n_local, 3), dtype=torch.float32, pin_memory=True)
+        x_host.copy_(x_dev)
+        res_host = torch.empty(n_local, dtype=torch.float32, pin_memory=True)
+        stage = torch.empty_like(x_dev)
+
+        def e2e_step():
+            stage.copy_(x_host, non_blocking=True)
+            one_step(stage)
+            res_host.copy_(out_dev, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        e2e_step()
+        e2e_ms = timed(e2e_step, args.steps) / args.steps
+        e2e = {"value": N / (e2e_ms * 1e-3), "unit": "queries/s", "ms_per_step": e2e_ms,
+               "h2d_bytes_per_step": int(n_local * 12), "d2h_bytes_per_step": int(n_local * 4),
+               "bytes_are": "per rank"}
+
+    if rank == 0:
+        line = {
+            "metric": "kNN queries/sec (N=256M float3, k=100)" if (N == BASELINE_N and k == BASELINE_K)
+                      else f"kNN queries/sec (N={N} float3, k={k})",
+            "value": value, "unit": "queries/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "fp32", "data": "synthetic uniform-random float3 in the unit cube, generated on device",
+            "impl": "ours",
+            "config": {"model": "unorderedDataVariant", "n_points": N, "k": k, "global_batch": N, "seq_len": k,
+                       "parallelism": ("single" if world == 1 else f"ring{world}-{args.transport}"),
+                       "step": "index build + all-kNN + k-th distance extraction",
+                       "l2": "inputs (>= 3 GB at the headline size) exceed the 126 MB L2; no explicit flush"},
+            "clocks": clocks, "gpu_launches": launches // max(1, args.steps) * args.steps,
+            "gpu_launches_per_step": launches // max(1, args.steps),
+        }
+        if e2e is not None:
+            line["e2e"] = e2e
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,463 @@
+// api.cu — C ABI glue: index lifetime, single-GPU queries, fused-ring object (peer mapping via CUDA IPC).
+// Host-side only; all kernels live in radix_sort.cu / build.cu / query.cu.
+//
+// Role in the reference: the body of main() between "points are on the host" and "results are on
+// the host" (/root/reference/unorderedDataVariant.cu:153-211), minus MPI, plus what MPI hid
+// (peer mapping, flow control).
+#include <string.h>
+#include <atomic>
+#include <vector>
+#include "../include/b200knn.h"
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200knn {
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+const char* last_error_cstr() { return g_last_error.c_str(); }
+static std::atomic<unsigned long long> g_launches{0};
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+}  // namespace b200knn
+
+using namespace b200knn;
+
+struct b200knn_index {
+  int device = 0;
+  int num_sms = 148;
+  int64_t n = 0;
+  uint32_t id_offset = 0;
+  Float4* pts = nullptr;
+  Box* boxes[kMaxLevels] = {};
+  int count[kMaxLevels] = {};
+  int levels = 0;
+  unsigned* d_bounds_ord = nullptr;
+  float* d_bounds6 = nullptr;
+  float h_bounds[6] = {};
+  float* result_sorted = nullptr;          // [groups*32]
+  unsigned long long* task_counter = nullptr;
+  unsigned long long* stats = nullptr;     // [4]
+  bool stats_on = false;
+
+  TreeView view() const {
+    TreeView t;
+    t.pts = pts;
+    for (int l = 0; l < kMaxLevels; ++l) { t.boxes[l] = boxes[l]; t.count[l] = count[l]; }
+    t.levels = levels;
+    t.n = (int)n;
+    return t;
+  }
+  int64_t groups() const { return div_up(n, kGroup); }
+};
+
+namespace {
+
+struct RingLayout {
+  int64_t heap[2], pos[2], cnt[2], flag_in[2], ack_in[2], result, bytes;
+};
+
+struct IpcBlob {
+  cudaIpcMemHandle_t handle;   // 64 bytes
+  RingLayout layout;
+  int32_t rank, world, k, groups_per_chunk;
+  int64_t pid;
+};
+static_assert(sizeof(IpcBlob) <= B200KNN_IPC_BLOB_BYTES, "blob too large");
+
+inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+RingLayout make_layout(int k, int Gc, int64_t result_floats) {
+  RingLayout L;
+  int64_t off = 0;
+  for (int b = 0; b < 2; ++b) { L.heap[b] = off; off = align_up(off + (int64_t)Gc * k * 32 * 4, 256); }
+  for (int b = 0; b < 2; ++b) { L.pos[b] = off; off = align_up(off + (int64_t)Gc * 32 * 16, 256); }
+  for (int b = 0; b < 2; ++b) { L.cnt[b] = off; off = align_up(off + (int64_t)Gc * 4, 256); }
+  for (int b = 0; b < 2; ++b) { L.flag_in[b] = off; off = align_up(off + (int64_t)Gc * 4, 256); }
+  for (int b = 0; b < 2; ++b) { L.ack_in[b] = off; off = align_up(off + (int64_t)Gc * 4, 256); }
+  L.result = off; off = align_up(off + result_floats * 4, 256);
+  L.bytes = off;
+  return L;
+}
+
+}  // namespace
+
+struct b200knn_ring {
+  b200knn_index* idx = nullptr;
+  int rank = 0, world = 1, k = 0, Gc = 0, C = 0;
+  char* base = nullptr;
+  RingLayout mine{};
+  char* next_base = nullptr; RingLayout next_layout{};
+  char* prev_base = nullptr; RingLayout prev_layout{};
+  bool opened_next = false, opened_prev = false;
+  unsigned seq_base = 1;
+};
+
+extern "C" {
+
+const char* b200knn_last_error(void) { return last_error_cstr(); }
+int b200knn_version(void) { return 100; }
+uint64_t b200knn_launch_count(void) { return g_launches.load(); }
+
+int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
+                         void* stream_, b200knn_index** out) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  KNN_REQUIRE(out != nullptr, "index_create: out is NULL");
+  KNN_REQUIRE(n >= 0 && n < (int64_t)0x7fffffff - 64, "index_create: n must be in [0, 2^31-64) per GPU");
+  b200knn_index* idx = new b200knn_index();
+  *out = idx;
+  idx->n = n;
+  idx->id_offset = id_offset;
+  KNN_CUDA_TRY(cudaGetDevice(&idx->device));
+  KNN_CUDA_TRY(cudaDeviceGetAttribute(&idx->num_sms, cudaDevAttrMultiProcessorCount, idx->device));
+  KNN_CUDA_TRY(cudaMalloc(&idx->d_bounds_ord, 6 * sizeof(unsigned)));
+  KNN_CUDA_TRY(cudaMalloc(&idx->d_bounds6, 6 * sizeof(float)));
+  KNN_CUDA_TRY(cudaMalloc(&idx->task_counter, sizeof(unsigned long long)));
+  KNN_CUDA_TRY(cudaMalloc(&idx->stats, 4 * sizeof(unsigned long long)));
+  KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 4 * sizeof(unsigned long long), stream));
+  int rc;
+  if ((rc = bounds_init(idx->d_bounds_ord, stream))) return rc;
+  if ((rc = bounds_accumulate(d_xyz, n, idx->d_bounds_ord, stream))) return rc;
+  if ((rc = bounds_decode(idx->d_bounds_ord, idx->d_bounds6, stream))) return rc;
+  KNN_CUDA_TRY(cudaMemcpyAsync(idx->h_bounds, idx->d_bounds6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  if (n == 0) {
+    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    return 0;
+  }
+  const int64_t groups = idx->groups();
+  const int64_t padded = groups * kGroup;
+  KNN_CUDA_TRY(cudaMalloc(&idx->pts, padded * sizeof(Float4)));
+  KNN_CUDA_TRY(cudaMalloc(&idx->result_sorted, padded * sizeof(float)));
+  // level sizes
+  int cnt = (int)groups;
+  int levels = 0;
+  for (;;) {
+    KNN_REQUIRE(levels < kMaxLevels, "index_create: too many tree levels");
+    idx->count[levels] = cnt;
+    KNN_CUDA_TRY(cudaMalloc(&idx->boxes[levels], (size_t)cnt * sizeof(Box)));
+    ++levels;
+    if (cnt <= kFanout) break;
+    cnt = (int)div_up(cnt, kFanout);
+  }
+  idx->levels = levels;
+
+  // temporaries (stream-ordered)
+  uint64_t *keys = nullptr, *keys_tmp = nullptr;
+  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr;
+  KNN_CUDA_TRY(cudaMallocAsync(&keys, n * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, n * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&vals, n * sizeof(uint32_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, n * sizeof(uint32_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(n), stream));
+  if ((rc = morton_keys(d_xyz, n, idx->d_bounds6, keys, vals, stream))) return rc;
+  int in_tmp = 0;
+  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n, 0, 64, stream, &in_tmp))) return rc;
+  const uint32_t* order = in_tmp ? vals_tmp : vals;
+  if ((rc = gather_points(d_xyz, order, d_ids, id_offset, n, idx->pts, stream))) return rc;
+  if ((rc = build_leaf_boxes(idx->pts, n, idx->boxes[0], stream))) return rc;
+  for (int l = 1; l < levels; ++l)
+    if ((rc = build_upper_boxes(idx->boxes[l - 1], idx->count[l - 1], idx->boxes[l], stream))) return rc;
+  KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
+  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+void b200knn_index_destroy(b200knn_index* idx) {
+  if (!idx) return;
+  cudaFree(idx->pts);
+  for (int l = 0; l < kMaxLevels; ++l) cudaFree(idx->boxes[l]);
+  cudaFree(idx->d_bounds_ord);
+  cudaFree(idx->d_bounds6);
+  cudaFree(idx->result_sorted);
+  cudaFree(idx->task_counter);
+  cudaFree(idx->stats);
+  delete idx;
+}
+
+int64_t b200knn_index_num_points(const b200knn_index* idx) { return idx ? idx->n : 0; }
+int b200knn_index_num_levels(const b200knn_index* idx) { return idx ? idx->levels : 0; }
+
+int b200knn_index_bounds(const b200knn_index* idx, float* host_bounds6) {
+  KNN_REQUIRE(idx && host_bounds6, "index_bounds: NULL argument");
+  memcpy(host_bounds6, idx->h_bounds, sizeof(idx->h_bounds));
+  return 0;
+}
+
+int b200knn_index_copy_sorted(const b200knn_index* idx, float* host_xyzw) {
+  KNN_REQUIRE(idx && host_xyzw, "index_copy_sorted: NULL argument");
+  if (idx->n == 0) return 0;
+  KNN_CUDA_TRY(cudaMemcpy(host_xyzw, idx->pts, idx->n * sizeof(Float4), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int b200knn_index_copy_boxes(const b200knn_index* idx, int level, float* host_boxes8, int* count) {
+  KNN_REQUIRE(idx && count, "index_copy_boxes: NULL argument");
+  KNN_REQUIRE(level >= 0 && level < idx->levels, "index_copy_boxes: level out of range");
+  *count = idx->count[level];
+  if (host_boxes8)
+    KNN_CUDA_TRY(cudaMemcpy(host_boxes8, idx->boxes[level], (size_t)idx->count[level] * sizeof(Box),
+                            cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+static void fill_local_only(RingParams& p, b200knn_index* idx, int k, float max_radius) {
+  memset(&p, 0, sizeof(p));
+  p.tree = idx->view();
+  p.k = k;
+  p.sentinel = sentinel_d2(max_radius);
+  p.R = 1;
+  p.rank = 0;
+  p.num_chunks = 1;
+  p.step_begin = 0;
+  p.step_end = 1;
+  p.use_flags = 0;
+  p.seq_base = 0;
+  p.task_counter = idx->task_counter;
+  p.stats = idx->stats_on ? idx->stats : nullptr;
+}
+
+int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  KNN_REQUIRE(idx && d_out, "knn_self: NULL argument");
+  KNN_REQUIRE(k >= 1, "knn_self: k must be >= 1");
+  if (idx->n == 0) return 0;
+  RingParams p;
+  fill_local_only(p, idx, k, max_radius);
+  p.groups_per_chunk = (int)idx->groups();
+  p.home_queries = idx->pts;
+  p.home_n = idx->n;
+  p.result_sorted = idx->result_sorted;
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 4 * sizeof(unsigned long long), stream));
+  int rc;
+  if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
+  return scatter_results(idx->pts, idx->result_sorted, idx->n, idx->id_offset, d_out, stream);
+}
+
+int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, int k, float max_radius,
+                      float* d_out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  KNN_REQUIRE(idx && d_out, "knn_query: NULL argument");
+  KNN_REQUIRE(k >= 1, "knn_query: k must be >= 1");
+  KNN_REQUIRE(nq >= 0 && nq < (int64_t)0x7fffffff - 64, "knn_query: nq out of range");
+  if (nq == 0) return 0;
+  const int64_t groups = div_up(nq, kGroup);
+  uint64_t *keys = nullptr, *keys_tmp = nullptr;
+  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr;
+  Float4* qsorted = nullptr;
+  float* rsorted = nullptr;
+  KNN_CUDA_TRY(cudaMallocAsync(&keys, nq * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, nq * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&vals, nq * sizeof(uint32_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, nq * sizeof(uint32_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(nq), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&qsorted, groups * kGroup * sizeof(Float4), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&rsorted, groups * kGroup * sizeof(float), stream));
+  int rc;
+  // Order queries along the index's own Morton grid (queries outside its box clamp to the faces).
+  if ((rc = morton_keys(d_queries, nq, idx->d_bounds6, keys, vals, stream))) return rc;
+  int in_tmp = 0;
+  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
+  if ((rc = gather_points(d_queries, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
+  RingParams p;
+  fill_local_only(p, idx, k, max_radius);
+  p.groups_per_chunk = (int)groups;
+  p.home_queries = qsorted;
+  p.home_n = nq;
+  p.result_sorted = rsorted;
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 4 * sizeof(unsigned long long), stream));
+  if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
+  if ((rc = scatter_results(qsorted, rsorted, nq, 0, d_out, stream))) return rc;
+  KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(qsorted, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(rsorted, stream));
+  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+int b200knn_index_enable_stats(b200knn_index* idx, int on) {
+  KNN_REQUIRE(idx, "index_enable_stats: NULL index");
+  idx->stats_on = on != 0;
+  return 0;
+}
+
+int b200knn_index_stats(b200knn_index* idx, uint64_t out4[4]) {
+  KNN_REQUIRE(idx && out4, "index_stats: NULL argument");
+  unsigned long long h[4];
+  KNN_CUDA_TRY(cudaMemcpy(h, idx->stats, sizeof(h), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < 4; ++i) out4[i] = h[i];
+  return 0;
+}
+
+int b200knn_index_unsort(b200knn_index* idx, const float* d_sorted_result, float* d_out, void* stream_) {
+  KNN_REQUIRE(idx && d_sorted_result && d_out, "index_unsort: NULL argument");
+  return scatter_results(idx->pts, d_sorted_result, idx->n, idx->id_offset, d_out, (cudaStream_t)stream_);
+}
+
+int b200knn_run_steps(b200knn_index* idx, const b200knn_step_args* a, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  KNN_REQUIRE(idx && a, "run_steps: NULL argument");
+  KNN_REQUIRE(a->world >= 1 && a->world <= B200KNN_MAX_RANKS, "run_steps: world out of range");
+  KNN_REQUIRE(a->groups_per_chunk >= 1 && a->num_chunks >= 1, "run_steps: bad chunking");
+  KNN_REQUIRE(a->step_begin >= 0 && a->step_end <= a->num_chunks * a->world && a->step_begin <= a->step_end,
+              "run_steps: bad step range");
+  RingParams p;
+  fill_local_only(p, idx, a->k, a->max_radius);
+  p.R = a->world;
+  p.rank = a->rank;
+  p.groups_per_chunk = a->groups_per_chunk;
+  p.num_chunks = a->num_chunks;
+  p.step_begin = a->step_begin;
+  p.step_end = a->step_end;
+  p.home_queries = idx->pts;
+  p.home_n = idx->n;
+  for (int b = 0; b < 2; ++b) {
+    p.inbox_heap[b] = a->inbox_heap[b];
+    p.inbox_pos[b] = reinterpret_cast<const Float4*>(a->inbox_pos[b]);
+    p.inbox_cnt[b] = a->inbox_cnt[b];
+    p.next_heap[b] = a->outbox_heap[b];
+    p.next_pos[b] = reinterpret_cast<Float4*>(a->outbox_pos[b]);
+    p.next_cnt[b] = a->outbox_cnt[b];
+  }
+  p.result_sorted = a->result_sorted;
+  return ring_launch(p, idx->num_sms, stream);
+}
+
+// ------------------------------------------------------------------------------------- fused ring
+
+int b200knn_ring_create(b200knn_index* idx, int rank, int world, int k, int64_t max_points_any_rank,
+                        int groups_per_chunk, b200knn_ring** out) {
+  KNN_REQUIRE(idx && out, "ring_create: NULL argument");
+  KNN_REQUIRE(world >= 1 && world <= B200KNN_MAX_RANKS, "ring_create: world must be in [1,16]");
+  KNN_REQUIRE(rank >= 0 && rank < world, "ring_create: rank out of range");
+  KNN_REQUIRE(k >= 1, "ring_create: k must be >= 1");
+  KNN_REQUIRE(max_points_any_rank >= idx->n, "ring_create: max_points_any_rank < local point count");
+  b200knn_ring* r = new b200knn_ring();
+  *out = r;
+  r->idx = idx;
+  r->rank = rank;
+  r->world = world;
+  r->k = k;
+  const int64_t max_groups = div_up(max_points_any_rank > 0 ? max_points_any_rank : 1, kGroup);
+  int64_t Gc = groups_per_chunk > 0 ? groups_per_chunk : 65536;
+  if (Gc > max_groups) Gc = max_groups;
+  r->Gc = (int)Gc;
+  r->C = (int)div_up(max_groups, Gc);
+  r->mine = make_layout(k, world > 1 ? r->Gc : 1, max_groups * kGroup);
+  KNN_CUDA_TRY(cudaMalloc(&r->base, r->mine.bytes));
+  KNN_CUDA_TRY(cudaMemset(r->base, 0, r->mine.bytes));
+  return 0;
+}
+
+void b200knn_ring_destroy(b200knn_ring* r) {
+  if (!r) return;
+  if (r->opened_next) cudaIpcCloseMemHandle(r->next_base);
+  if (r->opened_prev) cudaIpcCloseMemHandle(r->prev_base);
+  cudaFree(r->base);
+  delete r;
+}
+
+int64_t b200knn_ring_comm_bytes(const b200knn_ring* r) { return r ? r->mine.bytes : 0; }
+
+int b200knn_ring_export(b200knn_ring* r, void* blob_) {
+  KNN_REQUIRE(r && blob_, "ring_export: NULL argument");
+  IpcBlob blob;
+  memset(&blob, 0, sizeof(blob));
+  if (r->world > 1) KNN_CUDA_TRY(cudaIpcGetMemHandle(&blob.handle, r->base));
+  blob.layout = r->mine;
+  blob.rank = r->rank;
+  blob.world = r->world;
+  blob.k = r->k;
+  blob.groups_per_chunk = r->Gc;
+  blob.pid = 0;
+  memset(blob_, 0, B200KNN_IPC_BLOB_BYTES);
+  memcpy(blob_, &blob, sizeof(blob));
+  return 0;
+}
+
+int b200knn_ring_connect(b200knn_ring* r, const void* all_blobs) {
+  KNN_REQUIRE(r && all_blobs, "ring_connect: NULL argument");
+  if (r->world == 1) return 0;
+  const char* bytes = static_cast<const char*>(all_blobs);
+  auto blob_of = [&](int rank) {
+    IpcBlob b;
+    memcpy(&b, bytes + (size_t)rank * B200KNN_IPC_BLOB_BYTES, sizeof(b));
+    return b;
+  };
+  for (int q = 0; q < r->world; ++q) {
+    const IpcBlob b = blob_of(q);
+    KNN_REQUIRE(b.rank == q && b.world == r->world, "ring_connect: blobs are not in rank order");
+    KNN_REQUIRE(b.k == r->k && b.groups_per_chunk == r->Gc, "ring_connect: ranks disagree on k or chunking");
+  }
+  const int next = (r->rank + 1) % r->world, prev = (r->rank + r->world - 1) % r->world;
+  IpcBlob nb = blob_of(next);
+  void* ptr = nullptr;
+  KNN_CUDA_TRY(cudaIpcOpenMemHandle(&ptr, nb.handle, cudaIpcMemLazyEnablePeerAccess));
+  r->next_base = static_cast<char*>(ptr);
+  r->next_layout = nb.layout;
+  r->opened_next = true;
+  if (prev == next) {
+    r->prev_base = r->next_base;
+    r->prev_layout = nb.layout;
+  } else {
+    IpcBlob pb = blob_of(prev);
+    KNN_CUDA_TRY(cudaIpcOpenMemHandle(&ptr, pb.handle, cudaIpcMemLazyEnablePeerAccess));
+    r->prev_base = static_cast<char*>(ptr);
+    r->prev_layout = pb.layout;
+    r->opened_prev = true;
+  }
+  return 0;
+}
+
+int b200knn_ring_run(b200knn_ring* r, float max_radius, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  KNN_REQUIRE(r, "ring_run: NULL ring");
+  KNN_REQUIRE(r->world == 1 || r->next_base, "ring_run: ring_connect has not been called");
+  b200knn_index* idx = r->idx;
+  RingParams p;
+  fill_local_only(p, idx, r->k, max_radius);
+  p.R = r->world;
+  p.rank = r->rank;
+  p.groups_per_chunk = r->Gc;
+  p.num_chunks = r->C;
+  p.step_begin = 0;
+  p.step_end = r->C * r->world;
+  p.use_flags = r->world > 1;
+  p.seq_base = r->seq_base;
+  p.home_queries = idx->pts;
+  p.home_n = idx->n;
+  char* nb = r->world > 1 ? r->next_base : r->base;
+  char* pb = r->world > 1 ? r->prev_base : r->base;
+  const RingLayout& NL = r->world > 1 ? r->next_layout : r->mine;
+  const RingLayout& PL = r->world > 1 ? r->prev_layout : r->mine;
+  for (int b = 0; b < 2; ++b) {
+    p.inbox_heap[b] = reinterpret_cast<const float*>(r->base + r->mine.heap[b]);
+    p.inbox_pos[b] = reinterpret_cast<const Float4*>(r->base + r->mine.pos[b]);
+    p.inbox_cnt[b] = reinterpret_cast<const int*>(r->base + r->mine.cnt[b]);
+    p.flag_in[b] = reinterpret_cast<const unsigned*>(r->base + r->mine.flag_in[b]);
+    p.ack_in[b] = reinterpret_cast<const unsigned*>(r->base + r->mine.ack_in[b]);
+    p.next_heap[b] = reinterpret_cast<float*>(nb + NL.heap[b]);
+    p.next_pos[b] = reinterpret_cast<Float4*>(nb + NL.pos[b]);
+    p.next_cnt[b] = reinterpret_cast<int*>(nb + NL.cnt[b]);
+    p.next_flag[b] = reinterpret_cast<unsigned*>(nb + NL.flag_in[b]);
+    p.prev_ack[b] = reinterpret_cast<unsigned*>(pb + PL.ack_in[b]);
+  }
+  // last hop of a group runs on the rank before its home: results go to the NEXT rank's array
+  p.result_sorted = reinterpret_cast<float*>(nb + NL.result);
+  r->seq_base += (unsigned)(r->C * r->world + 8);
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 4 * sizeof(unsigned long long), stream));
+  return ring_launch(p, idx->num_sms, stream);
+}
+
+int b200knn_ring_results(b200knn_ring* r, float* d_out, void* stream_) {
+  KNN_REQUIRE(r && d_out, "ring_results: NULL argument");
+  return scatter_results(r->idx->pts, reinterpret_cast<const float*>(r->base + r->mine.result), r->idx->n,
+                         r->idx->id_offset, d_out, (cudaStream_t)stream_);
+}
+
+}  // extern "C"

@@ -1,0 +1,222 @@
+// build.cu — spatial index construction kernels (bounds, Morton keys, gather, box hierarchy).
+//
+// Role of cukd::buildTree (submodules/cudaKDTree/cukd/builder.h:108-151 -> builder_thrust.h:414-512)
+// in the reference, which runs one full comparison sort per tree level. Here the order comes from a
+// single radix sort of 63-bit Morton keys; the "tree" is the sorted point array plus a 32-ary
+// hierarchy of bounding boxes built bottom-up by warp reductions. Bounds use the order-preserving
+// uint encoding + atomicMin/Max (the reference does this on the CPU: prePartitionedDataVariant.cu:230-232).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200knn {
+
+namespace {
+
+__global__ void k_bounds_init(unsigned* b) {
+  if (threadIdx.x < 3) b[threadIdx.x] = 0xffffffffu;       // running min (ordered encoding)
+  else if (threadIdx.x < 6) b[threadIdx.x] = 0u;            // running max
+}
+
+__global__ void __launch_bounds__(256)
+k_bounds(const float* __restrict__ xyz, int64_t n, unsigned* __restrict__ b) {
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      const float v = xyz[3 * i + a];
+      lo[a] = fminf(lo[a], v);
+      hi[a] = fmaxf(hi[a], v);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(kFullMask, lo[a], o));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(kFullMask, hi[a], o));
+    }
+  }
+  if (lane_id() == 0) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      if (lo[a] <= hi[a]) {
+        atomicMin(&b[a], f2ord(lo[a]));
+        atomicMax(&b[3 + a], f2ord(hi[a]));
+      }
+    }
+  }
+}
+
+__global__ void k_bounds_decode(const unsigned* __restrict__ b, float* __restrict__ out) {
+  const int t = threadIdx.x;
+  if (t < 6) out[t] = ord2f(b[t]);
+}
+
+__global__ void __launch_bounds__(256)
+k_morton(const float* __restrict__ xyz, int64_t n, const float* __restrict__ bounds6,
+         uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float lox = bounds6[0], loy = bounds6[1], loz = bounds6[2];
+  const float ex = bounds6[3] - lox, ey = bounds6[4] - loy, ez = bounds6[5] - loz;
+  const float ivx = ex > 0.f ? 1.f / ex : 0.f;
+  const float ivy = ey > 0.f ? 1.f / ey : 0.f;
+  const float ivz = ez > 0.f ? 1.f / ez : 0.f;
+  keys[i] = morton63(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], lox, loy, loz, ivx, ivy, ivz);
+  vals[i] = (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(256)
+k_gather(const float* __restrict__ xyz, const uint32_t* __restrict__ order,
+         const uint32_t* __restrict__ ids, uint32_t id_offset, int64_t n, Float4* __restrict__ sorted) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t src = order[i];
+  float4 p;
+  p.x = xyz[3 * (size_t)src];
+  p.y = xyz[3 * (size_t)src + 1];
+  p.z = xyz[3 * (size_t)src + 2];
+  p.w = __uint_as_float(ids ? ids[src] : src + id_offset);
+  reinterpret_cast<float4*>(sorted)[i] = p;
+}
+
+__device__ __forceinline__ void warp_minmax3(float& lx, float& ly, float& lz, float& hx, float& hy, float& hz) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lx = fminf(lx, __shfl_xor_sync(kFullMask, lx, o));
+    ly = fminf(ly, __shfl_xor_sync(kFullMask, ly, o));
+    lz = fminf(lz, __shfl_xor_sync(kFullMask, lz, o));
+    hx = fmaxf(hx, __shfl_xor_sync(kFullMask, hx, o));
+    hy = fmaxf(hy, __shfl_xor_sync(kFullMask, hy, o));
+    hz = fmaxf(hz, __shfl_xor_sync(kFullMask, hz, o));
+  }
+}
+
+// One warp per leaf (32 consecutive sorted points).
+__global__ void __launch_bounds__(256)
+k_leaf_boxes(const Float4* __restrict__ pts, int64_t n, int num_leaves, Box* __restrict__ out) {
+  const int leaf = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (leaf >= num_leaves) return;
+  const int lane = lane_id();
+  const int64_t i = (int64_t)leaf * kGroup + lane;
+  float lx = INFINITY, ly = INFINITY, lz = INFINITY, hx = -INFINITY, hy = -INFINITY, hz = -INFINITY;
+  if (i < n) {
+    const float4 p = reinterpret_cast<const float4*>(pts)[i];
+    lx = hx = p.x; ly = hy = p.y; lz = hz = p.z;
+  }
+  warp_minmax3(lx, ly, lz, hx, hy, hz);
+  if (lane == 0) {
+    const int64_t rem = n - (int64_t)leaf * kGroup;
+    const int cnt = rem < kGroup ? (int)rem : kGroup;
+    float4 a = make_float4(lx, ly, lz, __int_as_float(cnt));
+    float4 b = make_float4(hx, hy, hz, 0.f);
+    reinterpret_cast<float4*>(out)[2 * (size_t)leaf] = a;
+    reinterpret_cast<float4*>(out)[2 * (size_t)leaf + 1] = b;
+  }
+}
+
+// One warp per parent: union of up to 32 child boxes.
+__global__ void __launch_bounds__(256)
+k_upper_boxes(const Box* __restrict__ child, int child_count, int parent_count, Box* __restrict__ out) {
+  const int parent = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (parent >= parent_count) return;
+  const int lane = lane_id();
+  const int c = parent * kFanout + lane;
+  float lx = INFINITY, ly = INFINITY, lz = INFINITY, hx = -INFINITY, hy = -INFINITY, hz = -INFINITY;
+  if (c < child_count) {
+    const float4 a = reinterpret_cast<const float4*>(child)[2 * (size_t)c];
+    const float4 b = reinterpret_cast<const float4*>(child)[2 * (size_t)c + 1];
+    lx = a.x; ly = a.y; lz = a.z; hx = b.x; hy = b.y; hz = b.z;
+  }
+  warp_minmax3(lx, ly, lz, hx, hy, hz);
+  if (lane == 0) {
+    const int rem = child_count - parent * kFanout;
+    const int cnt = rem < kFanout ? rem : kFanout;
+    reinterpret_cast<float4*>(out)[2 * (size_t)parent] = make_float4(lx, ly, lz, __int_as_float(cnt));
+    reinterpret_cast<float4*>(out)[2 * (size_t)parent + 1] = make_float4(hx, hy, hz, 0.f);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_scatter_results(const Float4* __restrict__ pts, const float* __restrict__ res, int64_t n,
+                  uint32_t id_offset, float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t id = __float_as_uint(pts[i].w) - id_offset;
+  out[id] = res[i];
+}
+
+inline int grid_for(int64_t n, int block) { return (int)div_up(n, block); }
+
+}  // namespace
+
+int bounds_init(unsigned* d_bounds_ord, cudaStream_t stream) {
+  k_bounds_init<<<1, 32, 0, stream>>>(d_bounds_ord);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int bounds_accumulate(const float* d_xyz, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  int64_t blocks = div_up(n, 256 * 8);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  k_bounds<<<(int)blocks, 256, 0, stream>>>(d_xyz, n, d_bounds_ord);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int bounds_decode(const unsigned* d_bounds_ord, float* d_bounds6, cudaStream_t stream) {
+  k_bounds_decode<<<1, 32, 0, stream>>>(d_bounds_ord, d_bounds6);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int morton_keys(const float* d_xyz, int64_t n, const float* d_bounds6, uint64_t* keys,
+                uint32_t* vals, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  k_morton<<<grid_for(n, 256), 256, 0, stream>>>(d_xyz, n, d_bounds6, keys, vals);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int gather_points(const float* d_xyz, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
+                  int64_t n, Float4* sorted, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  k_gather<<<grid_for(n, 256), 256, 0, stream>>>(d_xyz, order, ids, id_offset, n, sorted);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int build_leaf_boxes(const Float4* sorted, int64_t n, Box* level0, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  const int num_leaves = (int)div_up(n, kGroup);
+  k_leaf_boxes<<<grid_for(num_leaves, 8), 256, 0, stream>>>(sorted, n, num_leaves, level0);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int build_upper_boxes(const Box* child, int child_count, Box* parent, cudaStream_t stream) {
+  const int parent_count = (int)div_up(child_count, kFanout);
+  k_upper_boxes<<<grid_for(parent_count, 8), 256, 0, stream>>>(child, child_count, parent_count, parent);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int scatter_results(const Float4* sorted_pts, const float* sorted_result, int64_t n,
+                    uint32_t id_offset, float* out, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  k_scatter_results<<<grid_for(n, 256), 256, 0, stream>>>(sorted_pts, sorted_result, n, id_offset, out);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200knn

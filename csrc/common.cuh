@@ -1,0 +1,88 @@
+// common.cuh — error handling, small device helpers, system-scope flag primitives.
+// Role of cukd/common.h:276-343 (CUKD_CUDA_CHECK/CALL) in the reference; re-designed:
+// library code never throws or exits, it records an error string and returns a code.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include "knn_math.h"
+
+namespace b200knn {
+
+void set_last_error(const std::string& msg);   // api.cpp
+const char* last_error_cstr();
+void note_launch();                             // api.cu: counts kernel launches (bench evidence)
+
+#define KNN_CUDA_TRY(expr)                                                               \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      ::b200knn::set_last_error(std::string(#expr) + " failed: " +                       \
+                                cudaGetErrorString(_e) + " (" + __FILE__ + ":" +         \
+                                std::to_string(__LINE__) + ")");                         \
+      return (int)_e == 0 ? -1 : (int)_e;                                                \
+    }                                                                                    \
+  } while (0)
+
+#define KNN_REQUIRE(cond, msg)                                                           \
+  do {                                                                                   \
+    if (!(cond)) {                                                                       \
+      ::b200knn::set_last_error(std::string(msg) + " (" + __FILE__ + ":" +               \
+                                std::to_string(__LINE__) + ")");                         \
+      return -2;                                                                         \
+    }                                                                                    \
+  } while (0)
+
+#if defined(__CUDACC__)
+
+constexpr unsigned kFullMask = 0xffffffffu;
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+// Order-preserving float <-> uint mapping (for atomicMin/Max on floats of either sign).
+// Same idea as the reference's AtomicBox encoding (cukd/spatial-kdtree.h:102-187).
+__device__ __forceinline__ unsigned f2ord(float f) {
+  unsigned u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ord2f(unsigned u) {
+  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float(u);
+#else
+  float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+
+// ---- system-scope release/acquire flags (visible across NVLink peers) ----
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// Spin until *p >= want (sequence numbers only grow). Called by one lane.
+__device__ __forceinline__ void wait_flag_ge(const unsigned* p, unsigned want) {
+  unsigned ns = 32;
+  while ((int)(ld_acquire_sys(p) - want) < 0) {
+    __nanosleep(ns);
+    if (ns < 1024) ns <<= 1;
+  }
+}
+
+// L1-bypassing loads for buffers a peer GPU writes into (L2 is the coherence point).
+__device__ __forceinline__ float ldcg_f(const float* p) { return __ldcg(p); }
+__device__ __forceinline__ float4 ldcg_f4(const float4* p) { return __ldcg(p); }
+__device__ __forceinline__ int ldcg_i(const int* p) { return __ldcg(p); }
+
+#endif  // __CUDACC__
+
+}  // namespace b200knn

@@ -1,0 +1,270 @@
+// cpu_engine.cpp — host-side oracle and mirror engine (no CUDA needed).
+//
+//  * b200knn_cpu_bruteforce: the test oracle. Independent of every other piece of this library
+//    except the distance expression: all n squared distances per query, std::nth_element.
+//    Role of verifyKNN in the reference's test driver
+//    (submodules/cudaKDTree/testing/floatN-knn-and-fcp.cu:292-335), but exact instead of 1e-6.
+//  * b200knn_cpu_knn: the GPU algorithm restated for the host — Morton sort, 32-point leaves,
+//    32-ary box tree, group traversal with shared radius, strided 4-ary heaps. It validates the
+//    culling logic on machines without a GPU and is the CPU backend of the executables.
+//    Role of buildTree_host (cukd/builder_thrust.h:514-601), the reference's only CPU path.
+//
+// Compiled with -ffp-contract=off so that fmaf() calls are the only fused operations.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <numeric>
+#include <string>
+#include <thread>
+#include <vector>
+#include "../include/b200knn.h"
+#include "knn_math.h"
+
+namespace b200knn {
+void set_last_error(const std::string& msg);
+
+namespace {
+
+template <typename F>
+void parallel_for(int64_t n, int num_threads, F f) {
+  if (num_threads <= 0) num_threads = (int)std::thread::hardware_concurrency();
+  if (num_threads < 1) num_threads = 1;
+  if ((int64_t)num_threads > n) num_threads = (int)(n > 0 ? n : 1);
+  if (num_threads == 1) { f(0, n); return; }
+  std::vector<std::thread> ts;
+  const int64_t per = (n + num_threads - 1) / num_threads;
+  for (int t = 0; t < num_threads; ++t) {
+    const int64_t b = t * per, e = std::min<int64_t>(n, b + per);
+    if (b >= e) break;
+    ts.emplace_back([=] { f(b, e); });
+  }
+  for (auto& t : ts) t.join();
+}
+
+struct CpuTree {
+  std::vector<Float4> pts;                 // sorted, padded to groups*32 with +inf points
+  std::vector<Box> boxes[kMaxLevels];
+  int levels = 0;
+  int64_t n = 0;
+  float lo[3], hi[3];
+};
+
+Box make_box(const float* lo, const float* hi, int cnt) {
+  Box b;
+  b.lox = lo[0]; b.loy = lo[1]; b.loz = lo[2];
+  b.hix = hi[0]; b.hiy = hi[1]; b.hiz = hi[2];
+  memcpy(&b.cnt_bits, &cnt, 4);
+  b.pad = 0.f;
+  return b;
+}
+
+void bounds_of(const float* xyz, int64_t n, float* lo, float* hi) {
+  for (int a = 0; a < 3; ++a) { lo[a] = INFINITY; hi[a] = -INFINITY; }
+  for (int64_t i = 0; i < n; ++i)
+    for (int a = 0; a < 3; ++a) {
+      lo[a] = fminf(lo[a], xyz[3 * i + a]);
+      hi[a] = fmaxf(hi[a], xyz[3 * i + a]);
+    }
+}
+
+std::vector<uint32_t> morton_order(const float* xyz, int64_t n, const float* lo, const float* hi) {
+  float iv[3];
+  for (int a = 0; a < 3; ++a) { const float e = hi[a] - lo[a]; iv[a] = e > 0.f ? 1.f / e : 0.f; }
+  std::vector<uint64_t> keys(n);
+  for (int64_t i = 0; i < n; ++i)
+    keys[i] = morton63(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], lo[0], lo[1], lo[2], iv[0], iv[1], iv[2]);
+  std::vector<uint32_t> order(n);
+  std::iota(order.begin(), order.end(), 0u);
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+  return order;
+}
+
+void build_tree(const float* xyz, int64_t n, CpuTree& t) {
+  t.n = n;
+  bounds_of(xyz, n, t.lo, t.hi);
+  if (n == 0) { t.levels = 0; return; }
+  const std::vector<uint32_t> order = morton_order(xyz, n, t.lo, t.hi);
+  const int64_t groups = div_up(n, kGroup);
+  t.pts.assign(groups * kGroup, Float4{INFINITY, INFINITY, INFINITY, 0.f});
+  for (int64_t i = 0; i < n; ++i) {
+    const uint32_t s = order[i];
+    Float4 p{xyz[3 * (size_t)s], xyz[3 * (size_t)s + 1], xyz[3 * (size_t)s + 2], 0.f};
+    memcpy(&p.w, &s, 4);
+    t.pts[i] = p;
+  }
+  t.boxes[0].resize(groups);
+  for (int64_t g = 0; g < groups; ++g) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    const int cnt = (int)std::min<int64_t>(kGroup, n - g * kGroup);
+    for (int j = 0; j < cnt; ++j) {
+      const Float4& p = t.pts[g * kGroup + j];
+      lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
+      hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
+    }
+    t.boxes[0][g] = make_box(lo, hi, cnt);
+  }
+  int levels = 1;
+  while ((int64_t)t.boxes[levels - 1].size() > kFanout) {
+    const auto& ch = t.boxes[levels - 1];
+    const int64_t pc = div_up((int64_t)ch.size(), kFanout);
+    t.boxes[levels].resize(pc);
+    for (int64_t p = 0; p < pc; ++p) {
+      float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+      const int cnt = (int)std::min<int64_t>(kFanout, (int64_t)ch.size() - p * kFanout);
+      for (int j = 0; j < cnt; ++j) {
+        const Box& c = ch[p * kFanout + j];
+        lo[0] = fminf(lo[0], c.lox); lo[1] = fminf(lo[1], c.loy); lo[2] = fminf(lo[2], c.loz);
+        hi[0] = fmaxf(hi[0], c.hix); hi[1] = fmaxf(hi[1], c.hiy); hi[2] = fmaxf(hi[2], c.hiz);
+      }
+      t.boxes[levels][p] = make_box(lo, hi, cnt);
+    }
+    ++levels;
+  }
+  t.levels = levels;
+}
+
+struct Group {
+  float q[kGroup][3];
+  int cnt = 0;
+  float glo[3], ghi[3];
+  float maxR2;
+  std::vector<float> heap;   // [k][32]
+  int k;
+  float top(int lane) const { return heap[lane]; }
+  void refresh_max() {
+    maxR2 = 0.f;
+    for (int l = 0; l < cnt; ++l) maxR2 = fmaxf(maxR2, top(l));
+  }
+};
+
+void leaf(const CpuTree& t, int64_t leaf_idx, Group& g) {
+  const Box& b = t.boxes[0][leaf_idx];
+  bool any = false;
+  for (int l = 0; l < g.cnt && !any; ++l)
+    any = point_box_lb(g.q[l][0], g.q[l][1], g.q[l][2], b.lox, b.loy, b.loz, b.hix, b.hiy, b.hiz) < g.top(l);
+  if (!any) return;
+  for (int l = 0; l < g.cnt; ++l) {
+    for (int j = 0; j < kGroup; ++j) {
+      const Float4& p = t.pts[leaf_idx * kGroup + j];
+      const float d2 = dist2(g.q[l][0], g.q[l][1], g.q[l][2], p.x, p.y, p.z);
+      if (d2 < g.top(l)) heap_replace_top(g.heap.data() + l, kGroup, g.k, d2);
+    }
+  }
+  g.refresh_max();
+}
+
+void visit(const CpuTree& t, int level, int64_t base, int count, Group& g) {
+  float key[kFanout];
+  bool todo[kFanout];
+  for (int c = 0; c < count; ++c) {
+    const Box& b = t.boxes[level][base + c];
+    key[c] = box_box_lb(g.glo[0], g.glo[1], g.glo[2], g.ghi[0], g.ghi[1], g.ghi[2],
+                        b.lox, b.loy, b.loz, b.hix, b.hiy, b.hiz);
+    todo[c] = true;
+  }
+  for (;;) {
+    int who = -1;
+    for (int c = 0; c < count; ++c) {
+      if (!todo[c]) continue;
+      if (!(key[c] < g.maxR2)) { todo[c] = false; continue; }
+      if (who < 0 || key[c] < key[who]) who = c;
+    }
+    if (who < 0) break;
+    todo[who] = false;
+    const int64_t child = base + who;
+    if (level == 0) {
+      leaf(t, child, g);
+    } else {
+      const int64_t rem = (int64_t)t.boxes[level - 1].size() - child * kFanout;
+      visit(t, level - 1, child * kFanout, (int)std::min<int64_t>(rem, kFanout), g);
+    }
+  }
+}
+
+}  // namespace
+}  // namespace b200knn
+
+using namespace b200knn;
+
+extern "C" int b200knn_cpu_bruteforce(const float* xyz, int64_t n, const float* queries, int64_t nq, int k,
+                                      float max_radius, float* out, int num_threads) {
+  if (k < 1 || n < 0 || nq < 0 || (!xyz && n) || (!queries && nq) || (!out && nq)) {
+    set_last_error("cpu_bruteforce: invalid argument");
+    return -2;
+  }
+  const float sent = sentinel_d2(max_radius);
+  parallel_for(nq, num_threads, [&](int64_t b, int64_t e) {
+    std::vector<float> d(n);
+    for (int64_t qi = b; qi < e; ++qi) {
+      const float qx = queries[3 * qi], qy = queries[3 * qi + 1], qz = queries[3 * qi + 2];
+      for (int64_t i = 0; i < n; ++i) d[i] = dist2(qx, qy, qz, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+      float kth = INFINITY;
+      if (n >= k) {
+        std::nth_element(d.begin(), d.begin() + (k - 1), d.end());
+        kth = d[k - 1];
+      }
+      out[qi] = finalize_kth(fminf(kth, sent));
+    }
+  });
+  return 0;
+}
+
+extern "C" int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries, int64_t nq, int k,
+                               float max_radius, float* out, int num_threads) {
+  if (k < 1 || n < 0 || (!xyz && n)) {
+    set_last_error("cpu_knn: invalid argument");
+    return -2;
+  }
+  CpuTree tree;
+  build_tree(xyz, n, tree);
+  // queries: the indexed points themselves (sorted order = groups are leaves), or an external set
+  // ordered along the tree's Morton grid.
+  std::vector<Float4> qs;
+  int64_t qn;
+  if (queries == nullptr) {
+    qs = tree.pts;
+    qn = n;
+  } else {
+    qn = nq;
+    const std::vector<uint32_t> order = morton_order(queries, nq, tree.lo, tree.hi);
+    qs.resize(div_up(std::max<int64_t>(nq, 1), kGroup) * kGroup);
+    for (int64_t i = 0; i < nq; ++i) {
+      const uint32_t s = order[i];
+      Float4 p{queries[3 * (size_t)s], queries[3 * (size_t)s + 1], queries[3 * (size_t)s + 2], 0.f};
+      memcpy(&p.w, &s, 4);
+      qs[i] = p;
+    }
+  }
+  const float sent = sentinel_d2(max_radius);
+  const int64_t groups = div_up(qn, kGroup);
+  parallel_for(groups, num_threads, [&](int64_t gb, int64_t ge) {
+    Group g;
+    g.k = k;
+    g.heap.resize((size_t)k * kGroup);
+    for (int64_t gi = gb; gi < ge; ++gi) {
+      g.cnt = (int)std::min<int64_t>(kGroup, qn - gi * kGroup);
+      std::fill(g.heap.begin(), g.heap.end(), sent);
+      for (int a = 0; a < 3; ++a) { g.glo[a] = INFINITY; g.ghi[a] = -INFINITY; }
+      for (int l = 0; l < g.cnt; ++l) {
+        const Float4& p = qs[gi * kGroup + l];
+        g.q[l][0] = p.x; g.q[l][1] = p.y; g.q[l][2] = p.z;
+        for (int a = 0; a < 3; ++a) {
+          g.glo[a] = fminf(g.glo[a], g.q[l][a]);
+          g.ghi[a] = fmaxf(g.ghi[a], g.q[l][a]);
+        }
+      }
+      g.refresh_max();
+      if (tree.levels > 0) {
+        const int top = tree.levels - 1;
+        visit(tree, top, 0, (int)tree.boxes[top].size(), g);
+      }
+      for (int l = 0; l < g.cnt; ++l) {
+        uint32_t id;
+        memcpy(&id, &qs[gi * kGroup + l].w, 4);
+        out[id] = finalize_kth(g.top(l));
+      }
+    }
+  });
+  return 0;
+}

@@ -1,0 +1,93 @@
+// kernels.h — internal C++ interfaces between the .cu translation units and api.cpp.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "knn_math.h"
+
+namespace b200knn {
+
+// ---------------- radix sort (radix_sort.cu) ----------------
+size_t radix_sort_scratch_bytes(int64_t n);
+// Sorts bits [begin_bit, end_bit) in 8-bit digits. Ping-pongs between (keys,vals) and the tmp
+// pair; *result_in_tmp tells where the sorted sequence ended up.
+int radix_sort_u64(uint64_t* keys, uint32_t* vals, uint64_t* keys_tmp, uint32_t* vals_tmp,
+                   uint32_t* scratch, int64_t n, int begin_bit, int end_bit, cudaStream_t stream,
+                   int* result_in_tmp);
+int radix_sort_u32(uint32_t* keys, uint32_t* vals, uint32_t* keys_tmp, uint32_t* vals_tmp,
+                   uint32_t* scratch, int64_t n, int begin_bit, int end_bit, cudaStream_t stream,
+                   int* result_in_tmp);
+
+// ---------------- tree (build.cu) ----------------
+// Wide (32-ary) bounding-box tree over Morton-sorted points. Level 0 = leaf boxes (32 points
+// each), level l+1 groups 32 consecutive boxes of level l. Implicit topology: no pointers.
+struct TreeView {
+  const Float4* pts;            // sorted points; .w carries the caller's point id (as bits)
+  const Box* boxes[kMaxLevels]; // boxes[l][i]
+  int count[kMaxLevels];        // number of boxes on level l
+  int levels;                   // number of levels in use (top level has <= 32 boxes)
+  int n;                        // number of points
+};
+
+struct Bounds { float lo[3]; float hi[3]; };
+
+// d_bounds_ord: 6 unsigned (order-preserving encoding), must be initialised by bounds_init.
+int bounds_init(unsigned* d_bounds_ord, cudaStream_t stream);
+int bounds_accumulate(const float* d_xyz, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream);
+int bounds_decode(const unsigned* d_bounds_ord, float* d_bounds6, cudaStream_t stream);
+// keys[i] = morton63(point i) relative to *d_bounds6 (device-resident lo[3],hi[3]); vals[i] = i.
+int morton_keys(const float* d_xyz, int64_t n, const float* d_bounds6, uint64_t* keys,
+                uint32_t* vals, cudaStream_t stream);
+// sorted[i] = (xyz[order[i]], id = ids ? ids[order[i]] : order[i] + id_offset)
+int gather_points(const float* d_xyz, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
+                  int64_t n, Float4* sorted, cudaStream_t stream);
+int build_leaf_boxes(const Float4* sorted, int64_t n, Box* level0, cudaStream_t stream);
+int build_upper_boxes(const Box* child, int child_count, Box* parent, cudaStream_t stream);
+
+// ---------------- query / ring (query.cu) ----------------
+constexpr int kMaxRanks = 16;
+
+// One persistent kernel does everything between "points are sorted" and "k-th distances exist":
+// it walks tasks (step s, group g); step s = chunk*R + hop. hop 0 takes fresh queries from the
+// local tree's own points, hops 1..R-1 take groups another rank pushed into the local inbox,
+// the last hop writes k-th distances to the group's home rank. R == 1 degenerates to a plain
+// single-GPU all-kNN kernel with no flags touched.
+struct RingParams {
+  TreeView tree;
+  int k;
+  float sentinel;              // max_radius^2 or +inf
+  int R, rank;
+  int groups_per_chunk;        // Gc: identical on all ranks
+  int num_chunks;              // C: identical on all ranks
+  int step_begin, step_end;    // run steps [step_begin, step_end) (fused ring: 0 .. C*R)
+  int use_flags;               // 1: in-kernel peer handshake; 0: host orders the steps (baseline transport)
+  unsigned seq_base;
+  // queries of hop 0: the local tree's own points, or an external sorted query set
+  const Float4* home_queries;  // tree.pts for self-kNN
+  int64_t home_n;
+  // local inbox (written by the previous rank)
+  const float* inbox_heap[2];  // [Gc][k][32]
+  const Float4* inbox_pos[2];  // [Gc][32]
+  const int* inbox_cnt[2];     // [Gc]
+  const unsigned* flag_in[2];  // [Gc]  data-ready sequence numbers (written by prev)
+  const unsigned* ack_in[2];   // [Gc]  slot-consumed sequence numbers (written by next)
+  // peer pointers
+  float* next_heap[2];
+  Float4* next_pos[2];
+  int* next_cnt[2];
+  unsigned* next_flag[2];      // next rank's flag_in
+  unsigned* prev_ack[2];       // prev rank's ack_in
+  float* result_sorted;        // home rank's result array for the LAST hop (next rank's, or own if R==1)
+  unsigned long long* task_counter;   // local, zeroed before launch
+  unsigned long long* stats;   // optional [4]: leaves visited, candidates tested, heap inserts, inner nodes
+};
+
+size_t ring_smem_bytes(int k, int warps_per_cta);
+int ring_pick_warps_per_cta(int k);
+int ring_launch(const RingParams& p, int num_sms, cudaStream_t stream);
+
+// out[id(i)] = sorted_result[i]  (id taken from pts[i].w, minus id_offset)
+int scatter_results(const Float4* sorted_pts, const float* sorted_result, int64_t n,
+                    uint32_t id_offset, float* out, cudaStream_t stream);
+
+}  // namespace b200knn

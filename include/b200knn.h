@@ -1,0 +1,124 @@
+/* b200knn.h — C ABI of libb200knn (Blackwell-native large-scale k-nearest-neighbour distances).
+ *
+ * Everything here is callable from C, C++ (the cudaMpiKNN_* executables) and Python (ctypes; see
+ * mpi_cuda_largescaleknn_b200/ops/_lib.py). All functions return 0 on success, non-zero on error;
+ * b200knn_last_error() then holds a human-readable message (thread-local).
+ *
+ * Conventions
+ *   - points / queries: interleaved float32 x,y,z (the reference's raw "float3" layout,
+ *     /root/reference/unorderedDataVariant.cu:41-63), in DEVICE memory unless the name says cpu.
+ *   - result: one float32 per query = distance to the k-th nearest point, the query's own entry
+ *     included when it is part of the indexed set; +inf if fewer than k points exist; with a finite
+ *     max_radius r, sqrt(r*r) if fewer than k points lie inside r
+ *     (/root/reference/unorderedDataVariant.cu:89-103).
+ *   - `stream` is a cudaStream_t passed as void* (0 = default stream). Calls enqueue work and return;
+ *     they are asynchronous unless stated otherwise.
+ */
+#ifndef B200KNN_H
+#define B200KNN_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200KNN_MAX_RANKS 16
+#define B200KNN_IPC_BLOB_BYTES 256
+
+typedef struct b200knn_index b200knn_index;
+typedef struct b200knn_ring b200knn_ring;
+
+const char* b200knn_last_error(void);
+int b200knn_version(void);
+/* Number of kernels this library has launched in the calling process (monotonic). */
+uint64_t b200knn_launch_count(void);
+
+/* ---- spatial index over one GPU's points -------------------------------------------------------
+ * Role of cukd::buildTree (cudaKDTree/cukd/builder.h:108-151). One radix sort of Morton keys + a
+ * 32-ary box hierarchy. `ids` (device, uint32, optional) are caller-side identifiers stored with the
+ * points; when NULL, id = position + id_offset. Synchronises `stream` before returning (allocation
+ * sizes are computed on the host). */
+int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
+                         void* stream, b200knn_index** out);
+void b200knn_index_destroy(b200knn_index* idx);
+int64_t b200knn_index_num_points(const b200knn_index* idx);
+int b200knn_index_num_levels(const b200knn_index* idx);
+/* host float[6]: lo.xyz, hi.xyz of the indexed points (synchronous). */
+int b200knn_index_bounds(const b200knn_index* idx, float* host_bounds6);
+/* Debug/test helpers: copy the sorted points (x,y,z,id-bits as float4) or one level of boxes to
+ * host memory (synchronous). */
+int b200knn_index_copy_sorted(const b200knn_index* idx, float* host_xyzw);
+int b200knn_index_copy_boxes(const b200knn_index* idx, int level, float* host_boxes8, int* count);
+
+/* ---- single-GPU queries ------------------------------------------------------------------------
+ * knn_self: every indexed point is a query (the reference's use case); d_out[i] belongs to the i-th
+ * point handed to index_create. Role of runQuery + extractFinalResult
+ * (/root/reference/unorderedDataVariant.cu:75-103). */
+int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, void* stream);
+/* knn_query: arbitrary query points against the index (cukd::stackFree::knn, cukd/knn.h:617-631).
+ * Synchronises `stream` (temporary buffers). */
+int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, int k, float max_radius,
+                      float* d_out, void* stream);
+/* Traversal counters of the most recent query call on this index (synchronous):
+ * [0] leaves visited by groups, [1] candidate distance evaluations per lane, [2] heap insertions,
+ * [3] inner nodes opened. Role of CUKD_ENABLE_STATS (cukd/common.h:349-361). */
+int b200knn_index_stats(b200knn_index* idx, uint64_t out4[4]);
+int b200knn_index_enable_stats(b200knn_index* idx, int on);
+
+/* ---- multi-GPU fused ring ----------------------------------------------------------------------
+ * One process per GPU. Query groups and their k-candidate heaps travel rank -> rank+1; every GPU's
+ * tree stays home. The kernel writes into the next GPU's inbox over NVLink and signals with
+ * system-scope release/acquire flags; there is no host or NCCL call between hops.
+ * Role of the MPI ring in /root/reference/unorderedDataVariant.cu:173-205.
+ *
+ * Call order on every rank:
+ *   ring_create -> ring_export -> (allgather the blobs by any means) -> ring_connect -> barrier
+ *   -> ring_run -> stream sync -> barrier -> ring_results
+ * `max_points_any_rank` must be identical on all ranks. `groups_per_chunk` (0 = default) bounds the
+ * in-flight candidate memory: 2 * groups_per_chunk * (k*128 + 516) bytes per GPU. */
+int b200knn_ring_create(b200knn_index* idx, int rank, int world, int k, int64_t max_points_any_rank,
+                        int groups_per_chunk, b200knn_ring** out);
+void b200knn_ring_destroy(b200knn_ring* ring);
+int b200knn_ring_export(b200knn_ring* ring, void* blob /* B200KNN_IPC_BLOB_BYTES */);
+int b200knn_ring_connect(b200knn_ring* ring, const void* all_blobs /* world * B200KNN_IPC_BLOB_BYTES */);
+int b200knn_ring_run(b200knn_ring* ring, float max_radius, void* stream);
+int b200knn_ring_results(b200knn_ring* ring, float* d_out, void* stream);
+int64_t b200knn_ring_comm_bytes(const b200knn_ring* ring);
+
+/* Low-level: run a range of ring steps with caller-provided buffers and NO in-kernel handshake
+ * (use_flags = 0). This is the baseline transport path: the host moves outbox -> peer inbox with
+ * NCCL between launches. Buffer shapes: heap [groups_per_chunk][k][32] float, pos
+ * [groups_per_chunk][32] float4, cnt [groups_per_chunk] int32. */
+typedef struct b200knn_step_args {
+  int k, world, rank;
+  int groups_per_chunk, num_chunks;
+  int step_begin, step_end;
+  float max_radius;
+  const float* inbox_heap[2];
+  const float* inbox_pos[2];
+  const int32_t* inbox_cnt[2];
+  float* outbox_heap[2];
+  float* outbox_pos[2];
+  int32_t* outbox_cnt[2];
+  float* result_sorted;   /* receives k-th distances of groups finishing their last hop here */
+} b200knn_step_args;
+int b200knn_run_steps(b200knn_index* idx, const b200knn_step_args* args, void* stream);
+/* out[id - id_offset] = sorted_result[i] for the index's own points (undo the spatial order). */
+int b200knn_index_unsort(b200knn_index* idx, const float* d_sorted_result, float* d_out, void* stream);
+
+/* ---- CPU side (no GPU needed): oracle and mirror engine ----------------------------------------
+ * cpu_bruteforce: exact O(nq*n) k-th distance with the canonical fp32 expression
+ *   fmaf(dz,dz, fmaf(dx,dx, dy*dy)), d = query - point  (SURVEY.md fact 7); the test oracle.
+ *   Role of verifyKNN (cudaKDTree/testing/floatN-knn-and-fcp.cu:292-335).
+ * cpu_knn: the same index + group traversal as the GPU path, on the host (role of
+ *   buildTree_host, cukd/builder_thrust.h:514-601); used as CPU backend and for cross-checks. */
+int b200knn_cpu_bruteforce(const float* xyz, int64_t n, const float* queries, int64_t nq, int k,
+                           float max_radius, float* out, int num_threads);
+int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries_or_null, int64_t nq, int k,
+                    float max_radius, float* out, int num_threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200KNN_H */

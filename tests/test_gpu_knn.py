@@ -1,0 +1,183 @@
+"""GPU numerics: every CUDA path is compared bit-for-bit with the CPU brute-force oracle
+(plain fp32 reference of the same op)."""
+import math
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from mpi_cuda_largescaleknn_b200.utils import generators as gen
+from mpi_cuda_largescaleknn_b200.utils.oracle import bit_equal, bruteforce
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _knn(x, k, r=math.inf):
+    from mpi_cuda_largescaleknn_b200.ops.knn import knn
+    return knn(torch.from_numpy(x).to(_dev()), k, r).cpu().numpy()
+
+
+def test_library_is_native_and_loaded():
+    from mpi_cuda_largescaleknn_b200.ops._lib import LIB_PATH, lib
+    assert lib().b200knn_version() >= 100
+    maps = open("/proc/self/maps").read()
+    assert str(LIB_PATH) in maps
+
+
+def morton63_np(x, lo, hi):
+    ext = hi - lo
+    inv = np.where(ext > 0, np.float32(1.0) / ext, np.float32(0)).astype(np.float32)
+    t = np.clip((x - lo) * inv, 0, 1).astype(np.float32)
+    q = np.minimum((t * np.float32(2097151.0)).astype(np.uint64), np.uint64(2097151))
+    def spread(v):
+        v = v & np.uint64(0x1fffff)
+        v = (v | (v << np.uint64(32))) & np.uint64(0x1f00000000ffff)
+        v = (v | (v << np.uint64(16))) & np.uint64(0x1f0000ff0000ff)
+        v = (v | (v << np.uint64(8))) & np.uint64(0x100f00f00f00f00f)
+        v = (v | (v << np.uint64(4))) & np.uint64(0x10c30c30c30c30c3)
+        v = (v | (v << np.uint64(2))) & np.uint64(0x1249249249249249)
+        return v
+    return (spread(q[:, 0]) << np.uint64(2)) | (spread(q[:, 1]) << np.uint64(1)) | spread(q[:, 2])
+
+
+@pytest.mark.parametrize("n", [1, 31, 32, 33, 4095, 4096, 4097, 100_003, 1_000_000])
+def test_index_build_sort_and_boxes(n):
+    """Radix sort + gather + box hierarchy: sorted by Morton key, a permutation of the input,
+    every box is the exact union of its children (the reference's checkTree idea,
+    cudaKDTree/testing/floatN-knn-and-fcp.cu:338-377)."""
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
+    x = gen.uniform(n, seed=n)
+    idx = KnnIndex(torch.from_numpy(x).to(_dev()))
+    b = idx.bounds()
+    assert np.array_equal(b[:3], x.min(0)) and np.array_equal(b[3:], x.max(0))
+    s = idx.sorted_points()
+    ids = s[:, 3].copy().view(np.uint32)
+    assert np.array_equal(np.sort(ids), np.arange(n, dtype=np.uint32))
+    assert np.array_equal(s[:, :3], x[ids])
+    keys = morton63_np(s[:, :3], b[:3], b[3:])
+    assert np.all(keys[1:] >= keys[:-1])
+    # stability: equal keys keep input order
+    same = keys[1:] == keys[:-1]
+    assert np.all(ids[1:][same] > ids[:-1][same])
+    # leaf boxes
+    boxes = idx.boxes(0)
+    nl = (n + 31) // 32
+    assert len(boxes) == nl
+    pad = np.full((nl * 32 - n, 3), np.nan, np.float32)
+    pts = np.concatenate([s[:, :3], pad]).reshape(nl, 32, 3)
+    assert np.array_equal(boxes[:, 0:3], np.nanmin(pts, axis=1))
+    assert np.array_equal(boxes[:, 4:7], np.nanmax(pts, axis=1))
+    cnt = boxes[:, 3].copy().view(np.int32)
+    assert cnt.sum() == n and np.all(cnt[:-1] == 32)
+    prev = boxes
+    for lvl in range(1, idx.num_levels):
+        cur = idx.boxes(lvl)
+        assert len(cur) == (len(prev) + 31) // 32
+        for p in range(len(cur)):
+            ch = prev[p * 32:(p + 1) * 32]
+            assert np.array_equal(cur[p, 0:3], ch[:, 0:3].min(0))
+            assert np.array_equal(cur[p, 4:7], ch[:, 4:7].max(0))
+        prev = cur
+    assert len(prev) <= 32
+    idx.close()
+
+
+@pytest.mark.parametrize("n,k", [(1, 1), (31, 3), (32, 1), (33, 8), (1000, 10), (5000, 100), (20, 50),
+                                 (4097, 7), (30_000, 32), (100_000, 100)])
+def test_knn_self_equals_oracle(n, k):
+    x = gen.uniform(n, seed=11 * n + k)
+    got = _knn(x, k)
+    if n <= 30_000:
+        assert bit_equal(got, bruteforce(x, k=k))
+    else:
+        sel = np.random.default_rng(0).choice(n, 2000, replace=False)
+        assert bit_equal(got[sel], bruteforce(x, queries=x[sel], k=k))
+
+
+def test_knn_k1_is_zero_and_small_n_inf():
+    x = gen.uniform(3000, seed=5)
+    assert np.all(_knn(x, 1) == 0.0)
+    y = gen.uniform(9, seed=6)
+    assert np.all(np.isinf(_knn(y, 10)))
+
+
+@pytest.mark.parametrize("r", [0.01, 0.05, 0.3])
+def test_knn_max_radius(r):
+    x = gen.uniform(20_000, seed=7)
+    assert bit_equal(_knn(x, 16, r), bruteforce(x, k=16, max_radius=r))
+
+
+def test_knn_clustered_duplicates():
+    x = np.concatenate([gen.clustered_surface(20_000, seed=2), np.zeros((100, 3), np.float32),
+                        np.full((70, 3), 0.25, np.float32)])
+    assert bit_equal(_knn(x, 32), bruteforce(x, k=32))
+
+
+def test_knn_negative_and_large_coordinates():
+    rng = np.random.default_rng(3)
+    x = (rng.normal(0, 1000.0, (8000, 3))).astype(np.float32)
+    assert bit_equal(_knn(x, 10), bruteforce(x, k=10))
+
+
+def test_knn_degenerate_plane_and_line():
+    rng = np.random.default_rng(4)
+    x = rng.random((5000, 3), dtype=np.float32)
+    x[:, 2] = 0.5
+    assert bit_equal(_knn(x, 9), bruteforce(x, k=9))
+    x[:, 1] = -1.0
+    assert bit_equal(_knn(x, 9), bruteforce(x, k=9))
+
+
+@pytest.mark.parametrize("k", [221, 500])
+def test_knn_large_k_uses_fewer_warps(k):
+    x = gen.uniform(3000, seed=k)
+    assert bit_equal(_knn(x, k), bruteforce(x, k=k))
+
+
+def test_knn_query_external_points():
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
+    x = gen.uniform(50_000, seed=8)
+    q = gen.uniform(7001, seed=9) * 1.4 - 0.2
+    idx = KnnIndex(torch.from_numpy(x).to(_dev()))
+    got = idx.knn_query(torch.from_numpy(q).to(_dev()), 12).cpu().numpy()
+    assert bit_equal(got, bruteforce(x, queries=q, k=12))
+    # the same index answers self queries afterwards
+    got2 = idx.knn_self(5).cpu().numpy()
+    sel = np.arange(0, 50_000, 50)
+    assert bit_equal(got2[sel], bruteforce(x, queries=x[sel], k=5))
+    idx.close()
+
+
+def test_stats_counters():
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
+    x = gen.uniform(100_000, seed=10)
+    idx = KnnIndex(torch.from_numpy(x).to(_dev()))
+    idx.enable_stats(True)
+    idx.knn_self(10)
+    torch.cuda.synchronize()
+    st = idx.stats()
+    groups = (100_000 + 31) // 32
+    assert st["leaves_visited"] >= groups            # at least its own leaf
+    assert st["leaves_visited"] < groups * 400       # culling works
+    assert st["heap_inserts"] >= 100_000 * 10
+    idx.close()
+
+
+def test_ring_world1_and_baseline_world1_equal_self():
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
+    from mpi_cuda_largescaleknn_b200.parallel.ring import FusedRing, NcclRingBaseline
+    x = gen.uniform(40_000, seed=12)
+    idx = KnnIndex(torch.from_numpy(x).to(_dev()))
+    ref = idx.knn_self(20).cpu().numpy()
+    ring = FusedRing(idx, 20, groups_per_chunk=100)      # 13 chunks
+    assert bit_equal(ring.run().cpu().numpy(), ref)
+    assert bit_equal(ring.run().cpu().numpy(), ref)      # second run: sequence numbers advance
+    ring.close()
+    base = NcclRingBaseline(idx, 20, groups_per_chunk=300)
+    assert bit_equal(base.run().cpu().numpy(), ref)
+    idx.close()
