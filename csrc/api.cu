@@ -111,8 +111,8 @@ int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, u
   KNN_CUDA_TRY(cudaMalloc(&idx->d_bounds_ord, 6 * sizeof(unsigned)));
   KNN_CUDA_TRY(cudaMalloc(&idx->d_bounds6, 6 * sizeof(float)));
   KNN_CUDA_TRY(cudaMalloc(&idx->task_counter, sizeof(unsigned long long)));
-  KNN_CUDA_TRY(cudaMalloc(&idx->stats, 4 * sizeof(unsigned long long)));
-  KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 4 * sizeof(unsigned long long), stream));
+  KNN_CUDA_TRY(cudaMalloc(&idx->stats, 8 * sizeof(unsigned long long)));
+  KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
   int rc;
   if ((rc = bounds_init(idx->d_bounds_ord, stream))) return rc;
   if ((rc = bounds_accumulate(d_xyz, n, idx->d_bounds_ord, stream))) return rc;
@@ -152,6 +152,7 @@ int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, u
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n, 0, 64, stream, &in_tmp))) return rc;
   const uint32_t* order = in_tmp ? vals_tmp : vals;
   if ((rc = gather_points(d_xyz, order, d_ids, id_offset, n, idx->pts, stream))) return rc;
+  if ((rc = refine_runs(idx->pts, n, stream))) return rc;
   if ((rc = build_leaf_boxes(idx->pts, n, idx->boxes[0], stream))) return rc;
   for (int l = 1; l < levels; ++l)
     if ((rc = build_upper_boxes(idx->boxes[l - 1], idx->count[l - 1], idx->boxes[l], stream))) return rc;
@@ -229,7 +230,7 @@ int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, 
   p.home_queries = idx->pts;
   p.home_n = idx->n;
   p.result_sorted = idx->result_sorted;
-  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 4 * sizeof(unsigned long long), stream));
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
   int rc;
   if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
   return scatter_results(idx->pts, idx->result_sorted, idx->n, idx->id_offset, d_out, stream);
@@ -260,13 +261,14 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
   if ((rc = gather_points(d_queries, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
+  if ((rc = refine_runs(qsorted, nq, stream))) return rc;   // compact query groups, same as leaves
   RingParams p;
   fill_local_only(p, idx, k, max_radius);
   p.groups_per_chunk = (int)groups;
   p.home_queries = qsorted;
   p.home_n = nq;
   p.result_sorted = rsorted;
-  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 4 * sizeof(unsigned long long), stream));
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
   if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
   if ((rc = scatter_results(qsorted, rsorted, nq, 0, d_out, stream))) return rc;
   KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
@@ -286,11 +288,11 @@ int b200knn_index_enable_stats(b200knn_index* idx, int on) {
   return 0;
 }
 
-int b200knn_index_stats(b200knn_index* idx, uint64_t out4[4]) {
-  KNN_REQUIRE(idx && out4, "index_stats: NULL argument");
-  unsigned long long h[4];
+int b200knn_index_stats(b200knn_index* idx, uint64_t out8[8]) {
+  KNN_REQUIRE(idx && out8, "index_stats: NULL argument");
+  unsigned long long h[8];
   KNN_CUDA_TRY(cudaMemcpy(h, idx->stats, sizeof(h), cudaMemcpyDeviceToHost));
-  for (int i = 0; i < 4; ++i) out4[i] = h[i];
+  for (int i = 0; i < 8; ++i) out8[i] = h[i];
   return 0;
 }
 
@@ -450,7 +452,7 @@ int b200knn_ring_run(b200knn_ring* r, float max_radius, void* stream_) {
   // last hop of a group runs on the rank before its home: results go to the NEXT rank's array
   p.result_sorted = reinterpret_cast<float*>(nb + NL.result);
   r->seq_base += (unsigned)(r->C * r->world + 8);
-  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 4 * sizeof(unsigned long long), stream));
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
   return ring_launch(p, idx->num_sms, stream);
 }
 

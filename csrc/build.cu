@@ -138,6 +138,93 @@ k_upper_boxes(const Box* __restrict__ child, int child_count, int parent_count, 
   }
 }
 
+// ---- k-d refinement of Morton runs --------------------------------------------------------------
+// A run = 1024 consecutive Morton-sorted points = the 32 leaves under one level-1 node. Consecutive
+// Z-curve points make ragged leaves (elongated, sometimes straddling a curve jump); inside a run we
+// therefore re-order by 5 levels of exact median splits along the widest axis of each segment, which
+// turns the run into a small balanced k-d tree whose 32-point leaves are compact boxes. One CTA per
+// run, everything in shared memory: per level a segment-bbox reduction, then a bitonic sort of
+// 64-bit keys (segment | ordered coordinate | slot). This plays the role of the reference's per-level
+// sort + updateTags (cukd/builder_thrust.h:175-235,486-499) but only below the 1024-point level.
+constexpr int RF_RUN = 1024;
+constexpr int RF_THREADS = 512;
+constexpr int RF_LEVELS = 5;     // 1024 -> 32
+
+__global__ void __launch_bounds__(RF_THREADS)
+k_refine_runs(Float4* __restrict__ pts, int64_t n) {
+  __shared__ float4 P[RF_RUN];
+  __shared__ unsigned long long keys[RF_RUN];
+  __shared__ unsigned segbox[32][6];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int64_t base = (int64_t)blockIdx.x * RF_RUN;
+  const int nrun = (int)((n - base) < RF_RUN ? (n - base) : RF_RUN);
+  float4* gp = reinterpret_cast<float4*>(pts) + base;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int t = tid + h * RF_THREADS;
+    P[t] = (t < nrun) ? gp[t] : make_float4(INFINITY, INFINITY, INFINITY, 0.f);
+  }
+  __syncthreads();
+
+  for (int level = 0; level < RF_LEVELS; ++level) {
+    const int seg_shift = 10 - level;            // segment size = 1 << seg_shift
+    const int nseg = 1 << level;
+    if (tid < nseg * 6) segbox[tid / 6][tid % 6] = (tid % 6) < 3 ? 0xffffffffu : 0u;
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int t = tid + h * RF_THREADS;
+      const bool ok = t < nrun;                   // padding always stays at the tail of the run
+      const float4 p = P[t];
+      float lx = ok ? p.x : INFINITY, ly = ok ? p.y : INFINITY, lz = ok ? p.z : INFINITY;
+      float hx = ok ? p.x : -INFINITY, hy = ok ? p.y : -INFINITY, hz = ok ? p.z : -INFINITY;
+      warp_minmax3(lx, ly, lz, hx, hy, hz);       // a warp's 32 slots lie in one segment (size >= 64)
+      if (lane == 0 && lx <= hx) {
+        unsigned* b = segbox[t >> seg_shift];
+        atomicMin(&b[0], f2ord(lx)); atomicMin(&b[1], f2ord(ly)); atomicMin(&b[2], f2ord(lz));
+        atomicMax(&b[3], f2ord(hx)); atomicMax(&b[4], f2ord(hy)); atomicMax(&b[5], f2ord(hz));
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int t = tid + h * RF_THREADS;
+      const int seg = t >> seg_shift;
+      const unsigned* b = segbox[seg];
+      const float ex = ord2f(b[3]) - ord2f(b[0]), ey = ord2f(b[4]) - ord2f(b[1]), ez = ord2f(b[5]) - ord2f(b[2]);
+      const int axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
+      const float4 p = P[t];
+      const float c = axis == 0 ? p.x : (axis == 1 ? p.y : p.z);
+      const unsigned oc = (t < nrun) ? f2ord(c) : 0xffffffffu;
+      keys[t] = ((unsigned long long)seg << 42) | ((unsigned long long)oc << 10) | (unsigned long long)t;
+    }
+    __syncthreads();
+    const int seg_size = 1 << seg_shift;
+    for (int size = 2; size <= seg_size; size <<= 1) {
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        const int i = 2 * tid - (tid & (stride - 1));
+        const int j = i + stride;
+        const bool asc = (size == seg_size) || ((i & size) == 0);
+        const unsigned long long a = keys[i], b = keys[j];
+        if ((a > b) == asc) { keys[i] = b; keys[j] = a; }
+        __syncthreads();
+      }
+    }
+    float4 moved[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) moved[h] = P[(int)(keys[tid + h * RF_THREADS] & 1023ull)];
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) P[tid + h * RF_THREADS] = moved[h];
+    __syncthreads();
+  }
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int t = tid + h * RF_THREADS;
+    if (t < nrun) gp[t] = P[t];
+  }
+}
+
 __global__ void __launch_bounds__(256)
 k_scatter_results(const Float4* __restrict__ pts, const float* __restrict__ res, int64_t n,
                   uint32_t id_offset, float* __restrict__ out) {
@@ -188,6 +275,14 @@ int gather_points(const float* d_xyz, const uint32_t* order, const uint32_t* ids
                   int64_t n, Float4* sorted, cudaStream_t stream) {
   if (n <= 0) return 0;
   k_gather<<<grid_for(n, 256), 256, 0, stream>>>(d_xyz, order, ids, id_offset, n, sorted);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int refine_runs(Float4* sorted, int64_t n, cudaStream_t stream) {
+  if (n <= kGroup) return 0;
+  k_refine_runs<<<(int)div_up(n, RF_RUN), RF_THREADS, 0, stream>>>(sorted, n);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;

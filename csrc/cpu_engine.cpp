@@ -11,6 +11,7 @@
 //
 // Compiled with -ffp-contract=off so that fmaf() calls are the only fused operations.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <limits>
@@ -41,6 +42,8 @@ void parallel_for(int64_t n, int num_threads, F f) {
   }
   for (auto& t : ts) t.join();
 }
+
+std::atomic<unsigned long long> g_cpu_stats[4];   // leaves, candidates, inserts, inner nodes
 
 struct CpuTree {
   std::vector<Float4> pts;                 // sorted, padded to groups*32 with +inf points
@@ -93,6 +96,32 @@ void build_tree(const float* xyz, int64_t n, CpuTree& t) {
     memcpy(&p.w, &s, 4);
     t.pts[i] = p;
   }
+  // k-d refinement of every 1024-point Morton run (mirror of k_refine_runs in build.cu): exact
+  // median splits along the widest axis, 5 levels, padding stays at the tail.
+  if (n > kGroup) {
+    for (int64_t base = 0; base < n; base += 1024) {
+      const int nrun = (int)std::min<int64_t>(1024, n - base);
+      for (int seg_size = 1024; seg_size > kGroup; seg_size >>= 1) {
+        for (int s0 = 0; s0 < nrun; s0 += seg_size) {
+          const int s1 = std::min(nrun, s0 + seg_size);
+          float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+          for (int i = s0; i < s1; ++i) {
+            const Float4& p = t.pts[base + i];
+            lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
+            hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
+          }
+          const float ex = hi[0] - lo[0], ey = hi[1] - lo[1], ez = hi[2] - lo[2];
+          const int axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
+          std::stable_sort(t.pts.begin() + base + s0, t.pts.begin() + base + s1,
+                           [axis](const Float4& a, const Float4& b) {
+                             const float ca = axis == 0 ? a.x : (axis == 1 ? a.y : a.z);
+                             const float cb = axis == 0 ? b.x : (axis == 1 ? b.y : b.z);
+                             return ca < cb;
+                           });
+        }
+      }
+    }
+  }
   t.boxes[0].resize(groups);
   for (int64_t g = 0; g < groups; ++g) {
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -131,6 +160,7 @@ struct Group {
   float maxR2;
   std::vector<float> heap;   // [k][32]
   int k;
+  unsigned long long leaves = 0, inserts = 0, inner = 0;
   float top(int lane) const { return heap[lane]; }
   void refresh_max() {
     maxR2 = 0.f;
@@ -148,9 +178,10 @@ void leaf(const CpuTree& t, int64_t leaf_idx, Group& g) {
     for (int j = 0; j < kGroup; ++j) {
       const Float4& p = t.pts[leaf_idx * kGroup + j];
       const float d2 = dist2(g.q[l][0], g.q[l][1], g.q[l][2], p.x, p.y, p.z);
-      if (d2 < g.top(l)) heap_replace_top(g.heap.data() + l, kGroup, g.k, d2);
+      if (d2 < g.top(l)) { heap_replace_top(g.heap.data() + l, kGroup, g.k, d2); ++g.inserts; }
     }
   }
+  ++g.leaves;
   g.refresh_max();
 }
 
@@ -176,8 +207,41 @@ void visit(const CpuTree& t, int level, int64_t base, int count, Group& g) {
     if (level == 0) {
       leaf(t, child, g);
     } else {
+      ++g.inner;
       const int64_t rem = (int64_t)t.boxes[level - 1].size() - child * kFanout;
       visit(t, level - 1, child * kFanout, (int)std::min<int64_t>(rem, kFanout), g);
+    }
+  }
+}
+
+// Best-first traversal: one frontier of (lower bound, node) over all levels, always expanding the
+// globally nearest entry; stops when the nearest entry is no closer than the group radius.
+// Mirror of the warp-level frontier queue in query.cu.
+void best_first(const CpuTree& t, Group& g) {
+  struct Entry { float key; int level; int64_t idx; };
+  auto worse = [](const Entry& a, const Entry& b) { return a.key > b.key; };
+  std::vector<Entry> q;
+  auto push_children = [&](int level, int64_t base, int count) {
+    for (int c = 0; c < count; ++c) {
+      const Box& b = t.boxes[level][base + c];
+      const float key = box_box_lb(g.glo[0], g.glo[1], g.glo[2], g.ghi[0], g.ghi[1], g.ghi[2],
+                                   b.lox, b.loy, b.loz, b.hix, b.hiy, b.hiz);
+      if (key < g.maxR2) { q.push_back({key, level, base + c}); std::push_heap(q.begin(), q.end(), worse); }
+    }
+  };
+  const int top = t.levels - 1;
+  push_children(top, 0, (int)t.boxes[top].size());
+  while (!q.empty()) {
+    std::pop_heap(q.begin(), q.end(), worse);
+    const Entry e = q.back();
+    q.pop_back();
+    if (!(e.key < g.maxR2)) break;
+    if (e.level == 0) {
+      leaf(t, e.idx, g);
+    } else {
+      ++g.inner;
+      const int64_t rem = (int64_t)t.boxes[e.level - 1].size() - e.idx * kFanout;
+      push_children(e.level - 1, e.idx * kFanout, (int)std::min<int64_t>(rem, kFanout));
     }
   }
 }
@@ -207,6 +271,11 @@ extern "C" int b200knn_cpu_bruteforce(const float* xyz, int64_t n, const float* 
       out[qi] = finalize_kth(fminf(kth, sent));
     }
   });
+  return 0;
+}
+
+extern "C" int b200knn_cpu_stats(uint64_t out4[4], int reset) {
+  for (int i = 0; i < 4; ++i) { out4[i] = g_cpu_stats[i].load(); if (reset) g_cpu_stats[i] = 0; }
   return 0;
 }
 
@@ -256,8 +325,10 @@ extern "C" int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries
       }
       g.refresh_max();
       if (tree.levels > 0) {
+        static const bool dfs = getenv("B200KNN_CPU_DFS") != nullptr;
         const int top = tree.levels - 1;
-        visit(tree, top, 0, (int)tree.boxes[top].size(), g);
+        if (dfs) visit(tree, top, 0, (int)tree.boxes[top].size(), g);
+        else best_first(tree, g);
       }
       for (int l = 0; l < g.cnt; ++l) {
         uint32_t id;
@@ -265,6 +336,8 @@ extern "C" int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries
         out[id] = finalize_kth(g.top(l));
       }
     }
+    g_cpu_stats[0] += g.leaves; g_cpu_stats[1] += g.leaves * kGroup;
+    g_cpu_stats[2] += g.inserts; g_cpu_stats[3] += g.inner;
   });
   return 0;
 }

@@ -41,6 +41,8 @@ int morton_keys(const float* d_xyz, int64_t n, const float* d_bounds6, uint64_t*
 // sorted[i] = (xyz[order[i]], id = ids ? ids[order[i]] : order[i] + id_offset)
 int gather_points(const float* d_xyz, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
                   int64_t n, Float4* sorted, cudaStream_t stream);
+// Re-order every 1024-point Morton run into a balanced k-d tree with compact 32-point leaves.
+int refine_runs(Float4* sorted, int64_t n, cudaStream_t stream);
 int build_leaf_boxes(const Float4* sorted, int64_t n, Box* level0, cudaStream_t stream);
 int build_upper_boxes(const Box* child, int child_count, Box* parent, cudaStream_t stream);
 

@@ -62,8 +62,8 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
                       float* d_out, void* stream);
 /* Traversal counters of the most recent query call on this index (synchronous):
  * [0] leaves visited by groups, [1] candidate distance evaluations per lane, [2] heap insertions,
- * [3] inner nodes opened. Role of CUKD_ENABLE_STATS (cukd/common.h:349-361). */
-int b200knn_index_stats(b200knn_index* idx, uint64_t out4[4]);
+ * [3] inner nodes opened, [4] frontier overflows handled depth-first, [5] frontier purges. Role of CUKD_ENABLE_STATS (cukd/common.h:349-361). */
+int b200knn_index_stats(b200knn_index* idx, uint64_t out8[8]);
 int b200knn_index_enable_stats(b200knn_index* idx, int on);
 
 /* ---- multi-GPU fused ring ----------------------------------------------------------------------
@@ -117,6 +117,9 @@ int b200knn_cpu_bruteforce(const float* xyz, int64_t n, const float* queries, in
                            float max_radius, float* out, int num_threads);
 int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries_or_null, int64_t nq, int k,
                     float max_radius, float* out, int num_threads);
+
+/* Traversal counters accumulated by cpu_knn calls (same meaning as b200knn_index_stats). */
+int b200knn_cpu_stats(uint64_t out4[4], int reset);
 
 #ifdef __cplusplus
 }

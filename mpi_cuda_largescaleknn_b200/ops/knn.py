@@ -93,10 +93,11 @@ class KnnIndex:
         check(lib().b200knn_index_enable_stats(self._h, int(on)))
 
     def stats(self) -> dict:
-        out = np.zeros(4, np.uint64)
+        out = np.zeros(8, np.uint64)
         check(lib().b200knn_index_stats(self._h, out.ctypes.data))
         return {"leaves_visited": int(out[0]), "candidates": int(out[1]),
-                "heap_inserts": int(out[2]), "inner_nodes": int(out[3])}
+                "heap_inserts": int(out[2]), "inner_nodes": int(out[3]),
+                "dfs_fallbacks": int(out[4]), "purges": int(out[5])}
 
     def knn_self(self, k: int, max_radius: float = math.inf, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """k-th-neighbour distance of every indexed point, in the caller's original order."""

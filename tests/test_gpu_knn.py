@@ -59,11 +59,21 @@ def test_index_build_sort_and_boxes(n):
     ids = s[:, 3].copy().view(np.uint32)
     assert np.array_equal(np.sort(ids), np.arange(n, dtype=np.uint32))
     assert np.array_equal(s[:, :3], x[ids])
+    # Order: Morton across 1024-point runs (radix sort), k-d median order inside a run (refine).
     keys = morton63_np(s[:, :3], b[:3], b[3:])
-    assert np.all(keys[1:] >= keys[:-1])
-    # stability: equal keys keep input order
-    same = keys[1:] == keys[:-1]
-    assert np.all(ids[1:][same] > ids[:-1][same])
+    nruns = (n + 1023) // 1024
+    run_min = np.array([keys[r * 1024:(r + 1) * 1024].min() for r in range(nruns)])
+    run_max = np.array([keys[r * 1024:(r + 1) * 1024].max() for r in range(nruns)])
+    assert np.all(run_min[1:] >= run_max[:-1])
+    # every run holds exactly the points a stable Morton sort of the input puts there
+    ref_order = np.argsort(morton63_np(x, b[:3], b[3:]), kind="stable").astype(np.uint32)
+    for r in range(0, nruns, max(1, nruns // 64)):
+        assert np.array_equal(np.sort(ids[r * 1024:(r + 1) * 1024]), np.sort(ref_order[r * 1024:(r + 1) * 1024]))
+    # inside a full run: first median split is exact (left half <= right half on the widest axis)
+    if n >= 1024:
+        run = s[:1024, :3]
+        axis = int(np.argmax(run.max(0) - run.min(0)))
+        assert run[:512, axis].max() <= run[512:, axis].min()
     # leaf boxes
     boxes = idx.boxes(0)
     nl = (n + 31) // 32
