@@ -229,6 +229,7 @@ int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, 
   p.groups_per_chunk = (int)idx->groups();
   p.home_queries = idx->pts;
   p.home_n = idx->n;
+  p.home_is_tree = 1;
   p.result_sorted = idx->result_sorted;
   if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
   int rc;
@@ -318,6 +319,7 @@ int b200knn_run_steps(b200knn_index* idx, const b200knn_step_args* a, void* stre
   p.step_end = a->step_end;
   p.home_queries = idx->pts;
   p.home_n = idx->n;
+  p.home_is_tree = 1;
   for (int b = 0; b < 2; ++b) {
     p.inbox_heap[b] = a->inbox_heap[b];
     p.inbox_pos[b] = reinterpret_cast<const Float4*>(a->inbox_pos[b]);
@@ -433,6 +435,7 @@ int b200knn_ring_run(b200knn_ring* r, float max_radius, void* stream_) {
   p.seq_base = r->seq_base;
   p.home_queries = idx->pts;
   p.home_n = idx->n;
+  p.home_is_tree = 1;
   char* nb = r->world > 1 ? r->next_base : r->base;
   char* pb = r->world > 1 ? r->prev_base : r->base;
   const RingLayout& NL = r->world > 1 ? r->next_layout : r->mine;

@@ -217,12 +217,35 @@ void visit(const CpuTree& t, int level, int64_t base, int count, Group& g) {
 // Best-first traversal: one frontier of (lower bound, node) over all levels, always expanding the
 // globally nearest entry; stops when the nearest entry is no closer than the group radius.
 // Mirror of the warp-level frontier queue in query.cu.
-void best_first(const CpuTree& t, Group& g) {
+void best_first(const CpuTree& t, Group& g, int64_t seed_l1) {
   struct Entry { float key; int level; int64_t idx; };
   auto worse = [](const Entry& a, const Entry& b) { return a.key > b.key; };
   std::vector<Entry> q;
+  if (t.levels >= 2) {
+    if (seed_l1 < 0) {   // greedy descent to the nearest level-1 node (group visiting a foreign tree)
+      int64_t base = 0;
+      int64_t count = (int64_t)t.boxes[t.levels - 1].size();
+      for (int L = t.levels - 1;; --L) {
+        int64_t bestc = base; float bk = INFINITY;
+        for (int64_t c = base; c < base + count; ++c) {
+          const Box& b = t.boxes[L][c];
+          const float key = box_box_lb(g.glo[0], g.glo[1], g.glo[2], g.ghi[0], g.ghi[1], g.ghi[2],
+                                       b.lox, b.loy, b.loz, b.hix, b.hiy, b.hiz);
+          if (key < bk) { bk = key; bestc = c; }
+        }
+        if (L == 1) { seed_l1 = bestc; break; }
+        base = bestc * kFanout;
+        count = std::min<int64_t>(kFanout, (int64_t)t.boxes[L - 1].size() - base);
+      }
+    }
+    const int64_t rem = (int64_t)t.boxes[0].size() - seed_l1 * kFanout;
+    visit(t, 0, seed_l1 * kFanout, (int)std::min<int64_t>(rem, kFanout), g);   // seed phase
+  } else {
+    seed_l1 = -1;
+  }
   auto push_children = [&](int level, int64_t base, int count) {
     for (int c = 0; c < count; ++c) {
+      if (level == 1 && base + c == seed_l1) continue;
       const Box& b = t.boxes[level][base + c];
       const float key = box_box_lb(g.glo[0], g.glo[1], g.glo[2], g.ghi[0], g.ghi[1], g.ghi[2],
                                    b.lox, b.loy, b.loz, b.hix, b.hiy, b.hiz);
@@ -328,7 +351,7 @@ extern "C" int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries
         static const bool dfs = getenv("B200KNN_CPU_DFS") != nullptr;
         const int top = tree.levels - 1;
         if (dfs) visit(tree, top, 0, (int)tree.boxes[top].size(), g);
-        else best_first(tree, g);
+        else best_first(tree, g, queries == nullptr ? gi / kFanout : -1);
       }
       for (int l = 0; l < g.cnt; ++l) {
         uint32_t id;

@@ -67,6 +67,7 @@ struct RingParams {
   // queries of hop 0: the local tree's own points, or an external sorted query set
   const Float4* home_queries;  // tree.pts for self-kNN
   int64_t home_n;
+  int home_is_tree;            // 1 if home_queries are exactly the tree's own sorted points
   // local inbox (written by the previous rank)
   const float* inbox_heap[2];  // [Gc][k][32]
   const Float4* inbox_pos[2];  // [Gc][32]

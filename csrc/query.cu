@@ -118,62 +118,51 @@ __device__ __forceinline__ void maybe_leaf(const TreeView& t, int leaf, float lx
   if (__any_sync(kFullMask, g.valid && (lb < g.top))) process_leaf(t, leaf, cnt, g);
 }
 
-// Depth-first visit of children [base, base+count) of `level`, nearest first, with an explicit frame
-// stack in shared memory (boxes are re-loaded after returning from a child). Only used when the
-// frontier overflows; any visiting order is exact.
-__device__ __forceinline__ void dfs_fallback(const TreeView& t, int level, int base, int count, GroupCtx& g) {
+// ---- traversal ------------------------------------------------------------------------------------
+// One loop, two sources of "next node", one leaf call site:
+//   * FRAMES (depth >= 0): depth-first, nearest child first, explicit frame stack in shared memory
+//     (level, base, count, todo mask); boxes are re-loaded when control returns to a frame. Used (a) for
+//     the SEED phase — the 32 leaves of the level-1 node the group lives in (or the nearest one, for a
+//     group visiting a foreign tree) are swept first so that the radius is tight before anything is
+//     put on the frontier — and (b) when the frontier overflows (any visiting order is exact).
+//   * FRONTIER: best-first over (lower bound, node) entries of all levels, seed node excluded.
+__device__ __forceinline__ unsigned full_mask_of(int count) {
+  return count >= 32 ? 0xffffffffu : ((1u << count) - 1u);
+}
+
+__device__ __forceinline__ void push_frame(unsigned* fr, int depth, int level, int base, int count) {
+  fr[depth * 4 + 0] = (unsigned)level;
+  fr[depth * 4 + 1] = (unsigned)base;
+  fr[depth * 4 + 2] = (unsigned)count;
+  fr[depth * 4 + 3] = full_mask_of(count);
+}
+
+// Greedy descent to the level-1 node nearest to the group box (-1 if the tree has no level 1).
+__device__ __forceinline__ int find_seed_l1(const TreeView& t, const GroupCtx& g) {
+  if (t.levels < 2) return -1;
   const int lane = lane_id();
-  unsigned* fr = g.frames;    // [kMaxLevels][4]: level, base, count, todo mask
-  int depth = 0;
-  __syncwarp();
-  if (lane == 0) {
-    fr[0] = (unsigned)level; fr[1] = (unsigned)base; fr[2] = (unsigned)count;
-    fr[3] = count >= 32 ? 0xffffffffu : ((1u << count) - 1u);
-  }
-  __syncwarp();
-  while (depth >= 0) {
-    const int L = (int)fr[depth * 4 + 0], B = (int)fr[depth * 4 + 1], Cn = (int)fr[depth * 4 + 2];
-    const unsigned todo_in = fr[depth * 4 + 3];
-    const bool have = lane < Cn;
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-    if (have) {
-      const float4* bp = reinterpret_cast<const float4*>(t.boxes[L]) + 2 * (size_t)(B + lane);
-      a = __ldg(bp);
-      b = __ldg(bp + 1);
+  int base = 0, count = t.count[t.levels - 1];
+  for (int L = t.levels - 1;; --L) {
+    float key = INFINITY;
+    if (lane < count) {
+      const float4* bp = reinterpret_cast<const float4*>(t.boxes[L]) + 2 * (size_t)(base + lane);
+      const float4 a = __ldg(bp), b = __ldg(bp + 1);
+      key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
     }
-    const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
-    const bool pass = have && ((todo_in >> lane) & 1u) && (key < g.maxR2);
-    const unsigned pm = __ballot_sync(kFullMask, pass);
-    if (pm == 0u) { --depth; continue; }
-    const unsigned kb = pass ? __float_as_uint(key) : 0xffffffffu;
+    const unsigned kb = __float_as_uint(key);
     const unsigned m = __reduce_min_sync(kFullMask, kb);
-    const int who = __ffs(__ballot_sync(kFullMask, kb == m)) - 1;
-    const int child = B + who;
-    __syncwarp();
-    if (lane == 0) fr[depth * 4 + 3] = pm & ~(1u << who);
-    if (L == 0) {
-      const float lx = __shfl_sync(kFullMask, a.x, who), ly = __shfl_sync(kFullMask, a.y, who);
-      const float lz = __shfl_sync(kFullMask, a.z, who), hx = __shfl_sync(kFullMask, b.x, who);
-      const float hy = __shfl_sync(kFullMask, b.y, who), hz = __shfl_sync(kFullMask, b.z, who);
-      const int cnt = __float_as_int(__shfl_sync(kFullMask, a.w, who));
-      maybe_leaf(t, child, lx, ly, lz, hx, hy, hz, cnt, g);
-    } else {
-      ++g.n_inner;
-      ++depth;
-      const int rem = t.count[L - 1] - child * kFanout;
-      const int cc = rem < kFanout ? rem : kFanout;
-      if (lane == 0) {
-        fr[depth * 4 + 0] = (unsigned)(L - 1); fr[depth * 4 + 1] = (unsigned)(child * kFanout);
-        fr[depth * 4 + 2] = (unsigned)cc; fr[depth * 4 + 3] = cc >= 32 ? 0xffffffffu : ((1u << cc) - 1u);
-      }
-    }
-    __syncwarp();
+    const int child = base + __ffs(__ballot_sync(kFullMask, kb == m)) - 1;
+    if (L == 1) return child;
+    base = child * kFanout;
+    const int rem = t.count[L - 1] - base;
+    count = rem < kFanout ? rem : kFanout;
   }
 }
 
-// Push the children [base, base+count) of `level` that lie inside the group radius.
-__device__ __forceinline__ void frontier_expand(const TreeView& t, int level, int base, int count,
-                                                int& qcount, GroupCtx& g) {
+// Push the children [base, base+count) of `level` that lie inside the group radius. On overflow
+// (after purging stale entries) the children are handed to the frame stack instead.
+__device__ __forceinline__ void frontier_expand(const TreeView& t, int level, int base, int count, int seed_l1,
+                                                int& qcount, int& depth, GroupCtx& g) {
   const int lane = lane_id();
   const bool have = lane < count;
   float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
@@ -183,7 +172,7 @@ __device__ __forceinline__ void frontier_expand(const TreeView& t, int level, in
     b = __ldg(bp + 1);
   }
   const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
-  const bool pass = have && (key < g.maxR2);
+  const bool pass = have && (key < g.maxR2) && !(level == 1 && base + lane == seed_l1);
   const unsigned mask = __ballot_sync(kFullMask, pass);
   const int np = __popc(mask);
   if (np == 0) return;
@@ -213,7 +202,9 @@ __device__ __forceinline__ void frontier_expand(const TreeView& t, int level, in
   }
   if (qcount + np > kQueueCap) {
     ++g.n_fallback;
-    dfs_fallback(t, level, base, count, g);
+    depth = 0;
+    if (lane == 0) push_frame(g.frames, 0, level, base, count);
+    __syncwarp();
     return;
   }
   if (pass) {
@@ -225,41 +216,98 @@ __device__ __forceinline__ void frontier_expand(const TreeView& t, int level, in
   __syncwarp();
 }
 
-__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g) {
+__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1) {
   const int lane = lane_id();
+  unsigned* fr = g.frames;
   const int top_level = t.levels - 1;
-  int qcount = 0;
-  frontier_expand(t, top_level, 0, t.count[top_level], qcount, g);
-  while (qcount > 0) {
-    unsigned best = 0xffffffffu;
-    int bslot = 0;
-    for (int s = lane; s < qcount; s += 32) {
-      const unsigned kx = g.qkey[s];
-      if (kx < best) { best = kx; bslot = s; }
-    }
-    const unsigned m = __reduce_min_sync(kFullMask, best);
-    if (m >= __float_as_uint(g.maxR2)) break;          // nothing left inside the group radius
-    const int wl = __ffs(__ballot_sync(kFullMask, best == m)) - 1;
-    const int slot = __shfl_sync(kFullMask, bslot, wl);
-    const unsigned node = g.qnode[slot];
+  int depth = -1, qcount = 0;
+  bool started = false;
+  if (seed_l1 >= 0) {
+    const int rem = t.count[0] - seed_l1 * kFanout;
+    if (lane == 0) push_frame(fr, 0, 0, seed_l1 * kFanout, rem < kFanout ? rem : kFanout);
+    depth = 0;
     __syncwarp();
-    if (lane == 0) {
-      g.qkey[slot] = g.qkey[qcount - 1];
-      g.qnode[slot] = g.qnode[qcount - 1];
-    }
-    --qcount;
-    __syncwarp();
-    const int level = (int)(node >> kNodeIdxBits);
-    const int idx = (int)(node & ((1u << kNodeIdxBits) - 1u));
-    if (level == 0) {
+  }
+  for (;;) {
+    int leaf, cnt;
+    float lx, ly, lz, hx, hy, hz;
+    if (depth >= 0) {
+      // ---- frame step
+      const int L = (int)fr[depth * 4 + 0], B = (int)fr[depth * 4 + 1], Cn = (int)fr[depth * 4 + 2];
+      const unsigned todo_in = fr[depth * 4 + 3];
+      const bool have = lane < Cn;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+      if (have) {
+        const float4* bp = reinterpret_cast<const float4*>(t.boxes[L]) + 2 * (size_t)(B + lane);
+        a = __ldg(bp);
+        b = __ldg(bp + 1);
+      }
+      const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
+      const bool pass = have && ((todo_in >> lane) & 1u) && (key < g.maxR2) &&
+                        !(L == 1 && B + lane == seed_l1);
+      const unsigned pm = __ballot_sync(kFullMask, pass);
+      if (pm == 0u) { --depth; continue; }
+      const unsigned kb = pass ? __float_as_uint(key) : 0xffffffffu;
+      const unsigned m = __reduce_min_sync(kFullMask, kb);
+      const int who = __ffs(__ballot_sync(kFullMask, kb == m)) - 1;
+      const int child = B + who;
+      __syncwarp();
+      if (lane == 0) fr[depth * 4 + 3] = pm & ~(1u << who);
+      if (L != 0) {
+        ++g.n_inner;
+        ++depth;
+        const int rem = t.count[L - 1] - child * kFanout;
+        if (lane == 0) push_frame(fr, depth, L - 1, child * kFanout, rem < kFanout ? rem : kFanout);
+        __syncwarp();
+        continue;
+      }
+      __syncwarp();
+      leaf = child;
+      lx = __shfl_sync(kFullMask, a.x, who); ly = __shfl_sync(kFullMask, a.y, who);
+      lz = __shfl_sync(kFullMask, a.z, who); hx = __shfl_sync(kFullMask, b.x, who);
+      hy = __shfl_sync(kFullMask, b.y, who); hz = __shfl_sync(kFullMask, b.z, who);
+      cnt = __float_as_int(__shfl_sync(kFullMask, a.w, who));
+    } else {
+      // ---- frontier step
+      if (!started) {
+        started = true;
+        frontier_expand(t, top_level, 0, t.count[top_level], seed_l1, qcount, depth, g);
+        continue;
+      }
+      if (qcount == 0) break;
+      unsigned best = 0xffffffffu;
+      int bslot = 0;
+      for (int s = lane; s < qcount; s += 32) {
+        const unsigned kx = g.qkey[s];
+        if (kx < best) { best = kx; bslot = s; }
+      }
+      const unsigned m = __reduce_min_sync(kFullMask, best);
+      if (m >= __float_as_uint(g.maxR2)) break;          // nothing left inside the group radius
+      const int wl = __ffs(__ballot_sync(kFullMask, best == m)) - 1;
+      const int slot = __shfl_sync(kFullMask, bslot, wl);
+      const unsigned node = g.qnode[slot];
+      __syncwarp();
+      if (lane == 0) {
+        g.qkey[slot] = g.qkey[qcount - 1];
+        g.qnode[slot] = g.qnode[qcount - 1];
+      }
+      --qcount;
+      __syncwarp();
+      const int level = (int)(node >> kNodeIdxBits);
+      const int idx = (int)(node & ((1u << kNodeIdxBits) - 1u));
+      if (level != 0) {
+        ++g.n_inner;
+        const int rem = t.count[level - 1] - idx * kFanout;
+        frontier_expand(t, level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, seed_l1, qcount, depth, g);
+        continue;
+      }
       const float4* bp = reinterpret_cast<const float4*>(t.boxes[0]) + 2 * (size_t)idx;
       const float4 a = __ldg(bp), b = __ldg(bp + 1);
-      maybe_leaf(t, idx, a.x, a.y, a.z, b.x, b.y, b.z, __float_as_int(a.w), g);
-    } else {
-      ++g.n_inner;
-      const int rem = t.count[level - 1] - idx * kFanout;
-      frontier_expand(t, level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, qcount, g);
+      leaf = idx;
+      lx = a.x; ly = a.y; lz = a.z; hx = b.x; hy = b.y; hz = b.z;
+      cnt = __float_as_int(a.w);
     }
+    maybe_leaf(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
   }
 }
 
@@ -348,7 +396,10 @@ knn_ring_kernel(const RingParams p) {
       }
       g.glx = lx; g.gly = ly; g.glz = lz; g.ghx = hx; g.ghy = hy; g.ghz = hz;
       g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
-      traverse(p.tree, g);
+      // seed = the level-1 node holding the group's own leaf (self queries at home), else the nearest
+      const int seed = (hop == 0 && p.home_is_tree) ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1)
+                                                    : find_seed_l1(p.tree, g);
+      traverse(p.tree, g, seed);
     }
 
     // ------------------------------------------------------------------ output

@@ -33,6 +33,7 @@ for rep in range(a.reps):
         st = idx.stats()
         g = (a.n + 31) // 32
         rec.update({"leaves_per_group": st["leaves_visited"] / g, "inner_per_group": st["inner_nodes"] / g,
-                    "inserts_per_query": st["heap_inserts"] / a.n})
+                    "inserts_per_query": st["heap_inserts"] / a.n,
+                    "fallbacks_per_group": st["dfs_fallbacks"] / g, "purges_per_group": st["purges"] / g})
     print(json.dumps(rec), flush=True)
     idx.close()
