@@ -93,7 +93,7 @@ def main() -> int:
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=int(os.environ.get("B200KNN_BENCH_N", BASELINE_N)),
+    ap.add_argument("--num-points", dest="n", type=int, default=int(os.environ.get("B200KNN_BENCH_N", BASELINE_N)),
                     help="TOTAL number of points over all GPUs")
     ap.add_argument("--k", type=int, default=BASELINE_K)
     ap.add_argument("--transport", default="fused", choices=["fused", "nccl"],

@@ -10,6 +10,7 @@
 #include "../include/b200knn.h"
 #include "common.cuh"
 #include "kernels.h"
+#include "index_internal.h"
 
 namespace b200knn {
 static thread_local std::string g_last_error;
@@ -18,36 +19,6 @@ const char* last_error_cstr() { return g_last_error.c_str(); }
 static std::atomic<unsigned long long> g_launches{0};
 void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 }  // namespace b200knn
-
-using namespace b200knn;
-
-struct b200knn_index {
-  int device = 0;
-  int num_sms = 148;
-  int64_t n = 0;
-  uint32_t id_offset = 0;
-  Float4* pts = nullptr;
-  Box* boxes[kMaxLevels] = {};
-  int count[kMaxLevels] = {};
-  int levels = 0;
-  unsigned* d_bounds_ord = nullptr;
-  float* d_bounds6 = nullptr;
-  float h_bounds[6] = {};
-  float* result_sorted = nullptr;          // [groups*32]
-  unsigned long long* task_counter = nullptr;
-  unsigned long long* stats = nullptr;     // [4]
-  bool stats_on = false;
-
-  TreeView view() const {
-    TreeView t;
-    t.pts = pts;
-    for (int l = 0; l < kMaxLevels; ++l) { t.boxes[l] = boxes[l]; t.count[l] = count[l]; }
-    t.levels = levels;
-    t.n = (int)n;
-    return t;
-  }
-  int64_t groups() const { return div_up(n, kGroup); }
-};
 
 namespace {
 
@@ -97,9 +68,21 @@ const char* b200knn_last_error(void) { return last_error_cstr(); }
 int b200knn_version(void) { return 100; }
 uint64_t b200knn_launch_count(void) { return g_launches.load(); }
 
+static int index_create_impl(const float* d_xyz, int stride, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
+                             cudaStream_t stream, b200knn_index** out);
+
 int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
                          void* stream_, b200knn_index** out) {
-  cudaStream_t stream = (cudaStream_t)stream_;
+  return index_create_impl(d_xyz, 3, n, d_ids, id_offset, (cudaStream_t)stream_, out);
+}
+
+int b200knn_index_create_xyzw(const float* d_xyzw, int64_t n, uint32_t id_offset, void* stream_,
+                              b200knn_index** out) {
+  return index_create_impl(d_xyzw, 4, n, nullptr, id_offset, (cudaStream_t)stream_, out);
+}
+
+static int index_create_impl(const float* d_xyz, int stride, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
+                             cudaStream_t stream, b200knn_index** out) {
   KNN_REQUIRE(out != nullptr, "index_create: out is NULL");
   KNN_REQUIRE(n >= 0 && n < (int64_t)0x7fffffff - 64, "index_create: n must be in [0, 2^31-64) per GPU");
   b200knn_index* idx = new b200knn_index();
@@ -115,7 +98,7 @@ int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, u
   KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
   int rc;
   if ((rc = bounds_init(idx->d_bounds_ord, stream))) return rc;
-  if ((rc = bounds_accumulate(d_xyz, n, idx->d_bounds_ord, stream))) return rc;
+  if ((rc = bounds_accumulate(d_xyz, stride, n, idx->d_bounds_ord, stream))) return rc;
   if ((rc = bounds_decode(idx->d_bounds_ord, idx->d_bounds6, stream))) return rc;
   KNN_CUDA_TRY(cudaMemcpyAsync(idx->h_bounds, idx->d_bounds6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
   if (n == 0) {
@@ -147,11 +130,11 @@ int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, u
   KNN_CUDA_TRY(cudaMallocAsync(&vals, n * sizeof(uint32_t), stream));
   KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, n * sizeof(uint32_t), stream));
   KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(n), stream));
-  if ((rc = morton_keys(d_xyz, n, idx->d_bounds6, keys, vals, stream))) return rc;
+  if ((rc = morton_keys(d_xyz, stride, n, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n, 0, 64, stream, &in_tmp))) return rc;
   const uint32_t* order = in_tmp ? vals_tmp : vals;
-  if ((rc = gather_points(d_xyz, order, d_ids, id_offset, n, idx->pts, stream))) return rc;
+  if ((rc = gather_points(d_xyz, stride, order, d_ids, id_offset, n, idx->pts, stream))) return rc;
   if ((rc = refine_runs(idx->pts, n, stream))) return rc;
   if ((rc = build_leaf_boxes(idx->pts, n, idx->boxes[0], stream))) return rc;
   for (int l = 1; l < levels; ++l)
@@ -258,10 +241,10 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   KNN_CUDA_TRY(cudaMallocAsync(&rsorted, groups * kGroup * sizeof(float), stream));
   int rc;
   // Order queries along the index's own Morton grid (queries outside its box clamp to the faces).
-  if ((rc = morton_keys(d_queries, nq, idx->d_bounds6, keys, vals, stream))) return rc;
+  if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
-  if ((rc = gather_points(d_queries, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
+  if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
   if ((rc = refine_runs(qsorted, nq, stream))) return rc;   // compact query groups, same as leaves
   RingParams p;
   fill_local_only(p, idx, k, max_radius);

@@ -1,0 +1,481 @@
+// dist.cu — the distributed driver (host side): one process per GPU, peer memory mapped with CUDA
+// IPC into a symmetric heap, three strategies over the same kernels.
+//
+// Role of main() in the reference's two programs (/root/reference/unorderedDataVariant.cu:137-211,
+// /root/reference/prePartitionedDataVariant.cu:211-364) with MPI replaced by
+//   * a caller-supplied bootstrap (allgather + barrier of small host buffers: torch.distributed in
+//     Python, a unix-socket rendezvous in the C++ launcher) for set-up and round fences, and
+//   * in-kernel loads/stores on NVLink-mapped peer memory for every byte of bulk data.
+//
+// Modes
+//   RING            all-pairs ring, query groups + heaps circulate (query.cu); valid for any input
+//   PREPARTITIONED  every rank keeps the points it was given; per-group bounding-box culling decides
+//                   which groups visit which ranks (pv.cu)
+//   REDISTRIBUTE    unordered input is first scattered to spatial owners (global Morton order, sample
+//                   splitters, all-to-all by peer stores), then PREPARTITIONED runs on compact,
+//                   nearly disjoint regions, then results are scattered back to the reading rank.
+//                   This is what makes N fixed / more GPUs faster (the ring does R times the work).
+#include <string.h>
+#include <algorithm>
+#include <chrono>
+#include <vector>
+#include "common.cuh"
+#include "index_internal.h"
+
+namespace {
+
+struct HeapBlob {
+  cudaIpcMemHandle_t handle;
+  int64_t bytes;
+  int32_t rank, world;
+};
+
+inline size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+
+double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+}  // namespace
+
+struct b200knn_dist {
+  b200knn_bootstrap bs{};
+  int rank = 0, world = 1, device = 0, num_sms = 148;
+  char* base = nullptr;
+  size_t bytes = 0;
+  char* peer[B200KNN_MAX_RANKS] = {};
+  size_t bump = 0;
+  unsigned long long* task_counter = nullptr;
+
+  int allgather(const void* send, void* recv, int64_t nbytes) {
+    if (world == 1) { memcpy(recv, send, (size_t)nbytes); return 0; }
+    return bs.allgather(bs.ctx, send, recv, nbytes);
+  }
+  int barrier() { return world == 1 ? 0 : bs.barrier(bs.ctx); }
+  size_t alloc(size_t n) { const size_t o = bump; bump = align256(bump + n); return o; }
+};
+
+namespace {
+
+int close_heap(b200knn_dist* d) {
+  for (int r = 0; r < d->world; ++r) {
+    if (r != d->rank && d->peer[r]) cudaIpcCloseMemHandle(d->peer[r]);
+    d->peer[r] = nullptr;
+  }
+  if (d->base) cudaFree(d->base);
+  d->base = nullptr;
+  d->bytes = 0;
+  return 0;
+}
+
+// Collective: every rank must call with the same `need`.
+int ensure_heap(b200knn_dist* d, size_t need) {
+  need = align256(need);
+  if (need <= d->bytes) return 0;
+  KNN_CUDA_TRY(cudaDeviceSynchronize());
+  if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
+  close_heap(d);
+  const size_t grow = need + need / 8;
+  KNN_CUDA_TRY(cudaMalloc(&d->base, grow));
+  KNN_CUDA_TRY(cudaMemset(d->base, 0, grow));
+  d->bytes = grow;
+  d->peer[d->rank] = d->base;
+  if (d->world > 1) {
+    HeapBlob mine;
+    memset(&mine, 0, sizeof(mine));
+    KNN_CUDA_TRY(cudaIpcGetMemHandle(&mine.handle, d->base));
+    mine.bytes = (int64_t)grow;
+    mine.rank = d->rank;
+    mine.world = d->world;
+    std::vector<HeapBlob> all(d->world);
+    if (d->allgather(&mine, all.data(), sizeof(HeapBlob))) { set_last_error("bootstrap allgather failed"); return -3; }
+    for (int r = 0; r < d->world; ++r) {
+      if (r == d->rank) continue;
+      KNN_REQUIRE(all[r].rank == r && all[r].bytes == (int64_t)grow, "ranks disagree on the symmetric heap size");
+      void* p = nullptr;
+      KNN_CUDA_TRY(cudaIpcOpenMemHandle(&p, all[r].handle, cudaIpcMemLazyEnablePeerAccess));
+      d->peer[r] = static_cast<char*>(p);
+    }
+    if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
+  }
+  return 0;
+}
+
+size_t pv_heap_need(int k, int Gc) {
+  return 2 * align256((size_t)Gc * pv_slot_bytes(k)) + 4 * 256;
+}
+
+struct PvPlan { int Gc; int C; int64_t max_groups; };
+
+PvPlan pv_plan(int64_t max_n, int groups_per_chunk) {
+  PvPlan pl;
+  pl.max_groups = div_up(max_n > 0 ? max_n : 1, kGroup);
+  int64_t Gc = groups_per_chunk > 0 ? groups_per_chunk : 131072;
+  if (Gc > pl.max_groups) Gc = pl.max_groups;
+  pl.Gc = (int)Gc;
+  pl.C = (int)div_up(pl.max_groups, Gc);
+  return pl;
+}
+
+// The culled exchange over an existing local index. Heap must already be large enough; sub-allocations
+// are taken from d->bump (symmetric: same sequence on every rank). Results land in idx->result_sorted.
+int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const PvPlan& pl, cudaStream_t stream,
+           b200knn_dist_report* rep) {
+  const int R = d->world, me = d->rank;
+  // everyone's box
+  std::vector<float> boxes((size_t)R * 6);
+  if (d->allgather(idx->h_bounds, boxes.data(), 6 * sizeof(float))) { set_last_error("bootstrap allgather failed"); return -3; }
+
+  const size_t slot = pv_slot_bytes(k);
+  const size_t off_pending = d->alloc((size_t)pl.Gc * slot);
+  const size_t off_inbox = d->alloc((size_t)pl.Gc * slot);
+  const size_t off_pcount = d->alloc(4);
+  const size_t off_icount = d->alloc(4);
+  const size_t off_ocount = d->alloc(4);
+  KNN_REQUIRE(d->bump <= d->bytes, "symmetric heap too small (internal sizing error)");
+
+  PvMainParams p;
+  memset(&p, 0, sizeof(p));
+  p.tree = idx->view();
+  p.k = k;
+  p.sentinel = sentinel_d2(max_radius);
+  p.R = R;
+  p.rank = me;
+  for (int r = 0; r < R; ++r) for (int a = 0; a < 6; ++a) p.boxes[r][a] = boxes[(size_t)r * 6 + a];
+  p.home_queries = idx->pts;
+  p.home_n = idx->n;
+  p.home_is_tree = 1;
+  p.result_sorted = idx->result_sorted;
+  p.pending = d->base + off_pending;
+  p.pending_count = reinterpret_cast<int*>(d->base + off_pcount);
+  p.inbox = d->base + off_inbox;
+  p.inbox_count = reinterpret_cast<const int*>(d->base + off_icount);
+  p.task_counter = d->task_counter;
+  p.stats = idx->stats_on ? idx->stats : nullptr;
+  int* out_count = reinterpret_cast<int*>(d->base + off_ocount);
+  const int64_t my_groups = idx->groups();
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
+
+  int rc;
+  for (int c = 0; c < pl.C; ++c) {
+    KNN_CUDA_TRY(cudaMemsetAsync(p.pending_count, 0, sizeof(int), stream));
+    p.phase = 0;
+    p.group_begin = (int64_t)c * pl.Gc;
+    int64_t gc = my_groups - p.group_begin;
+    gc = gc < 0 ? 0 : (gc > pl.Gc ? pl.Gc : gc);
+    p.group_count = (int)gc;
+    if ((rc = pv_main_launch(p, p.group_count, idx->num_sms, stream))) return rc;
+    if (R == 1) continue;
+    // any work for the exchange at all? (one tiny allgather per chunk saves 2(R-1) fences when not)
+    int my_pending = 0;
+    KNN_CUDA_TRY(cudaMemcpyAsync(&my_pending, p.pending_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    std::vector<int> all_pending(R);
+    if (d->allgather(&my_pending, all_pending.data(), sizeof(int))) { set_last_error("bootstrap allgather failed"); return -3; }
+    int64_t total_pending = 0;
+    for (int v : all_pending) total_pending += v;
+    if (rep) { rep->pending_groups += my_pending; rep->chunks += 1; }
+    if (total_pending == 0) continue;
+    for (int j = 1; j < R; ++j) {
+      const int dst = (me + j) % R, src = (me - j + R) % R;
+      if ((rc = pv_push_launch(p.pending, p.pending_count, k, &boxes[(size_t)dst * 6], d->peer[dst] + off_inbox,
+                               out_count, idx->num_sms, stream))) return rc;
+      if ((rc = pv_publish_launch(out_count, reinterpret_cast<int*>(d->peer[dst] + off_icount), stream))) return rc;
+      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
+      p.phase = 1;
+      p.src_pending = d->peer[src] + off_pending;
+      if ((rc = pv_main_launch(p, pl.Gc, idx->num_sms, stream))) return rc;
+      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
+      if (rep) rep->rounds += 1;
+    }
+    if ((rc = pv_final_launch(p.pending, p.pending_count, k, idx->result_sorted, idx->num_sms, stream))) return rc;
+  }
+  return 0;
+}
+
+int knn_prepartitioned(b200knn_dist* d, const float* d_xyz, int64_t n_local, int k, float max_radius,
+                       int groups_per_chunk, float* d_out, cudaStream_t stream, b200knn_dist_report* rep) {
+  int rc;
+  int64_t max_n = 0;
+  {
+    std::vector<int64_t> all(d->world);
+    if (d->allgather(&n_local, all.data(), sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
+    for (int64_t v : all) max_n = std::max(max_n, v);
+  }
+  const PvPlan pl = pv_plan(max_n, groups_per_chunk);
+  if ((rc = ensure_heap(d, pv_heap_need(k, pl.Gc)))) return rc;
+  d->bump = 0;
+  const double t0 = now_ms();
+  b200knn_index* idx = nullptr;
+  if ((rc = b200knn_index_create(d_xyz, n_local, nullptr, 0, stream, &idx))) { b200knn_index_destroy(idx); return rc; }
+  const double t1 = now_ms();
+  rc = run_pv(d, idx, k, max_radius, pl, stream, rep);
+  if (!rc) rc = scatter_results(idx->pts, idx->result_sorted, idx->n, 0, d_out, stream);
+  if (!rc) { cudaError_t e = cudaStreamSynchronize(stream); if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; } }
+  if (rep) { rep->ms_build += t1 - t0; rep->ms_query += now_ms() - t1; }
+  b200knn_index_destroy(idx);
+  return rc;
+}
+
+int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64_t global_begin, int k,
+                     float max_radius, int groups_per_chunk, float* d_out, cudaStream_t stream,
+                     b200knn_dist_report* rep) {
+  const int R = d->world, me = d->rank;
+  int rc;
+  const double t0 = now_ms();
+  // ---- who has what
+  struct Info { int64_t n, begin; float box[6]; };
+  Info mine{};
+  mine.n = n_local;
+  mine.begin = global_begin;
+  unsigned* d_bord = nullptr;
+  float* d_box6 = nullptr;
+  KNN_CUDA_TRY(cudaMallocAsync(&d_bord, 6 * sizeof(unsigned), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&d_box6, 6 * sizeof(float), stream));
+  if ((rc = bounds_init(d_bord, stream))) return rc;
+  if ((rc = bounds_accumulate(d_xyz, 3, n_local, d_bord, stream))) return rc;
+  if ((rc = bounds_decode(d_bord, d_box6, stream))) return rc;
+  KNN_CUDA_TRY(cudaMemcpyAsync(mine.box, d_box6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  std::vector<Info> info(R);
+  if (d->allgather(&mine, info.data(), sizeof(Info))) { set_last_error("bootstrap allgather failed"); return -3; }
+  float gbox[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  int64_t max_local = 0, total = 0;
+  for (int r = 0; r < R; ++r) {
+    for (int a = 0; a < 3; ++a) { gbox[a] = fminf(gbox[a], info[r].box[a]); gbox[3 + a] = fmaxf(gbox[3 + a], info[r].box[3 + a]); }
+    max_local = std::max(max_local, info[r].n);
+    total += info[r].n;
+    KNN_REQUIRE(r == 0 || info[r].begin == info[r - 1].begin + info[r - 1].n,
+                "redistribute: ranks must hold consecutive slices of the global point order");
+  }
+  KNN_REQUIRE(info[0].begin + total <= (int64_t)0xffffffffll, "redistribute: global point ids must fit 32 bits");
+  KNN_CUDA_TRY(cudaMemcpyAsync(d_box6, gbox, sizeof(gbox), cudaMemcpyHostToDevice, stream));
+
+  // ---- local sort by GLOBAL Morton key
+  uint64_t *keys = nullptr, *keys_tmp = nullptr, *d_samples = nullptr, *d_split = nullptr;
+  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr;
+  int64_t* d_cut = nullptr;
+  const int S = 2048;
+  const int64_t na = n_local > 0 ? n_local : 1;
+  KNN_CUDA_TRY(cudaMallocAsync(&keys, na * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, na * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&vals, na * sizeof(uint32_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, na * sizeof(uint32_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(na), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&d_samples, S * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&d_split, B200KNN_MAX_RANKS * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&d_cut, B200KNN_MAX_RANKS * sizeof(int64_t), stream));
+  if ((rc = morton_keys(d_xyz, 3, n_local, d_box6, keys, vals, stream))) return rc;
+  int in_tmp = 0;
+  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n_local, 0, 64, stream, &in_tmp))) return rc;
+  const uint64_t* skeys = in_tmp ? keys_tmp : keys;
+  const uint32_t* order = in_tmp ? vals_tmp : vals;
+
+  // ---- splitters from evenly spaced local order statistics
+  std::vector<uint64_t> my_samples(S), all_samples((size_t)S * R);
+  if ((rc = sample_keys_launch(skeys, n_local, S, d_samples, stream))) return rc;
+  KNN_CUDA_TRY(cudaMemcpyAsync(my_samples.data(), d_samples, S * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
+  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  if (d->allgather(my_samples.data(), all_samples.data(), S * sizeof(uint64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
+  std::sort(all_samples.begin(), all_samples.end());
+  uint64_t split[B200KNN_MAX_RANKS] = {};
+  for (int j = 1; j < R; ++j) split[j - 1] = all_samples[(size_t)j * S];
+  std::vector<int64_t> cut(R + 1, 0);
+  if (R > 1) {
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_split, split, (R - 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
+    if ((rc = lower_bounds_launch(skeys, n_local, d_split, R - 1, d_cut, stream))) return rc;
+    KNN_CUDA_TRY(cudaMemcpyAsync(cut.data() + 1, d_cut, (R - 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
+    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  }
+  cut[R] = n_local;
+
+  // ---- count matrix
+  std::vector<int64_t> send(R), M((size_t)R * R);
+  for (int r = 0; r < R; ++r) send[r] = cut[r + 1] - cut[r];
+  if (d->allgather(send.data(), M.data(), R * sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
+  int64_t max_recv = 0, my_recv = 0;
+  std::vector<int64_t> recv_n(R, 0);
+  for (int dst = 0; dst < R; ++dst) {
+    for (int s = 0; s < R; ++s) recv_n[dst] += M[(size_t)s * R + dst];
+    max_recv = std::max(max_recv, recv_n[dst]);
+  }
+  my_recv = recv_n[me];
+  KNN_REQUIRE(max_recv < (int64_t)0x7fffffff - 64, "redistribute: a rank would receive more than 2^31 points");
+
+  // ---- symmetric heap: receive buffer + result landing zone + exchange slots
+  const PvPlan pl = pv_plan(max_recv, groups_per_chunk);
+  const size_t need = align256((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4)) +
+                      align256((size_t)std::max<int64_t>(max_local, 1) * sizeof(float)) + pv_heap_need(k, pl.Gc);
+  if ((rc = ensure_heap(d, need))) return rc;
+  d->bump = 0;
+  const size_t off_recv = d->alloc((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4));
+  const size_t off_out = d->alloc((size_t)std::max<int64_t>(max_local, 1) * sizeof(float));
+
+  RedistributeParams rp;
+  memset(&rp, 0, sizeof(rp));
+  rp.xyz = d_xyz;
+  rp.order = order;
+  rp.n = n_local;
+  rp.global_begin = global_begin;
+  rp.R = R;
+  for (int r = 0; r <= R; ++r) rp.cut[r] = cut[r];
+  for (int dst = 0; dst < R; ++dst) {
+    rp.recv[dst] = reinterpret_cast<Float4*>(d->peer[dst] + off_recv);
+    int64_t off = 0;
+    for (int s = 0; s < me; ++s) off += M[(size_t)s * R + dst];
+    rp.recv_offset[dst] = off;
+  }
+  if ((rc = redistribute_launch(rp, stream))) return rc;
+  KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(d_samples, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(d_split, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(d_cut, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(d_bord, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(d_box6, stream));
+  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
+  const double t1 = now_ms();
+
+  // ---- local index over the received (spatially compact) points, then the culled exchange
+  b200knn_index* idx = nullptr;
+  rc = b200knn_index_create_xyzw(reinterpret_cast<const float*>(d->base + off_recv), my_recv, 0, stream, &idx);
+  const double t2 = now_ms();
+  if (!rc) rc = run_pv(d, idx, k, max_radius, pl, stream, rep);
+  const double t3 = now_ms();
+
+  // ---- results go back to the rank that read the point
+  if (!rc) {
+    ReturnParams q;
+    memset(&q, 0, sizeof(q));
+    q.pts = idx->pts;
+    q.result_sorted = idx->result_sorted;
+    q.n = idx->n;
+    q.R = R;
+    for (int r = 0; r < R; ++r) {
+      q.begin[r] = info[r].begin;
+      q.out[r] = reinterpret_cast<float*>(d->peer[r] + off_out);
+    }
+    q.begin[R] = info[R - 1].begin + info[R - 1].n;
+    rc = return_results_launch(q, stream);
+  }
+  if (!rc) {
+    cudaError_t e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
+  }
+  if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
+  if (!rc && n_local > 0) {
+    cudaError_t e = cudaMemcpyAsync(d_out, d->base + off_out, (size_t)n_local * sizeof(float), cudaMemcpyDeviceToDevice, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
+  }
+  // nobody may start overwriting the landing zone (next call) before everyone has copied out
+  if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
+  if (rep) {
+    rep->ms_redistribute += t1 - t0;
+    rep->ms_build += t2 - t1;
+    rep->ms_query += t3 - t2;
+    rep->ms_return += now_ms() - t3;
+    rep->points_after_redistribute = my_recv;
+  }
+  b200knn_index_destroy(idx);
+  return rc;
+}
+
+int knn_ring(b200knn_dist* d, const float* d_xyz, int64_t n_local, int k, float max_radius, int groups_per_chunk,
+             float* d_out, cudaStream_t stream, b200knn_dist_report* rep) {
+  int rc;
+  int64_t max_n = 0;
+  {
+    std::vector<int64_t> all(d->world);
+    if (d->allgather(&n_local, all.data(), sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
+    for (int64_t v : all) max_n = std::max(max_n, v);
+  }
+  const double t0 = now_ms();
+  b200knn_index* idx = nullptr;
+  b200knn_ring* ring = nullptr;
+  rc = b200knn_index_create(d_xyz, n_local, nullptr, 0, stream, &idx);
+  const double t1 = now_ms();
+  if (!rc) rc = b200knn_ring_create(idx, d->rank, d->world, k, max_n, groups_per_chunk, &ring);
+  std::vector<char> mine(B200KNN_IPC_BLOB_BYTES), all((size_t)B200KNN_IPC_BLOB_BYTES * d->world);
+  if (!rc) rc = b200knn_ring_export(ring, mine.data());
+  if (!rc && d->allgather(mine.data(), all.data(), B200KNN_IPC_BLOB_BYTES)) { set_last_error("bootstrap allgather failed"); rc = -3; }
+  if (!rc) rc = b200knn_ring_connect(ring, all.data());
+  if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
+  if (!rc) rc = b200knn_ring_run(ring, max_radius, stream);
+  if (!rc) { cudaError_t e = cudaStreamSynchronize(stream); if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; } }
+  if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
+  if (!rc) rc = b200knn_ring_results(ring, d_out, stream);
+  if (!rc) { cudaError_t e = cudaStreamSynchronize(stream); if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; } }
+  if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
+  if (rep) { rep->ms_build += t1 - t0; rep->ms_query += now_ms() - t1; }
+  b200knn_ring_destroy(ring);
+  b200knn_index_destroy(idx);
+  return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200knn_dist_create(const b200knn_bootstrap* bs, b200knn_dist** out) {
+  KNN_REQUIRE(bs && out, "dist_create: NULL argument");
+  KNN_REQUIRE(bs->world >= 1 && bs->world <= B200KNN_MAX_RANKS, "dist_create: world must be in [1,16]");
+  KNN_REQUIRE(bs->rank >= 0 && bs->rank < bs->world, "dist_create: rank out of range");
+  KNN_REQUIRE(bs->world == 1 || (bs->allgather && bs->barrier), "dist_create: bootstrap callbacks missing");
+  b200knn_dist* d = new b200knn_dist();
+  *out = d;
+  d->bs = *bs;
+  d->rank = bs->rank;
+  d->world = bs->world;
+  KNN_CUDA_TRY(cudaGetDevice(&d->device));
+  KNN_CUDA_TRY(cudaDeviceGetAttribute(&d->num_sms, cudaDevAttrMultiProcessorCount, d->device));
+  KNN_CUDA_TRY(cudaMalloc(&d->task_counter, sizeof(unsigned long long)));
+  return 0;
+}
+
+void b200knn_dist_destroy(b200knn_dist* d) {
+  if (!d) return;
+  cudaDeviceSynchronize();
+  if (d->world > 1) d->barrier();
+  close_heap(d);
+  cudaFree(d->task_counter);
+  delete d;
+}
+
+int64_t b200knn_dist_heap_bytes(const b200knn_dist* d) { return d ? (int64_t)d->bytes : 0; }
+
+int b200knn_dist_knn(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64_t global_begin, int k,
+                     float max_radius, int mode, int groups_per_chunk, float* d_out, void* stream_,
+                     b200knn_dist_report* report) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  KNN_REQUIRE(d, "dist_knn: NULL engine");
+  KNN_REQUIRE(k >= 1, "dist_knn: k must be >= 1");
+  KNN_REQUIRE(n_local >= 0 && (n_local == 0 || (d_xyz && d_out)), "dist_knn: bad point buffers");
+  if (report) memset(report, 0, sizeof(*report));
+  const double t0 = now_ms();
+  int rc;
+  switch (mode) {
+    case B200KNN_MODE_RING:
+      rc = knn_ring(d, d_xyz, n_local, k, max_radius, groups_per_chunk, d_out, stream, report);
+      break;
+    case B200KNN_MODE_PREPARTITIONED:
+      rc = knn_prepartitioned(d, d_xyz, n_local, k, max_radius, groups_per_chunk, d_out, stream, report);
+      break;
+    case B200KNN_MODE_REDISTRIBUTE:
+      rc = knn_redistribute(d, d_xyz, n_local, global_begin, k, max_radius, groups_per_chunk, d_out, stream, report);
+      break;
+    default:
+      set_last_error("dist_knn: unknown mode");
+      rc = -2;
+  }
+  if (report) report->ms_total = now_ms() - t0;
+  return rc;
+}
+
+}  // extern "C"

@@ -33,13 +33,14 @@ struct Bounds { float lo[3]; float hi[3]; };
 
 // d_bounds_ord: 6 unsigned (order-preserving encoding), must be initialised by bounds_init.
 int bounds_init(unsigned* d_bounds_ord, cudaStream_t stream);
-int bounds_accumulate(const float* d_xyz, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream);
+int bounds_accumulate(const float* d_xyz, int stride, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream);
 int bounds_decode(const unsigned* d_bounds_ord, float* d_bounds6, cudaStream_t stream);
+// `stride` = floats per input point: 3 (xyz) or 4 (xyzw, id bits in w).
 // keys[i] = morton63(point i) relative to *d_bounds6 (device-resident lo[3],hi[3]); vals[i] = i.
-int morton_keys(const float* d_xyz, int64_t n, const float* d_bounds6, uint64_t* keys,
+int morton_keys(const float* d_xyz, int stride, int64_t n, const float* d_bounds6, uint64_t* keys,
                 uint32_t* vals, cudaStream_t stream);
 // sorted[i] = (xyz[order[i]], id = ids ? ids[order[i]] : order[i] + id_offset)
-int gather_points(const float* d_xyz, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
+int gather_points(const float* d_xyz, int stride, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
                   int64_t n, Float4* sorted, cudaStream_t stream);
 // Re-order every 1024-point Morton run into a balanced k-d tree with compact 32-point leaves.
 int refine_runs(Float4* sorted, int64_t n, cudaStream_t stream);
@@ -88,6 +89,65 @@ struct RingParams {
 size_t ring_smem_bytes(int k, int warps_per_cta);
 int ring_pick_warps_per_cta(int k);
 int ring_launch(const RingParams& p, int num_sms, cudaStream_t stream);
+
+// ---------------- culled exchange / redistribution (pv.cu) ----------------
+// A slot carries one group: heap [k][32] floats, positions [32] float4, meta [4] int32.
+KNN_HD size_t pv_slot_bytes(int k) { return (size_t)k * 128 + 512 + 16; }
+
+struct PvMainParams {
+  TreeView tree;
+  int k;
+  float sentinel;
+  int phase;                   // 0 = LOCAL (home groups, fresh heaps), 1 = SERVE (visiting groups from the inbox)
+  int R, rank;
+  float boxes[kMaxRanks][6];   // every rank's bounding box (lo xyz, hi xyz)
+  // LOCAL
+  const Float4* home_queries;
+  int64_t home_n;
+  int home_is_tree;
+  int64_t group_begin;         // first home group of this chunk
+  int group_count;             // groups in this chunk
+  float* result_sorted;
+  char* pending;               // local pending slots
+  int* pending_count;
+  // SERVE
+  const char* inbox;           // local inbox slots (filled by a peer's pv_push)
+  const int* inbox_count;
+  char* src_pending;           // the visiting groups' home GPU's pending slots (peer pointer)
+  unsigned long long* task_counter;
+  unsigned long long* stats;
+};
+int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream);
+int pv_push_launch(const char* pending, const int* pending_count, int k, const float* box6, char* peer_inbox,
+                   int* out_count, int num_sms, cudaStream_t stream);
+int pv_publish_launch(const int* out_count, int* peer_inbox_count, cudaStream_t stream);
+int pv_final_launch(const char* pending, const int* pending_count, int k, float* result_sorted, int num_sms,
+                    cudaStream_t stream);
+
+struct RedistributeParams {
+  const float* xyz;            // local points, caller order
+  const uint32_t* order;       // order[i] = caller index of the i-th point in global Morton order
+  int64_t n;
+  int64_t global_begin;        // global index of local point 0
+  int R;
+  int64_t cut[kMaxRanks + 1];  // destination d takes sorted positions [cut[d], cut[d+1])
+  Float4* recv[kMaxRanks];     // destination receive buffers (peer pointers)
+  int64_t recv_offset[kMaxRanks];   // where this rank's run starts inside recv[d]
+};
+int redistribute_launch(const RedistributeParams& p, cudaStream_t stream);
+
+struct ReturnParams {
+  const Float4* pts;           // local sorted points, .w = global id
+  const float* result_sorted;
+  int64_t n;
+  int R;
+  int64_t begin[kMaxRanks + 1];     // rank o originally read global ids [begin[o], begin[o+1])
+  float* out[kMaxRanks];       // owners' output arrays (peer pointers)
+};
+int return_results_launch(const ReturnParams& p, cudaStream_t stream);
+int sample_keys_launch(const uint64_t* sorted_keys, int64_t n, int samples, uint64_t* out, cudaStream_t stream);
+int lower_bounds_launch(const uint64_t* sorted_keys, int64_t n, const uint64_t* splitters, int count,
+                        int64_t* out, cudaStream_t stream);
 
 // out[id(i)] = sorted_result[i]  (id taken from pts[i].w, minus id_offset)
 int scatter_results(const Float4* sorted_pts, const float* sorted_result, int64_t n,

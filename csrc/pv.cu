@@ -1,0 +1,322 @@
+// pv.cu — kernels of the bounding-box-culled exchange (pre-partitioned variant and the redistributed
+// fast path of the unordered variant), plus point redistribution and result return.
+//
+// Reference behaviour being replaced (/root/reference/prePartitionedDataVariant.cu:304-357): every
+// round each rank pulls ONE whole peer tree, chosen by one scalar radius per rank against one box
+// per peer, and re-runs all of its queries against it. Here the trees never move and culling is per
+// query group:
+//   pv_main (phase LOCAL)  all home groups against the home tree; a group whose ball still reaches
+//                          another rank's box keeps its heaps in a "pending" slot
+//   pv_push                per round, pending groups that reach the round's destination box are
+//                          compacted and written straight into that GPU's inbox (peer stores)
+//   pv_main (phase SERVE)  the destination traverses its tree for the visiting groups and writes the
+//                          improved heaps straight back into the home GPU's pending slots (peer
+//                          stores) — the merge-back
+//   pv_final               k-th distances of pending groups
+// Rounds are separated by a host barrier (see dist.cu); all data movement is done by these kernels
+// over NVLink-mapped peer memory, never by a collective library.
+//
+// redistribute / return_results: the all-to-all scatter of points to their spatial owner and of the
+// results back to the rank that read the point — both as in-kernel peer stores (new capability;
+// the reference never redistributes).
+#include "traverse.cuh"
+
+namespace b200knn {
+
+namespace {
+
+__device__ __forceinline__ float* slot_heap(char* slot) { return reinterpret_cast<float*>(slot); }
+__device__ __forceinline__ const float* slot_heap(const char* slot) { return reinterpret_cast<const float*>(slot); }
+__device__ __forceinline__ float4* slot_pos(char* slot, int k) {
+  return reinterpret_cast<float4*>(slot + (size_t)k * 128);
+}
+__device__ __forceinline__ const float4* slot_pos(const char* slot, int k) {
+  return reinterpret_cast<const float4*>(slot + (size_t)k * 128);
+}
+__device__ __forceinline__ int* slot_meta(char* slot, int k) {
+  return reinterpret_cast<int*>(slot + (size_t)k * 128 + 512);
+}
+__device__ __forceinline__ const int* slot_meta(const char* slot, int k) {
+  return reinterpret_cast<const int*>(slot + (size_t)k * 128 + 512);
+}
+
+__global__ void __launch_bounds__(Q_MAX_WARPS * 32, 1)
+pv_main_kernel(const PvMainParams p) {
+  extern __shared__ __align__(16) float q_smem[];
+  const int lane = lane_id();
+  const int k = p.k;
+  GroupCtx g;
+  group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k);
+  const int kp = g.kp;
+  const size_t slot_bytes = pv_slot_bytes(k);
+  const int total = p.phase == 0 ? p.group_count : ldcg_i(p.inbox_count);
+
+  for (;;) {
+    unsigned long long t = 0;
+    if (lane == 0) t = atomicAdd(p.task_counter, 1ull);
+    t = __shfl_sync(kFullMask, t, 0);
+    if (t >= (unsigned long long)total) break;
+
+    int cnt, home_slot = 0;
+    int64_t home_group = 0;
+    if (p.phase == 0) {
+      home_group = p.group_begin + (int64_t)t;
+      const int64_t rem = p.home_n - home_group * kGroup;
+      cnt = rem <= 0 ? 0 : (rem < kGroup ? (int)rem : kGroup);
+      if (cnt > 0) {
+        const int src = lane < cnt ? lane : cnt - 1;
+        const float4 q = __ldg(reinterpret_cast<const float4*>(p.home_queries) + home_group * kGroup + src);
+        g.qx = q.x; g.qy = q.y; g.qz = q.z;
+        const float sent = p.sentinel;
+        for (int i = 0; i < k; ++i) g.heap[i * 32] = sent;
+        g.top = sent;
+      }
+    } else {
+      const char* slot = p.inbox + (size_t)t * slot_bytes;
+      const int* meta = slot_meta(slot, k);
+      home_slot = ldcg_i(meta + 0);
+      cnt = ldcg_i(meta + 1);
+      const float4 q = ldcg_f4(slot_pos(slot, k) + lane);
+      g.qx = q.x; g.qy = q.y; g.qz = q.z;
+      const float* src = slot_heap(slot) + lane;
+      for (int i = 0; i < k; ++i) g.heap[i * 32] = ldcg_f(src + (size_t)i * 32);
+      g.top = g.heap[0];
+    }
+    g.valid = lane < cnt;
+
+    if (cnt > 0 && p.tree.n > 0) {
+      for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;
+      group_bounds(g);
+      const int seed = (p.phase == 0 && p.home_is_tree)
+                           ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1)
+                           : find_seed_l1(p.tree, g);
+      traverse(p.tree, g, seed);
+    }
+
+    if (p.phase == 0) {
+      if (cnt > 0) {
+        if (g.valid) p.result_sorted[home_group * kGroup + lane] = finalize_kth(g.top);
+        // does any lane's ball still reach another rank's box?
+        bool need = false;
+        for (int s = 0; s < p.R; ++s) {
+          if (s == p.rank) continue;
+          const float lb = point_box_lb(g.qx, g.qy, g.qz, p.boxes[s][0], p.boxes[s][1], p.boxes[s][2],
+                                        p.boxes[s][3], p.boxes[s][4], p.boxes[s][5]);
+          need = need || (lb < g.top);
+        }
+        if (__any_sync(kFullMask, g.valid && need)) {
+          int slot_idx = 0;
+          if (lane == 0) slot_idx = atomicAdd(p.pending_count, 1);
+          slot_idx = __shfl_sync(kFullMask, slot_idx, 0);
+          char* slot = p.pending + (size_t)slot_idx * slot_bytes;
+          float* dst = slot_heap(slot) + lane;
+          for (int i = 0; i < k; ++i) dst[(size_t)i * 32] = g.heap[i * 32];
+          slot_pos(slot, k)[lane] = make_float4(g.qx, g.qy, g.qz, 0.f);
+          if (lane == 0) {
+            int* meta = slot_meta(slot, k);
+            meta[0] = (int)(home_group & 0xffffffffll);
+            meta[1] = cnt;
+            meta[2] = (int)(home_group >> 32);
+            meta[3] = 0;
+          }
+        }
+      }
+    } else if (cnt > 0) {
+      // merge-back: improved heaps go straight into the home GPU's pending slot
+      float* dst = slot_heap(p.src_pending + (size_t)home_slot * slot_bytes) + lane;
+      for (int i = 0; i < k; ++i) dst[(size_t)i * 32] = g.heap[i * 32];
+    }
+    __syncwarp();
+  }
+  flush_stats(g, p.stats);
+}
+
+// One warp per pending slot: if any lane's ball reaches the destination box, copy the whole slot
+// into the next free slot of the destination GPU's inbox.
+__global__ void __launch_bounds__(256)
+pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending_count, int k,
+               float blx, float bly, float blz, float bhx, float bhy, float bhz,
+               char* __restrict__ peer_inbox, int* __restrict__ out_count) {
+  const int lane = lane_id();
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const size_t slot_bytes = pv_slot_bytes(k);
+  const int total = *pending_count;
+  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < total; s += warps) {
+    const char* slot = pending + (size_t)s * slot_bytes;
+    const int cnt = slot_meta(slot, k)[1];
+    const float4 q = slot_pos(slot, k)[lane];
+    const float top = slot_heap(slot)[lane];
+    const float lb = point_box_lb(q.x, q.y, q.z, blx, bly, blz, bhx, bhy, bhz);
+    if (!__any_sync(kFullMask, lane < cnt && lb < top)) continue;
+    int o = 0;
+    if (lane == 0) o = atomicAdd(out_count, 1);
+    o = __shfl_sync(kFullMask, o, 0);
+    char* dst = peer_inbox + (size_t)o * slot_bytes;
+    // heap rows + positions: k*128 + 512 bytes = (k*8 + 32) float4 per warp pass of 32
+    const float4* src4 = reinterpret_cast<const float4*>(slot);
+    float4* dst4 = reinterpret_cast<float4*>(dst);
+    const int n4 = k * 8 + 32;
+    for (int i = lane; i < n4; i += 32) dst4[i] = src4[i];
+    if (lane == 0) {
+      int* meta = slot_meta(dst, k);
+      meta[0] = s;        // home slot: where the merge-back goes
+      meta[1] = cnt;
+      meta[2] = 0;
+      meta[3] = 0;
+    }
+  }
+}
+
+__global__ void pv_publish_kernel(const int* __restrict__ out_count, int* __restrict__ peer_inbox_count) {
+  if (threadIdx.x == 0) *peer_inbox_count = *out_count;
+}
+
+__global__ void __launch_bounds__(256)
+pv_final_kernel(const char* __restrict__ pending, const int* __restrict__ pending_count, int k,
+                float* __restrict__ result_sorted) {
+  const int lane = lane_id();
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const size_t slot_bytes = pv_slot_bytes(k);
+  const int total = *pending_count;
+  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < total; s += warps) {
+    const char* slot = pending + (size_t)s * slot_bytes;
+    const int* meta = slot_meta(slot, k);
+    const int64_t home_group = ((int64_t)meta[2] << 32) | (uint32_t)meta[0];
+    if (lane < meta[1]) result_sorted[home_group * kGroup + lane] = finalize_kth(slot_heap(slot)[lane]);
+  }
+}
+
+// ---- redistribution ---------------------------------------------------------------------------
+// Local points are already ordered by global Morton key, so each destination's share is one
+// contiguous run [cut[d], cut[d+1]). Thread i writes point order[i] (with its global id) into the
+// destination GPU's receive buffer: coalesced 16-byte peer stores within each run.
+__global__ void __launch_bounds__(256)
+redistribute_kernel(const RedistributeParams p) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.n) return;
+  int d = 0;
+  while (d + 1 < p.R && i >= p.cut[d + 1]) ++d;
+  const uint32_t src = p.order[i];
+  float4 v;
+  v.x = p.xyz[3 * (size_t)src];
+  v.y = p.xyz[3 * (size_t)src + 1];
+  v.z = p.xyz[3 * (size_t)src + 2];
+  v.w = __uint_as_float((uint32_t)(p.global_begin + src));
+  reinterpret_cast<float4*>(p.recv[d])[p.recv_offset[d] + (i - p.cut[d])] = v;
+}
+
+// result of sorted point i goes to the rank that originally read the point: out[owner][id - begin].
+__global__ void __launch_bounds__(256)
+return_results_kernel(const ReturnParams p) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= p.n) return;
+  const uint32_t id = __float_as_uint(p.pts[i].w);
+  int o = 0;
+  while (o + 1 < p.R && (int64_t)id >= p.begin[o + 1]) ++o;
+  p.out[o][(int64_t)id - p.begin[o]] = p.result_sorted[i];
+}
+
+__global__ void __launch_bounds__(256)
+sample_keys_kernel(const uint64_t* __restrict__ sorted_keys, int64_t n, int samples, uint64_t* __restrict__ out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= samples) return;
+  // evenly spaced order statistics of the local key distribution
+  out[j] = n > 0 ? sorted_keys[(int64_t)(((double)j + 0.5) * (double)n / (double)samples)] : ~0ull;
+}
+
+__global__ void lower_bounds_kernel(const uint64_t* __restrict__ sorted_keys, int64_t n,
+                                    const uint64_t* __restrict__ splitters, int count, int64_t* __restrict__ out) {
+  const int j = threadIdx.x;
+  if (j >= count) return;
+  const uint64_t s = splitters[j];
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (sorted_keys[mid] < s) lo = mid + 1; else hi = mid;
+  }
+  out[j] = lo;
+}
+
+inline int blocks_for(int64_t n, int block) { return (int)div_up(n, block); }
+
+}  // namespace
+
+int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream) {
+  KNN_REQUIRE(p.k >= 1, "k must be >= 1");
+  const int warps = group_pick_warps(p.k, (const void*)pv_main_kernel);
+  KNN_REQUIRE(warps >= 1, "k too large for the shared-memory heap (k <= 1790)");
+  const size_t smem = group_smem_bytes(p.k, warps);
+  KNN_CUDA_TRY(cudaFuncSetAttribute(pv_main_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pv_main_kernel, warps * 32, smem));
+  KNN_REQUIRE(occ >= 1, "pv kernel does not fit on an SM");
+  if (max_tasks <= 0) return 0;
+  long long want = ((long long)max_tasks + warps - 1) / warps;
+  long long cap = (long long)num_sms * occ;
+  const int grid = (int)(want < cap ? want : cap);
+  KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
+  pv_main_kernel<<<grid, warps * 32, smem, stream>>>(p);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int pv_push_launch(const char* pending, const int* pending_count, int k, const float* box6, char* peer_inbox,
+                   int* out_count, int num_sms, cudaStream_t stream) {
+  KNN_CUDA_TRY(cudaMemsetAsync(out_count, 0, sizeof(int), stream));
+  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, box6[0], box6[1], box6[2], box6[3],
+                                                 box6[4], box6[5], peer_inbox, out_count);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int pv_publish_launch(const int* out_count, int* peer_inbox_count, cudaStream_t stream) {
+  pv_publish_kernel<<<1, 32, 0, stream>>>(out_count, peer_inbox_count);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int pv_final_launch(const char* pending, const int* pending_count, int k, float* result_sorted, int num_sms,
+                    cudaStream_t stream) {
+  pv_final_kernel<<<num_sms * 4, 256, 0, stream>>>(pending, pending_count, k, result_sorted);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int redistribute_launch(const RedistributeParams& p, cudaStream_t stream) {
+  if (p.n <= 0) return 0;
+  redistribute_kernel<<<blocks_for(p.n, 256), 256, 0, stream>>>(p);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int return_results_launch(const ReturnParams& p, cudaStream_t stream) {
+  if (p.n <= 0) return 0;
+  return_results_kernel<<<blocks_for(p.n, 256), 256, 0, stream>>>(p);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int sample_keys_launch(const uint64_t* sorted_keys, int64_t n, int samples, uint64_t* out, cudaStream_t stream) {
+  sample_keys_kernel<<<blocks_for(samples, 256), 256, 0, stream>>>(sorted_keys, n, samples, out);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int lower_bounds_launch(const uint64_t* sorted_keys, int64_t n, const uint64_t* splitters, int count,
+                        int64_t* out, cudaStream_t stream) {
+  KNN_REQUIRE(count <= 32, "lower_bounds: too many splitters");
+  if (count <= 0) return 0;
+  lower_bounds_kernel<<<1, 32, 0, stream>>>(sorted_keys, n, splitters, count, out);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200knn

@@ -1,0 +1,343 @@
+// traverse.cuh — device-side group traversal shared by the query/ring kernel (query.cu) and the
+// culled-exchange kernels (pv.cu): per-warp context, padded 4-ary heap, leaf sweep, seed phase,
+// best-first frontier with depth-first overflow. See the header comment of query.cu for the design.
+#pragma once
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200knn {
+namespace {
+
+constexpr int Q_MAX_WARPS = 16;        // per CTA
+constexpr int kQueueCap = 256;         // frontier entries per warp (2 KB)
+constexpr unsigned kNodeIdxBits = 28;  // node = level << 28 | index
+
+__host__ __device__ constexpr int heap_padded(int k) { return 4 * ((k - 1 + 3) / 4) + 1; }
+__host__ __device__ constexpr size_t warp_smem_floats(int k) {
+  return (size_t)heap_padded(k) * 32 + 128 + 2 * kQueueCap + 32;
+}
+
+struct GroupCtx {
+  float qx, qy, qz;     // this lane's query
+  float top;            // this lane's current k-th squared distance (heap root)
+  float glx, gly, glz, ghx, ghy, ghz;   // bounding box of the group's valid queries (warp-uniform)
+  float maxR2;          // max over valid lanes of top (warp-uniform)
+  float* heap;          // shared: heap[i*32] is entry i of this lane
+  float4* stage;        // shared: 32 leaf points
+  unsigned* qkey;       // shared: frontier lower bounds (float bits; non-negative => uint-ordered)
+  unsigned* qnode;      // shared: frontier nodes
+  unsigned* frames;     // shared: frame stack of the depth-first fallback
+  int kp;               // padded heap size
+  bool valid;
+  unsigned n_leaves, n_inner, n_inserts, n_fallback, n_purge;
+};
+
+// Replace the root (precondition e < root) and sift down. Children of i: 4i+1..4i+4, all present.
+__device__ __forceinline__ float heap_replace_padded(float* h, int kp, float e) {
+  int i = 0;
+  for (;;) {
+    const int c0 = 4 * i + 1;
+    if (c0 >= kp) break;
+    const float a0 = h[c0 * 32], a1 = h[(c0 + 1) * 32], a2 = h[(c0 + 2) * 32], a3 = h[(c0 + 3) * 32];
+    const float m01 = fmaxf(a0, a1), m23 = fmaxf(a2, a3);
+    const int i01 = a1 > a0 ? c0 + 1 : c0, i23 = a3 > a2 ? c0 + 3 : c0 + 2;
+    const float best = fmaxf(m01, m23);
+    const int bi = m23 > m01 ? i23 : i01;
+    if (!(best > e)) break;
+    h[i * 32] = best;
+    i = bi;
+  }
+  h[i * 32] = e;
+  return h[0];
+}
+
+__device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g) {
+  const int lane = lane_id();
+  float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);   // padding never beats any top
+  if (lane < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane);
+  g.stage[lane] = p;
+  __syncwarp();
+
+  // phase 1: convergent distance sweep
+  unsigned mask = 0;
+  const float top0 = g.top;
+#pragma unroll
+  for (int j = 0; j < kGroup; ++j) {
+    const float4 c = g.stage[j];
+    const float d2 = dist2(g.qx, g.qy, g.qz, c.x, c.y, c.z);
+    mask |= (d2 < top0) ? (1u << j) : 0u;
+  }
+  if (!g.valid) mask = 0;
+
+  // phase 2: only lanes with survivors loop, only over their survivors
+  while (mask) {
+    const int j = __ffs(mask) - 1;
+    mask &= mask - 1;
+    const float4 c = g.stage[j];
+    const float d2 = dist2(g.qx, g.qy, g.qz, c.x, c.y, c.z);
+    if (d2 < g.top) {
+      g.top = heap_replace_padded(g.heap, g.kp, d2);
+      ++g.n_inserts;
+    }
+  }
+  __syncwarp();
+  g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
+  ++g.n_leaves;
+}
+
+// Exact per-query test against the leaf box; skip the leaf if no lane can improve.
+__device__ __forceinline__ void maybe_leaf(const TreeView& t, int leaf, float lx, float ly, float lz,
+                                           float hx, float hy, float hz, int cnt, GroupCtx& g) {
+  const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
+  if (__any_sync(kFullMask, g.valid && (lb < g.top))) process_leaf(t, leaf, cnt, g);
+}
+
+// ---- traversal ------------------------------------------------------------------------------------
+// One loop, two sources of "next node", one leaf call site:
+//   * FRAMES (depth >= 0): depth-first, nearest child first, explicit frame stack in shared memory
+//     (level, base, count, todo mask); boxes are re-loaded when control returns to a frame. Used (a) for
+//     the SEED phase — the 32 leaves of the level-1 node the group lives in (or the nearest one, for a
+//     group visiting a foreign tree) are swept first so that the radius is tight before anything is
+//     put on the frontier — and (b) when the frontier overflows (any visiting order is exact).
+//   * FRONTIER: best-first over (lower bound, node) entries of all levels, seed node excluded.
+__device__ __forceinline__ unsigned full_mask_of(int count) {
+  return count >= 32 ? 0xffffffffu : ((1u << count) - 1u);
+}
+
+__device__ __forceinline__ void push_frame(unsigned* fr, int depth, int level, int base, int count) {
+  fr[depth * 4 + 0] = (unsigned)level;
+  fr[depth * 4 + 1] = (unsigned)base;
+  fr[depth * 4 + 2] = (unsigned)count;
+  fr[depth * 4 + 3] = full_mask_of(count);
+}
+
+// Greedy descent to the level-1 node nearest to the group box (-1 if the tree has no level 1).
+__device__ __forceinline__ int find_seed_l1(const TreeView& t, const GroupCtx& g) {
+  if (t.levels < 2) return -1;
+  const int lane = lane_id();
+  int base = 0, count = t.count[t.levels - 1];
+  for (int L = t.levels - 1;; --L) {
+    float key = INFINITY;
+    if (lane < count) {
+      const float4* bp = reinterpret_cast<const float4*>(t.boxes[L]) + 2 * (size_t)(base + lane);
+      const float4 a = __ldg(bp), b = __ldg(bp + 1);
+      key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
+    }
+    const unsigned kb = __float_as_uint(key);
+    const unsigned m = __reduce_min_sync(kFullMask, kb);
+    const int child = base + __ffs(__ballot_sync(kFullMask, kb == m)) - 1;
+    if (L == 1) return child;
+    base = child * kFanout;
+    const int rem = t.count[L - 1] - base;
+    count = rem < kFanout ? rem : kFanout;
+  }
+}
+
+// Push the children [base, base+count) of `level` that lie inside the group radius. On overflow
+// (after purging stale entries) the children are handed to the frame stack instead.
+__device__ __forceinline__ void frontier_expand(const TreeView& t, int level, int base, int count, int seed_l1,
+                                                int& qcount, int& depth, GroupCtx& g) {
+  const int lane = lane_id();
+  const bool have = lane < count;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+  if (have) {
+    const float4* bp = reinterpret_cast<const float4*>(t.boxes[level]) + 2 * (size_t)(base + lane);
+    a = __ldg(bp);
+    b = __ldg(bp + 1);
+  }
+  const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
+  const bool pass = have && (key < g.maxR2) && !(level == 1 && base + lane == seed_l1);
+  const unsigned mask = __ballot_sync(kFullMask, pass);
+  const int np = __popc(mask);
+  if (np == 0) return;
+  const unsigned lt = (1u << lane) - 1u;
+  if (qcount + np > kQueueCap) {
+    // purge entries that the shrinking radius has made irrelevant (in-place, order-preserving)
+    const unsigned maxbits = __float_as_uint(g.maxR2);
+    int kept = 0;
+    for (int s0 = 0; s0 < qcount; s0 += 32) {
+      const int s = s0 + lane;
+      const bool in = s < qcount;
+      const unsigned kx = in ? g.qkey[s] : 0xffffffffu;
+      const unsigned nd = in ? g.qnode[s] : 0u;
+      const bool keep = in && (kx < maxbits);
+      const unsigned km = __ballot_sync(kFullMask, keep);
+      __syncwarp();
+      if (keep) {
+        const int pos = kept + __popc(km & lt);
+        g.qkey[pos] = kx;
+        g.qnode[pos] = nd;
+      }
+      kept += __popc(km);
+      __syncwarp();
+    }
+    qcount = kept;
+    ++g.n_purge;
+  }
+  if (qcount + np > kQueueCap) {
+    ++g.n_fallback;
+    depth = 0;
+    if (lane == 0) push_frame(g.frames, 0, level, base, count);
+    __syncwarp();
+    return;
+  }
+  if (pass) {
+    const int pos = qcount + __popc(mask & lt);
+    g.qkey[pos] = __float_as_uint(key);
+    g.qnode[pos] = ((unsigned)level << kNodeIdxBits) | (unsigned)(base + lane);
+  }
+  qcount += np;
+  __syncwarp();
+}
+
+__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1) {
+  const int lane = lane_id();
+  unsigned* fr = g.frames;
+  const int top_level = t.levels - 1;
+  int depth = -1, qcount = 0;
+  bool started = false;
+  if (seed_l1 >= 0) {
+    const int rem = t.count[0] - seed_l1 * kFanout;
+    if (lane == 0) push_frame(fr, 0, 0, seed_l1 * kFanout, rem < kFanout ? rem : kFanout);
+    depth = 0;
+    __syncwarp();
+  }
+  for (;;) {
+    int leaf, cnt;
+    float lx, ly, lz, hx, hy, hz;
+    if (depth >= 0) {
+      // ---- frame step
+      const int L = (int)fr[depth * 4 + 0], B = (int)fr[depth * 4 + 1], Cn = (int)fr[depth * 4 + 2];
+      const unsigned todo_in = fr[depth * 4 + 3];
+      const bool have = lane < Cn;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+      if (have) {
+        const float4* bp = reinterpret_cast<const float4*>(t.boxes[L]) + 2 * (size_t)(B + lane);
+        a = __ldg(bp);
+        b = __ldg(bp + 1);
+      }
+      const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
+      const bool pass = have && ((todo_in >> lane) & 1u) && (key < g.maxR2) &&
+                        !(L == 1 && B + lane == seed_l1);
+      const unsigned pm = __ballot_sync(kFullMask, pass);
+      if (pm == 0u) { --depth; continue; }
+      const unsigned kb = pass ? __float_as_uint(key) : 0xffffffffu;
+      const unsigned m = __reduce_min_sync(kFullMask, kb);
+      const int who = __ffs(__ballot_sync(kFullMask, kb == m)) - 1;
+      const int child = B + who;
+      __syncwarp();
+      if (lane == 0) fr[depth * 4 + 3] = pm & ~(1u << who);
+      if (L != 0) {
+        ++g.n_inner;
+        ++depth;
+        const int rem = t.count[L - 1] - child * kFanout;
+        if (lane == 0) push_frame(fr, depth, L - 1, child * kFanout, rem < kFanout ? rem : kFanout);
+        __syncwarp();
+        continue;
+      }
+      __syncwarp();
+      leaf = child;
+      lx = __shfl_sync(kFullMask, a.x, who); ly = __shfl_sync(kFullMask, a.y, who);
+      lz = __shfl_sync(kFullMask, a.z, who); hx = __shfl_sync(kFullMask, b.x, who);
+      hy = __shfl_sync(kFullMask, b.y, who); hz = __shfl_sync(kFullMask, b.z, who);
+      cnt = __float_as_int(__shfl_sync(kFullMask, a.w, who));
+    } else {
+      // ---- frontier step
+      if (!started) {
+        started = true;
+        frontier_expand(t, top_level, 0, t.count[top_level], seed_l1, qcount, depth, g);
+        continue;
+      }
+      if (qcount == 0) break;
+      unsigned best = 0xffffffffu;
+      int bslot = 0;
+      for (int s = lane; s < qcount; s += 32) {
+        const unsigned kx = g.qkey[s];
+        if (kx < best) { best = kx; bslot = s; }
+      }
+      const unsigned m = __reduce_min_sync(kFullMask, best);
+      if (m >= __float_as_uint(g.maxR2)) break;          // nothing left inside the group radius
+      const int wl = __ffs(__ballot_sync(kFullMask, best == m)) - 1;
+      const int slot = __shfl_sync(kFullMask, bslot, wl);
+      const unsigned node = g.qnode[slot];
+      __syncwarp();
+      if (lane == 0) {
+        g.qkey[slot] = g.qkey[qcount - 1];
+        g.qnode[slot] = g.qnode[qcount - 1];
+      }
+      --qcount;
+      __syncwarp();
+      const int level = (int)(node >> kNodeIdxBits);
+      const int idx = (int)(node & ((1u << kNodeIdxBits) - 1u));
+      if (level != 0) {
+        ++g.n_inner;
+        const int rem = t.count[level - 1] - idx * kFanout;
+        frontier_expand(t, level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, seed_l1, qcount, depth, g);
+        continue;
+      }
+      const float4* bp = reinterpret_cast<const float4*>(t.boxes[0]) + 2 * (size_t)idx;
+      const float4 a = __ldg(bp), b = __ldg(bp + 1);
+      leaf = idx;
+      lx = a.x; ly = a.y; lz = a.z; hx = b.x; hy = b.y; hz = b.z;
+      cnt = __float_as_int(a.w);
+    }
+    maybe_leaf(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
+  }
+}
+
+// Carve one warp's slice of dynamic shared memory.
+__device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int warp, int lane, int k) {
+  const int kp = heap_padded(k);
+  float* warp_base = smem + warp * warp_smem_floats(k);
+  g.heap = warp_base + lane;
+  g.stage = reinterpret_cast<float4*>(warp_base + (size_t)kp * 32);
+  g.qkey = reinterpret_cast<unsigned*>(warp_base + (size_t)kp * 32 + 128);
+  g.qnode = g.qkey + kQueueCap;
+  g.frames = g.qnode + kQueueCap;
+  g.kp = kp;
+  g.n_leaves = g.n_inner = g.n_inserts = g.n_fallback = g.n_purge = 0;
+}
+
+// Group bounding box + group radius from the lanes' queries and heap tops.
+__device__ __forceinline__ void group_bounds(GroupCtx& g) {
+  float lx = g.valid ? g.qx : INFINITY, ly = g.valid ? g.qy : INFINITY, lz = g.valid ? g.qz : INFINITY;
+  float hx = g.valid ? g.qx : -INFINITY, hy = g.valid ? g.qy : -INFINITY, hz = g.valid ? g.qz : -INFINITY;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lx = fminf(lx, __shfl_xor_sync(kFullMask, lx, o));
+    ly = fminf(ly, __shfl_xor_sync(kFullMask, ly, o));
+    lz = fminf(lz, __shfl_xor_sync(kFullMask, lz, o));
+    hx = fmaxf(hx, __shfl_xor_sync(kFullMask, hx, o));
+    hy = fmaxf(hy, __shfl_xor_sync(kFullMask, hy, o));
+    hz = fmaxf(hz, __shfl_xor_sync(kFullMask, hz, o));
+  }
+  g.glx = lx; g.gly = ly; g.glz = lz; g.ghx = hx; g.ghy = hy; g.ghz = hz;
+  g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
+}
+
+__device__ __forceinline__ void flush_stats(const GroupCtx& g, unsigned long long* stats) {
+  if (stats == nullptr) return;
+  unsigned ins = g.n_inserts;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ins += __shfl_xor_sync(kFullMask, ins, o);
+  if (lane_id() == 0) {
+    atomicAdd(stats + 0, (unsigned long long)g.n_leaves);
+    atomicAdd(stats + 1, (unsigned long long)g.n_leaves * kGroup);
+    atomicAdd(stats + 2, (unsigned long long)ins);
+    atomicAdd(stats + 3, (unsigned long long)g.n_inner);
+    atomicAdd(stats + 4, (unsigned long long)g.n_fallback);
+    atomicAdd(stats + 5, (unsigned long long)g.n_purge);
+  }
+}
+
+constexpr size_t kSmemPerSM = 233472;     // 228 KB
+constexpr size_t kSmemPerCtaMax = 232448; // 227 KB
+constexpr size_t kSmemCtaReserve = 1024;
+
+}  // namespace
+
+// Launch shape of any kernel built on GroupCtx: warps per CTA and dynamic shared memory bytes.
+size_t group_smem_bytes(int k, int warps_per_cta);
+int group_pick_warps(int k, const void* kernel);
+
+}  // namespace b200knn

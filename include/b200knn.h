@@ -41,6 +41,10 @@ uint64_t b200knn_launch_count(void);
  * sizes are computed on the host). */
 int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
                          void* stream, b200knn_index** out);
+/* Same, from x,y,z,w records (16 bytes per point) whose w holds the point's uint32 id as raw bits —
+ * the layout redistributed points arrive in. */
+int b200knn_index_create_xyzw(const float* d_xyzw, int64_t n, uint32_t id_offset, void* stream,
+                              b200knn_index** out);
 void b200knn_index_destroy(b200knn_index* idx);
 int64_t b200knn_index_num_points(const b200knn_index* idx);
 int b200knn_index_num_levels(const b200knn_index* idx);
@@ -106,6 +110,54 @@ typedef struct b200knn_step_args {
 int b200knn_run_steps(b200knn_index* idx, const b200knn_step_args* args, void* stream);
 /* out[id - id_offset] = sorted_result[i] for the index's own points (undo the spatial order). */
 int b200knn_index_unsort(b200knn_index* idx, const float* d_sorted_result, float* d_out, void* stream);
+
+/* ---- distributed driver ------------------------------------------------------------------------
+ * The body of the reference's two main() functions, minus file I/O: every rank calls dist_knn with
+ * the points it holds and gets the k-th-neighbour distance over the UNION of all ranks' points.
+ *
+ * The library never talks to a launcher or a network itself. The caller supplies a bootstrap: two
+ * blocking host-side collectives over small buffers (torch.distributed in Python, the unix-socket
+ * rendezvous of apps/knnrun in C++). They are used for set-up (CUDA IPC handles, boxes, counts) and
+ * as round fences; all bulk data moves by kernels over NVLink-mapped peer memory.
+ * Role of MPI_Init/Allgather/Allreduce/Barrier in the reference
+ * (/root/reference/prePartitionedDataVariant.cu:254-319). */
+typedef struct b200knn_bootstrap {
+  void* ctx;
+  int rank, world;
+  /* recv holds world * bytes_per_rank bytes, in rank order. Return 0 on success. */
+  int (*allgather)(void* ctx, const void* send, void* recv, int64_t bytes_per_rank);
+  int (*barrier)(void* ctx);
+} b200knn_bootstrap;
+
+typedef struct b200knn_dist b200knn_dist;
+
+enum {
+  B200KNN_MODE_RING = 0,            /* all-pairs fused ring; any input (unorderedDataVariant.cu:173-205) */
+  B200KNN_MODE_PREPARTITIONED = 1,  /* keep points where they are; bbox-culled per-group exchange
+                                       (prePartitionedDataVariant.cu:304-357) */
+  B200KNN_MODE_REDISTRIBUTE = 2     /* scatter points to spatial owners first, then as mode 1, then
+                                       return results to the reading rank (no counterpart in the
+                                       reference; makes unordered input scale with GPU count) */
+};
+
+typedef struct b200knn_dist_report {
+  double ms_total, ms_redistribute, ms_build, ms_query, ms_return;   /* host wall clock, this rank */
+  int64_t pending_groups;           /* home groups that had to visit at least one other rank */
+  int64_t points_after_redistribute;
+  int32_t chunks, rounds;
+} b200knn_dist_report;
+
+/* Collective over all ranks of the bootstrap. The engine keeps a symmetric, IPC-mapped heap that
+ * grows on demand and is reused across dist_knn calls. */
+int b200knn_dist_create(const b200knn_bootstrap* bs, b200knn_dist** out);
+void b200knn_dist_destroy(b200knn_dist* d);
+int64_t b200knn_dist_heap_bytes(const b200knn_dist* d);
+/* d_out[i] = k-th-neighbour distance of local point i. `global_begin` = index of local point 0 in the
+ * global order (mode 2 only: ranks must hold consecutive slices, as the reference's file split does).
+ * groups_per_chunk = 0 picks the default. Synchronous: returns when d_out is complete. */
+int b200knn_dist_knn(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64_t global_begin, int k,
+                     float max_radius, int mode, int groups_per_chunk, float* d_out, void* stream,
+                     b200knn_dist_report* report_or_null);
 
 /* ---- CPU side (no GPU needed): oracle and mirror engine ----------------------------------------
  * cpu_bruteforce: exact O(nq*n) k-th distance with the canonical fp32 expression

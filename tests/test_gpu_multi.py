@@ -24,3 +24,9 @@ def test_fused_and_baseline_ring_match_oracle():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun("mp_ring_worker.py", n)
     assert out.returncode == 0 and "MP_RING_OK" in out.stdout, out.stdout[-4000:]
+
+
+def test_distributed_driver_all_modes_match_oracle():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun("mp_dist_worker.py", n)
+    assert out.returncode == 0 and "MP_DIST_OK" in out.stdout, out.stdout[-4000:]
