@@ -98,6 +98,8 @@ def main() -> int:
     ap.add_argument("--k", type=int, default=BASELINE_K)
     ap.add_argument("--transport", default="fused", choices=["fused", "nccl"],
                     help="multi-GPU ring transport: in-kernel NVLink hand-off (product) or NCCL send/recv (baseline)")
+    ap.add_argument("--mode", default="auto", choices=["auto", "redistribute", "ring", "prepartitioned"],
+                    help="multi-GPU strategy (auto = redistribute: scatter to spatial owners + bbox-culled exchange)")
     ap.add_argument("--chunk-groups", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -120,11 +122,12 @@ def main() -> int:
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
 
     from mpi_cuda_largescaleknn_b200.ops._lib import lib
     from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
-    from mpi_cuda_largescaleknn_b200.parallel.ring import FusedRing, NcclRingBaseline
+    from mpi_cuda_largescaleknn_b200.parallel.dist import DistKnn
+    from mpi_cuda_largescaleknn_b200.parallel.ring import NcclRingBaseline
     from mpi_cuda_largescaleknn_b200.utils.generators import torch_uniform
 
     N, k = args.n, args.k
@@ -139,17 +142,20 @@ def main() -> int:
             dist.barrier()
             torch.cuda.synchronize()
 
+    mode = "redistribute" if args.mode == "auto" else args.mode
+    engine = DistKnn() if world > 1 else None
+
     def one_step(points):
-        idx = KnnIndex(points, id_offset=0)
         if world == 1:
+            idx = KnnIndex(points, id_offset=0)
             idx.knn_self(k, out=out_dev)
+            idx.close()
+        elif mode == "ring" and args.transport == "nccl":
+            idx = KnnIndex(points, id_offset=0)
+            NcclRingBaseline(idx, k, groups_per_chunk=args.chunk_groups).run(out=out_dev)
+            idx.close()
         else:
-            cls = FusedRing if args.transport == "fused" else NcclRingBaseline
-            ring = cls(idx, k, groups_per_chunk=args.chunk_groups)
-            ring.run(out=out_dev)
-            if hasattr(ring, "close"):
-                ring.close()
-        idx.close()
+            engine.knn(points, k, mode=mode, global_begin=begin, groups_per_chunk=args.chunk_groups, out=out_dev)
 
     def timed(fn, steps):
         """K steps bracketed by barrier+sync, CUDA events on the launching stream, max over ranks."""
@@ -206,7 +212,8 @@ def main() -> int:
             "dtype": "fp32", "data": "synthetic uniform-random float3 in the unit cube, generated on device",
             "impl": "ours",
             "config": {"model": "unorderedDataVariant", "n_points": N, "k": k, "global_batch": N, "seq_len": k,
-                       "parallelism": ("single" if world == 1 else f"ring{world}-{args.transport}"),
+                       "parallelism": ("single" if world == 1 else
+                                       (f"ring{world}-{args.transport}" if mode == "ring" else f"{mode}{world}")),
                        "step": "index build + all-kNN + k-th distance extraction",
                        "l2": "inputs (>= 3 GB at the headline size) exceed the 126 MB L2; no explicit flush"},
             "clocks": clocks, "gpu_launches": launches // max(1, args.steps) * args.steps,
@@ -214,8 +221,11 @@ def main() -> int:
         }
         if e2e is not None:
             line["e2e"] = e2e
+        if engine is not None and engine.last_report:
+            line["report_rank0"] = engine.last_report
         print(json.dumps(line), flush=True)
     if world > 1:
+        engine.close()
         dist.barrier()
         dist.destroy_process_group()
     return 0
