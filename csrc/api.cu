@@ -62,6 +62,23 @@ struct b200knn_ring {
   unsigned seq_base = 1;
 };
 
+namespace b200knn {
+// Stream-ordered allocations are served from the device's default pool; keep freed blocks cached
+// instead of returning them to the driver at every synchronisation (index build/destroy per kNN
+// call would otherwise pay a multi-GB cudaMalloc/cudaFree each time).
+void keep_pool_memory(int device) {
+  static std::atomic<unsigned> done{0};
+  const unsigned bit = 1u << (device & 31);
+  if (done.load() & bit) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    unsigned long long keep = ~0ull;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  }
+  done.fetch_or(bit);
+}
+}  // namespace b200knn
+
 extern "C" {
 
 const char* b200knn_last_error(void) { return last_error_cstr(); }
@@ -89,12 +106,14 @@ static int index_create_impl(const float* d_xyz, int stride, int64_t n, const ui
   *out = idx;
   idx->n = n;
   idx->id_offset = id_offset;
+  idx->stream = stream;
   KNN_CUDA_TRY(cudaGetDevice(&idx->device));
+  keep_pool_memory(idx->device);
   KNN_CUDA_TRY(cudaDeviceGetAttribute(&idx->num_sms, cudaDevAttrMultiProcessorCount, idx->device));
-  KNN_CUDA_TRY(cudaMalloc(&idx->d_bounds_ord, 6 * sizeof(unsigned)));
-  KNN_CUDA_TRY(cudaMalloc(&idx->d_bounds6, 6 * sizeof(float)));
-  KNN_CUDA_TRY(cudaMalloc(&idx->task_counter, sizeof(unsigned long long)));
-  KNN_CUDA_TRY(cudaMalloc(&idx->stats, 8 * sizeof(unsigned long long)));
+  KNN_CUDA_TRY(cudaMallocAsync(&idx->d_bounds_ord, 6 * sizeof(unsigned), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&idx->d_bounds6, 6 * sizeof(float), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&idx->task_counter, sizeof(unsigned long long), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&idx->stats, 8 * sizeof(unsigned long long), stream));
   KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
   int rc;
   if ((rc = bounds_init(idx->d_bounds_ord, stream))) return rc;
@@ -107,15 +126,15 @@ static int index_create_impl(const float* d_xyz, int stride, int64_t n, const ui
   }
   const int64_t groups = idx->groups();
   const int64_t padded = groups * kGroup;
-  KNN_CUDA_TRY(cudaMalloc(&idx->pts, padded * sizeof(Float4)));
-  KNN_CUDA_TRY(cudaMalloc(&idx->result_sorted, padded * sizeof(float)));
+  KNN_CUDA_TRY(cudaMallocAsync(&idx->pts, padded * sizeof(Float4), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&idx->result_sorted, padded * sizeof(float), stream));
   // level sizes
   int cnt = (int)groups;
   int levels = 0;
   for (;;) {
     KNN_REQUIRE(levels < kMaxLevels, "index_create: too many tree levels");
     idx->count[levels] = cnt;
-    KNN_CUDA_TRY(cudaMalloc(&idx->boxes[levels], (size_t)cnt * sizeof(Box)));
+    KNN_CUDA_TRY(cudaMallocAsync(&idx->boxes[levels], (size_t)cnt * sizeof(Box), stream));
     ++levels;
     if (cnt <= kFanout) break;
     cnt = (int)div_up(cnt, kFanout);
@@ -150,13 +169,14 @@ static int index_create_impl(const float* d_xyz, int stride, int64_t n, const ui
 
 void b200knn_index_destroy(b200knn_index* idx) {
   if (!idx) return;
-  cudaFree(idx->pts);
-  for (int l = 0; l < kMaxLevels; ++l) cudaFree(idx->boxes[l]);
-  cudaFree(idx->d_bounds_ord);
-  cudaFree(idx->d_bounds6);
-  cudaFree(idx->result_sorted);
-  cudaFree(idx->task_counter);
-  cudaFree(idx->stats);
+  cudaStreamSynchronize(idx->stream);   // buffers go back to the pool only after their last use
+  if (idx->pts) cudaFreeAsync(idx->pts, idx->stream);
+  for (int l = 0; l < kMaxLevels; ++l) if (idx->boxes[l]) cudaFreeAsync(idx->boxes[l], idx->stream);
+  if (idx->d_bounds_ord) cudaFreeAsync(idx->d_bounds_ord, idx->stream);
+  if (idx->d_bounds6) cudaFreeAsync(idx->d_bounds6, idx->stream);
+  if (idx->result_sorted) cudaFreeAsync(idx->result_sorted, idx->stream);
+  if (idx->task_counter) cudaFreeAsync(idx->task_counter, idx->stream);
+  if (idx->stats) cudaFreeAsync(idx->stats, idx->stream);
   delete idx;
 }
 

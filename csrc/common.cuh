@@ -12,6 +12,7 @@ namespace b200knn {
 
 void set_last_error(const std::string& msg);   // api.cpp
 const char* last_error_cstr();
+void keep_pool_memory(int device);               // api.cu: raise the default mempool release threshold
 void note_launch();                             // api.cu: counts kernel launches (bench evidence)
 
 #define KNN_CUDA_TRY(expr)                                                               \

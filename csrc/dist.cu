@@ -107,10 +107,11 @@ size_t pv_heap_need(int k, int Gc) {
 
 struct PvPlan { int Gc; int C; int64_t max_groups; };
 
-PvPlan pv_plan(int64_t max_n, int groups_per_chunk) {
+PvPlan pv_plan(int64_t max_n, int k, int groups_per_chunk) {
   PvPlan pl;
   pl.max_groups = div_up(max_n > 0 ? max_n : 1, kGroup);
-  int64_t Gc = groups_per_chunk > 0 ? groups_per_chunk : 131072;
+  // default: as many home groups per chunk as a 32 GB slot budget (pending + inbox) allows
+  int64_t Gc = groups_per_chunk > 0 ? groups_per_chunk : (int64_t)((16ull << 30) / pv_slot_bytes(k));
   if (Gc > pl.max_groups) Gc = pl.max_groups;
   pl.Gc = (int)Gc;
   pl.C = (int)div_up(pl.max_groups, Gc);
@@ -164,18 +165,23 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     int64_t gc = my_groups - p.group_begin;
     gc = gc < 0 ? 0 : (gc > pl.Gc ? pl.Gc : gc);
     p.group_count = (int)gc;
+    const double tl0 = now_ms();
     if ((rc = pv_main_launch(p, p.group_count, idx->num_sms, stream))) return rc;
     if (R == 1) continue;
     // any work for the exchange at all? (one tiny allgather per chunk saves 2(R-1) fences when not)
     int my_pending = 0;
     KNN_CUDA_TRY(cudaMemcpyAsync(&my_pending, p.pending_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
     KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    const double tl1 = now_ms();
+    if (rep) rep->ms_local_phase += tl1 - tl0;
     std::vector<int> all_pending(R);
     if (d->allgather(&my_pending, all_pending.data(), sizeof(int))) { set_last_error("bootstrap allgather failed"); return -3; }
     int64_t total_pending = 0;
     for (int v : all_pending) total_pending += v;
     if (rep) { rep->pending_groups += my_pending; rep->chunks += 1; }
+    if (rep) rep->ms_host_collectives += now_ms() - tl1;
     if (total_pending == 0) continue;
+    const double tr0 = now_ms();
     for (int j = 1; j < R; ++j) {
       const int dst = (me + j) % R, src = (me - j + R) % R;
       if ((rc = pv_push_launch(p.pending, p.pending_count, k, &boxes[(size_t)dst * 6], d->peer[dst] + off_inbox,
@@ -191,6 +197,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
       if (rep) rep->rounds += 1;
     }
     if ((rc = pv_final_launch(p.pending, p.pending_count, k, idx->result_sorted, idx->num_sms, stream))) return rc;
+    if (rep) rep->ms_rounds += now_ms() - tr0;
   }
   return 0;
 }
@@ -204,7 +211,7 @@ int knn_prepartitioned(b200knn_dist* d, const float* d_xyz, int64_t n_local, int
     if (d->allgather(&n_local, all.data(), sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
     for (int64_t v : all) max_n = std::max(max_n, v);
   }
-  const PvPlan pl = pv_plan(max_n, groups_per_chunk);
+  const PvPlan pl = pv_plan(max_n, k, groups_per_chunk);
   if ((rc = ensure_heap(d, pv_heap_need(k, pl.Gc)))) return rc;
   d->bump = 0;
   const double t0 = now_ms();
@@ -305,7 +312,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   KNN_REQUIRE(max_recv < (int64_t)0x7fffffff - 64, "redistribute: a rank would receive more than 2^31 points");
 
   // ---- symmetric heap: receive buffer + result landing zone + exchange slots
-  const PvPlan pl = pv_plan(max_recv, groups_per_chunk);
+  const PvPlan pl = pv_plan(max_recv, k, groups_per_chunk);
   const size_t need = align256((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4)) +
                       align256((size_t)std::max<int64_t>(max_local, 1) * sizeof(float)) + pv_heap_need(k, pl.Gc);
   if ((rc = ensure_heap(d, need))) return rc;
@@ -434,6 +441,7 @@ int b200knn_dist_create(const b200knn_bootstrap* bs, b200knn_dist** out) {
   d->rank = bs->rank;
   d->world = bs->world;
   KNN_CUDA_TRY(cudaGetDevice(&d->device));
+  keep_pool_memory(d->device);
   KNN_CUDA_TRY(cudaDeviceGetAttribute(&d->num_sms, cudaDevAttrMultiProcessorCount, d->device));
   KNN_CUDA_TRY(cudaMalloc(&d->task_counter, sizeof(unsigned long long)));
   return 0;

@@ -21,6 +21,7 @@ struct b200knn_index {
   unsigned long long* task_counter = nullptr;
   unsigned long long* stats = nullptr;     // [4]
   bool stats_on = false;
+  cudaStream_t stream = 0;                 // stream the buffers were allocated on / last used on
 
   TreeView view() const {
     TreeView t;

@@ -145,6 +145,7 @@ typedef struct b200knn_dist_report {
   int64_t pending_groups;           /* home groups that had to visit at least one other rank */
   int64_t points_after_redistribute;
   int32_t chunks, rounds;
+  double ms_local_phase, ms_host_collectives, ms_rounds;   /* breakdown of ms_query in modes 1 and 2 */
 } b200knn_dist_report;
 
 /* Collective over all ranks of the bootstrap. The engine keeps a symmetric, IPC-mapped heap that

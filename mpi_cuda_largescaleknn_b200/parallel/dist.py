@@ -37,7 +37,8 @@ class Bootstrap(C.Structure):
 class DistReport(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_redistribute", C.c_double), ("ms_build", C.c_double),
                 ("ms_query", C.c_double), ("ms_return", C.c_double), ("pending_groups", C.c_int64),
-                ("points_after_redistribute", C.c_int64), ("chunks", C.c_int32), ("rounds", C.c_int32)]
+                ("points_after_redistribute", C.c_int64), ("chunks", C.c_int32), ("rounds", C.c_int32),
+                ("ms_local_phase", C.c_double), ("ms_host_collectives", C.c_double), ("ms_rounds", C.c_double)]
 
     def as_dict(self) -> dict:
         return {name: getattr(self, name) for name, _ in self._fields_}
