@@ -123,9 +123,26 @@ PvPlan pv_plan(int64_t max_n, int k, int groups_per_chunk) {
 int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const PvPlan& pl, cudaStream_t stream,
            b200knn_dist_report* rep) {
   const int R = d->world, me = d->rank;
-  // everyone's box
-  std::vector<float> boxes((size_t)R * 6);
-  if (d->allgather(idx->h_bounds, boxes.data(), 6 * sizeof(float))) { set_last_error("bootstrap allgather failed"); return -3; }
+  // everyone's region: the (<= 32) top-level boxes of its tree. One box per rank is too coarse: a
+  // few stray points at the end of a Morton range can stretch it across a neighbour's whole region.
+  struct Region { int32_t count; int32_t pad[7]; Box boxes[kFanout]; };
+  std::vector<Region> regions(R);
+  {
+    Region mine;
+    memset(&mine, 0, sizeof(mine));
+    if (idx->levels > 0) {
+      mine.count = idx->count[idx->levels - 1];
+      KNN_CUDA_TRY(cudaMemcpyAsync(mine.boxes, idx->boxes[idx->levels - 1], (size_t)mine.count * sizeof(Box),
+                                   cudaMemcpyDeviceToHost, stream));
+      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    }
+    if (d->allgather(&mine, regions.data(), sizeof(Region))) { set_last_error("bootstrap allgather failed"); return -3; }
+  }
+  Box* d_regions = nullptr;
+  KNN_CUDA_TRY(cudaMallocAsync(&d_regions, (size_t)R * kFanout * sizeof(Box), stream));
+  for (int r = 0; r < R; ++r)
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_regions + (size_t)r * kFanout, regions[r].boxes, kFanout * sizeof(Box),
+                                 cudaMemcpyHostToDevice, stream));
 
   const size_t slot = pv_slot_bytes(k);
   const size_t off_pending = d->alloc((size_t)pl.Gc * slot);
@@ -142,7 +159,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.sentinel = sentinel_d2(max_radius);
   p.R = R;
   p.rank = me;
-  for (int r = 0; r < R; ++r) for (int a = 0; a < 6; ++a) p.boxes[r][a] = boxes[(size_t)r * 6 + a];
+  p.region_boxes = d_regions;
+  for (int r = 0; r < R; ++r) p.region_count[r] = regions[r].count;
   p.home_queries = idx->pts;
   p.home_n = idx->n;
   p.home_is_tree = 1;
@@ -184,7 +202,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     const double tr0 = now_ms();
     for (int j = 1; j < R; ++j) {
       const int dst = (me + j) % R, src = (me - j + R) % R;
-      if ((rc = pv_push_launch(p.pending, p.pending_count, k, &boxes[(size_t)dst * 6], d->peer[dst] + off_inbox,
+      if ((rc = pv_push_launch(p.pending, p.pending_count, k, d_regions + (size_t)dst * kFanout, regions[dst].count,
+                               d->peer[dst] + off_inbox,
                                out_count, idx->num_sms, stream))) return rc;
       if ((rc = pv_publish_launch(out_count, reinterpret_cast<int*>(d->peer[dst] + off_icount), stream))) return rc;
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
@@ -199,6 +218,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     if ((rc = pv_final_launch(p.pending, p.pending_count, k, idx->result_sorted, idx->num_sms, stream))) return rc;
     if (rep) rep->ms_rounds += now_ms() - tr0;
   }
+  KNN_CUDA_TRY(cudaFreeAsync(d_regions, stream));
   return 0;
 }
 
@@ -288,7 +308,25 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   if (d->allgather(my_samples.data(), all_samples.data(), S * sizeof(uint64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
   std::sort(all_samples.begin(), all_samples.end());
   uint64_t split[B200KNN_MAX_RANKS] = {};
-  for (int j = 1; j < R; ++j) split[j - 1] = all_samples[(size_t)j * S];
+  // Splitter j = the j/R quantile of the pooled samples, snapped to the coarsest Morton-cell
+  // boundary inside a +-0.5 % window around it. A boundary that is a whole-cell boundary keeps every
+  // rank's region a union of whole cells, so a few stray points at the end of a range cannot inflate
+  // a rank's bounding box across a neighbouring rank's region (which would defeat the culling).
+  {
+    const size_t total_s = (size_t)S * R;
+    const size_t w = std::max<size_t>(1, total_s / 200);
+    for (int j = 1; j < R; ++j) {
+      const size_t q = (size_t)j * S;
+      const uint64_t lo = all_samples[q > w ? q - w : 0];
+      const uint64_t hi = all_samples[std::min(total_s - 1, q + w)];
+      uint64_t best = all_samples[q];
+      for (int b = 63; b >= 0; --b) {
+        const uint64_t cand = (hi >> b) << b;
+        if (cand >= lo && cand > 0) { best = cand; break; }
+      }
+      split[j - 1] = best;
+    }
+  }
   std::vector<int64_t> cut(R + 1, 0);
   if (R > 1) {
     KNN_CUDA_TRY(cudaMemcpyAsync(d_split, split, (R - 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));

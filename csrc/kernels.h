@@ -100,7 +100,8 @@ struct PvMainParams {
   float sentinel;
   int phase;                   // 0 = LOCAL (home groups, fresh heaps), 1 = SERVE (visiting groups from the inbox)
   int R, rank;
-  float boxes[kMaxRanks][6];   // every rank's bounding box (lo xyz, hi xyz)
+  const Box* region_boxes;     // [R][32]: every rank's region = the top-level boxes of its tree
+  int region_count[kMaxRanks]; // boxes in use per rank (0 for an empty rank)
   // LOCAL
   const Float4* home_queries;
   int64_t home_n;
@@ -118,8 +119,8 @@ struct PvMainParams {
   unsigned long long* stats;
 };
 int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream);
-int pv_push_launch(const char* pending, const int* pending_count, int k, const float* box6, char* peer_inbox,
-                   int* out_count, int num_sms, cudaStream_t stream);
+int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, int dst_box_count,
+                   char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
 int pv_publish_launch(const int* out_count, int* peer_inbox_count, cudaStream_t stream);
 int pv_final_launch(const char* pending, const int* pending_count, int k, float* result_sorted, int num_sms,
                     cudaStream_t stream);

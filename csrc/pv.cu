@@ -96,15 +96,18 @@ pv_main_kernel(const PvMainParams p) {
     if (p.phase == 0) {
       if (cnt > 0) {
         if (g.valid) p.result_sorted[home_group * kGroup + lane] = finalize_kth(g.top);
-        // does any lane's ball still reach another rank's box?
+        // does the group's ball still reach another rank's region? lane = one of that rank's boxes
+        group_bounds(g);
         bool need = false;
         for (int s = 0; s < p.R; ++s) {
           if (s == p.rank) continue;
-          const float lb = point_box_lb(g.qx, g.qy, g.qz, p.boxes[s][0], p.boxes[s][1], p.boxes[s][2],
-                                        p.boxes[s][3], p.boxes[s][4], p.boxes[s][5]);
-          need = need || (lb < g.top);
+          if (lane < p.region_count[s]) {
+            const float4* bp = reinterpret_cast<const float4*>(p.region_boxes + (size_t)s * kFanout + lane);
+            const float4 a = __ldg(bp), b = __ldg(bp + 1);
+            need = need || (box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z) < g.maxR2);
+          }
         }
-        if (__any_sync(kFullMask, g.valid && need)) {
+        if (__any_sync(kFullMask, need)) {
           int slot_idx = 0;
           if (lane == 0) slot_idx = atomicAdd(p.pending_count, 1);
           slot_idx = __shfl_sync(kFullMask, slot_idx, 0);
@@ -131,23 +134,43 @@ pv_main_kernel(const PvMainParams p) {
   flush_stats(g, p.stats);
 }
 
-// One warp per pending slot: if any lane's ball reaches the destination box, copy the whole slot
-// into the next free slot of the destination GPU's inbox.
+// One warp per pending slot: if the group's ball reaches any box of the destination's region, copy
+// the whole slot into the next free slot of the destination GPU's inbox.
 __global__ void __launch_bounds__(256)
 pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending_count, int k,
-               float blx, float bly, float blz, float bhx, float bhy, float bhz,
+               const Box* __restrict__ dst_boxes, int dst_box_count,
                char* __restrict__ peer_inbox, int* __restrict__ out_count) {
   const int lane = lane_id();
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const size_t slot_bytes = pv_slot_bytes(k);
   const int total = *pending_count;
+  float4 ba = make_float4(0.f, 0.f, 0.f, 0.f), bb = ba;
+  if (lane < dst_box_count) {
+    const float4* bp = reinterpret_cast<const float4*>(dst_boxes + lane);
+    ba = __ldg(bp);
+    bb = __ldg(bp + 1);
+  }
   for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < total; s += warps) {
     const char* slot = pending + (size_t)s * slot_bytes;
     const int cnt = slot_meta(slot, k)[1];
     const float4 q = slot_pos(slot, k)[lane];
+    const bool valid = lane < cnt;
+    float lx = valid ? q.x : INFINITY, ly = valid ? q.y : INFINITY, lz = valid ? q.z : INFINITY;
+    float hx = valid ? q.x : -INFINITY, hy = valid ? q.y : -INFINITY, hz = valid ? q.z : -INFINITY;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lx = fminf(lx, __shfl_xor_sync(kFullMask, lx, o));
+      ly = fminf(ly, __shfl_xor_sync(kFullMask, ly, o));
+      lz = fminf(lz, __shfl_xor_sync(kFullMask, lz, o));
+      hx = fmaxf(hx, __shfl_xor_sync(kFullMask, hx, o));
+      hy = fmaxf(hy, __shfl_xor_sync(kFullMask, hy, o));
+      hz = fmaxf(hz, __shfl_xor_sync(kFullMask, hz, o));
+    }
     const float top = slot_heap(slot)[lane];
-    const float lb = point_box_lb(q.x, q.y, q.z, blx, bly, blz, bhx, bhy, bhz);
-    if (!__any_sync(kFullMask, lane < cnt && lb < top)) continue;
+    const float maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, valid ? __float_as_uint(top) : 0u));
+    const bool hit = lane < dst_box_count &&
+                     box_box_lb(lx, ly, lz, hx, hy, hz, ba.x, ba.y, ba.z, bb.x, bb.y, bb.z) < maxR2;
+    if (!__any_sync(kFullMask, hit)) continue;
     int o = 0;
     if (lane == 0) o = atomicAdd(out_count, 1);
     o = __shfl_sync(kFullMask, o, 0);
@@ -261,11 +284,11 @@ int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream
   return 0;
 }
 
-int pv_push_launch(const char* pending, const int* pending_count, int k, const float* box6, char* peer_inbox,
-                   int* out_count, int num_sms, cudaStream_t stream) {
+int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, int dst_box_count,
+                   char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream) {
   KNN_CUDA_TRY(cudaMemsetAsync(out_count, 0, sizeof(int), stream));
-  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, box6[0], box6[1], box6[2], box6[3],
-                                                 box6[4], box6[5], peer_inbox, out_count);
+  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, dst_boxes, dst_box_count,
+                                                 peer_inbox, out_count);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;
