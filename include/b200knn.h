@@ -64,6 +64,23 @@ int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, 
  * Synchronises `stream` (temporary buffers). */
 int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, int k, float max_radius,
                       float* d_out, void* stream);
+/* knn_self_noalloc: same result as index_create + knn_self for n <= B200KNN_NOALLOC_MAX_POINTS, but
+ * the library allocates nothing: the sorted points, the box tree, the sort buffers and the counters
+ * all live in one fixed device array inside the library (about 11.9 MB per GPU that loads it, held
+ * until exit). Meant for callers that may not allocate device memory once they are running — a host
+ * application that has handed the whole GPU to its own arena, a loop that cannot tolerate the
+ * device-wide stalls cudaMalloc/cudaFree can cause, a plug-in whose host forbids allocator calls
+ * after start-up. The caller passes its own input and output buffers. Larger n is an error. The
+ * first call on a device resolves the array's address (cudaGetSymbolAddress), so make that call
+ * before starting any stream capture. All calls share the array and it keeps the previous call's
+ * contents; whatever must start at zero is cleared by each call, and calls whose GPU work overlaps
+ * (two streams, two threads) race — keep them on one stream. Enqueues on `stream` and returns.
+ * (No counterpart in the reference.) */
+#define B200KNN_NOALLOC_MAX_POINTS 262144
+int b200knn_knn_self_noalloc(const float* d_xyz, int64_t n, int k, float max_radius, float* d_out,
+                             void* stream);
+int64_t b200knn_noalloc_max_points(void);
+int64_t b200knn_noalloc_scratch_bytes(void);
 /* Traversal counters of the most recent query call on this index (synchronous):
  * [0] leaves visited by groups, [1] candidate distance evaluations per lane, [2] heap insertions,
  * [3] inner nodes opened, [4] frontier overflows handled depth-first, [5] frontier purges. Role of CUKD_ENABLE_STATS (cukd/common.h:349-361). */
