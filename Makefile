@@ -35,3 +35,25 @@ clean:
 	rm -rf $(BUILD)
 
 .PHONY: all lib clean
+
+# ---- executables (same names and command lines as the reference's) ----
+APPS := $(BUILD)/knnrun $(BUILD)/cudaMpiKNN_unorderedData $(BUILD)/cudaMpiKNN_prePartitionedData
+APPFLAGS := -O2 -std=c++17 -Iinclude -Xcompiler -ffp-contract=off
+
+apps: $(APPS)
+all: apps
+
+$(BUILD)/knnrun: apps/knnrun.cpp
+	@mkdir -p $(BUILD)
+	$(CXX) -O2 -std=c++17 $< -o $@
+
+$(BUILD)/backend.o: apps/backend.cpp apps/knn_apps.hpp include/b200knn.h
+	$(NVCC) $(APPFLAGS) -x cu $(ARCH) -c $< -o $@
+
+$(BUILD)/cudaMpiKNN_unorderedData: apps/unordered.cpp $(BUILD)/backend.o $(LIB) apps/knn_apps.hpp
+	$(NVCC) $(APPFLAGS) $(ARCH) $< $(BUILD)/backend.o -o $@ -L$(BUILD) -lb200knn -Xlinker -rpath,'$$ORIGIN'
+
+$(BUILD)/cudaMpiKNN_prePartitionedData: apps/prepartitioned.cpp $(BUILD)/backend.o $(LIB) apps/knn_apps.hpp
+	$(NVCC) $(APPFLAGS) $(ARCH) $< $(BUILD)/backend.o -o $@ -L$(BUILD) -lb200knn -Xlinker -rpath,'$$ORIGIN'
+
+.PHONY: apps
