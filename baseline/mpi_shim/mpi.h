@@ -1,7 +1,8 @@
 /* mpi.h — minimal stand-in for the ten MPI calls the reference uses, so that the
  * UNMODIFIED reference sources build and run on an image without any MPI installation.
- * Transport: eager messages as files in a shared-memory directory ($SHIM_DIR, /dev/shm); device
- * buffers are staged through the host. This is baseline plumbing only — nothing in b200knn uses it. */
+ * Transport: device buffers by CUDA IPC rendezvous (one device-to-device copy, as a CUDA-aware MPI
+ * would do); small host buffers as files in $SHIM_DIR (/dev/shm). Baseline plumbing only — nothing
+ * in b200knn uses it. */
 #ifndef B200KNN_MPI_SHIM_H
 #define B200KNN_MPI_SHIM_H
 #ifdef __cplusplus

@@ -4,7 +4,8 @@ JSON line with "impl": "reference". None of this repository's kernels or engine 
 
 How the reference is run
   * no MPI on the image -> ranks are plain processes; baseline/mpi_shim provides the ten MPI calls
-    (eager messages through files in /dev/shm, device buffers staged through the host).
+    (device buffers by CUDA IPC rendezvous = one device-to-device copy over NVLink, as a CUDA-aware
+    MPI would do; tiny host messages through files in /dev/shm).
   * the unmodified reference needs pointsPerRank * k < 2^31 (int overflow), so the
     number of reference ranks is the smallest multiple of the GPU count that satisfies it, spread with
     the reference's own -g flag (rank % gpus). If those ranks' candidate heaps (n*k*8 bytes each) do
