@@ -1,0 +1,115 @@
+#!/usr/bin/env python
+"""Run the BASELINE.json configurations 3, 4 and 5 (and 2 for reference) on all visible GPUs.
+
+    torchrun --nnodes=1 --nproc-per-node=8 --master-addr 127.0.0.1 tools/run_configs.py [--scale 1.0] [--only 3,4,5]
+
+Data is generated on the device per rank (no files at this size); each config reports the device
+time of one full step (index build + queries + extraction, max over ranks), queries/s, the rank-0
+phase report and the spread of per-rank local-phase times (load imbalance)."""
+import argparse, json, math, os, sys
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+import torch
+import torch.distributed as dist
+from mpi_cuda_largescaleknn_b200.parallel.dist import DistKnn
+
+
+def blob(n, centre, sigma, dev, seed):
+    g = torch.Generator(device=dev); g.manual_seed(seed)
+    return torch.randn((n, 3), generator=g, device=dev) * sigma + torch.tensor(centre, device=dev)
+
+
+def clustered_surface(n, dev, seed, clusters=64):
+    """Half in tight power-law-sized clusters (sigma 10^-3.5..10^-1.5), half on a sphere surface."""
+    g = torch.Generator(device=dev); g.manual_seed(seed)
+    gc = torch.Generator(device="cpu"); gc.manual_seed(1234)          # cluster table identical on all ranks
+    w = torch.distributions.Pareto(torch.tensor(1.0), torch.tensor(1.2)).sample((clusters,)) - 1.0 + 0.05
+    torch.manual_seed(1234)
+    w = (torch.rand(clusters, generator=gc) ** (-1 / 1.2)) - 1.0 + 0.05
+    centres = torch.rand((clusters, 3), generator=gc)
+    sig = 10 ** (torch.rand(clusters, generator=gc) * 2.0 - 3.5)
+    n_cl = n // 2
+    which = torch.multinomial(w / w.sum(), n_cl, replacement=True, generator=gc).to(dev)
+    pts_c = centres.to(dev)[which] + torch.randn((n_cl, 3), generator=g, device=dev) * sig.to(dev)[which][:, None]
+    m = n - n_cl
+    v = torch.randn((m, 3), generator=g, device=dev)
+    v = v / v.norm(dim=1, keepdim=True)
+    pts_s = 0.5 + 0.45 * v + torch.randn((m, 3), generator=g, device=dev) * 1e-4
+    return torch.cat([pts_c, pts_s])[torch.randperm(n, generator=g, device=dev)].contiguous()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--only", default="3,4,5")
+    ap.add_argument("--steps", type=int, default=2)
+    a = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
+    eng = DistKnn()
+    side = max(1, round(world ** (1 / 3)))
+    while side ** 3 < world:
+        side += 1
+    centres = [(float(i), float(j), float(l)) for i in range(side) for j in range(side) for l in range(side)][:world]
+
+    def run(name, pts, k, mode, begin):
+        out = torch.empty(pts.shape[0], device=dev)
+        times = []
+        for it in range(1 + a.steps):
+            torch.cuda.synchronize()
+            if world > 1: dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            eng.knn(pts, k, mode=mode, global_begin=begin, out=out)
+            e1.record(); torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+            if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            if it > 0: times.append(float(t.item()))
+        rep = eng.last_report
+        lp = torch.tensor([rep["ms_local_phase"], rep["ms_query"], float(rep["pending_groups"]), float(pts.shape[0])],
+                          dtype=torch.float64, device=dev)
+        allp = [torch.zeros_like(lp) for _ in range(world)]
+        if world > 1: dist.all_gather(allp, lp)
+        else: allp = [lp]
+        n_total = int(sum(float(x[3]) for x in allp))
+        ms = sum(times) / len(times)
+        finite = bool(torch.isfinite(out).all().item()) if pts.shape[0] else True
+        if rank == 0:
+            print(json.dumps({"config": name, "n_total": n_total, "k": k, "mode": mode, "gpus": world, "ms_per_step": ms,
+                              "queries_per_s": n_total / ms * 1e3, "all_finite": finite,
+                              "local_phase_ms_per_rank": [round(float(x[0]), 1) for x in allp],
+                              "pending_groups_per_rank": [int(x[2]) for x in allp],
+                              "heap_bytes": eng.heap_bytes, "report_rank0": rep}), flush=True)
+        del out
+
+    only = set(a.only.split(","))
+    if "3" in only:
+        n = int(64 * 1024 * 1024 * a.scale)
+        sigma = 0.5 / 2.128   # P(|x-c| > 0.5 on one axis) ~ 3.3 % -> ~10 % of a blob beyond its cell
+        run("3: prePartitioned, %d files x %d Gaussian-blob points, ~10%% overlap" % (world, n),
+            blob(n, centres[rank], sigma, dev, 100 + rank), 100, "prepartitioned", 0)
+    if "4" in only:
+        N = int(1_000_000_000 * a.scale)
+        b, e = N * rank // world, N * (rank + 1) // world
+        g = torch.Generator(device=dev); g.manual_seed(200 + rank)
+        run("4: unordered, %d uniform float3" % N, torch.rand((e - b, 3), generator=g, device=dev), 100, "redistribute", b)
+    if "5" in only:
+        N = int(512 * 1024 * 1024 * a.scale)
+        b, e = N * rank // world, N * (rank + 1) // world
+        run("5: unordered, %d clustered/surface points" % N, clustered_surface(e - b, dev, 300 + rank), 32, "redistribute", b)
+    if "2" in only:
+        N = int(256 * 1024 * 1024 * a.scale)
+        b, e = N * rank // world, N * (rank + 1) // world
+        g = torch.Generator(device=dev); g.manual_seed(1234 + rank)
+        run("2: unordered, %d uniform float3" % N, torch.rand((e - b, 3), generator=g, device=dev), 100, "redistribute", b)
+    eng.close()
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
