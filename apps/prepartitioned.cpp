@@ -23,9 +23,10 @@ int main(int ac, char** av) {
     std::vector<float> result;
     if (gpu_available()) {
       select_gpu(bs, o);
-      const int mode = o.mode >= 0 ? o.mode : B200KNN_MODE_PREPARTITIONED;
-      // ring needs no global order; redistribute is meaningless for per-rank files -> culled exchange
-      result = run_gpu(bs, pts, 0, o, mode == B200KNN_MODE_REDISTRIBUTE ? B200KNN_MODE_PREPARTITIONED : mode);
+      // default: in place when the files' boxes are (nearly) disjoint, else redistribute the union
+      // (--in-place / --redistribute / --ring force a strategy)
+      const int mode = o.mode >= 0 ? o.mode : B200KNN_MODE_AUTO;
+      result = run_gpu(bs, pts, 0, o, mode == B200KNN_MODE_REDISTRIBUTE ? B200KNN_MODE_AUTO : mode);
     } else {
       result = run_cpu(bs, pts, o);
     }

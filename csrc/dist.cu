@@ -123,26 +123,33 @@ PvPlan pv_plan(int64_t max_n, int k, int groups_per_chunk) {
 int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const PvPlan& pl, cudaStream_t stream,
            b200knn_dist_report* rep) {
   const int R = d->world, me = d->rank;
-  // everyone's region: the (<= 32) top-level boxes of its tree. One box per rank is too coarse: a
-  // few stray points at the end of a Morton range can stretch it across a neighbour's whole region.
-  struct Region { int32_t count; int32_t pad[7]; Box boxes[kFanout]; };
-  std::vector<Region> regions(R);
+  // everyone's region: the boxes of the deepest tree level with at most kRegionBoxes nodes, plus the
+  // overall box for a quick reject. One box per rank is far too coarse: a few stray points at the end
+  // of a Morton range, or the tails of a Gaussian blob, stretch it across the neighbours' regions.
+  struct RegionHead { int32_t count; int32_t pad; float box[6]; };
+  const size_t region_bytes = sizeof(RegionHead) + (size_t)kRegionBoxes * sizeof(Box);
+  std::vector<char> my_region(region_bytes, 0), all_regions(region_bytes * R);
   {
-    Region mine;
-    memset(&mine, 0, sizeof(mine));
+    RegionHead* head = reinterpret_cast<RegionHead*>(my_region.data());
+    memcpy(head->box, idx->h_bounds, sizeof(head->box));
     if (idx->levels > 0) {
-      mine.count = idx->count[idx->levels - 1];
-      KNN_CUDA_TRY(cudaMemcpyAsync(mine.boxes, idx->boxes[idx->levels - 1], (size_t)mine.count * sizeof(Box),
+      int lr = 0;
+      while (idx->count[lr] > kRegionBoxes) ++lr;
+      head->count = idx->count[lr];
+      KNN_CUDA_TRY(cudaMemcpyAsync(my_region.data() + sizeof(RegionHead), idx->boxes[lr], (size_t)head->count * sizeof(Box),
                                    cudaMemcpyDeviceToHost, stream));
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
     }
-    if (d->allgather(&mine, regions.data(), sizeof(Region))) { set_last_error("bootstrap allgather failed"); return -3; }
+    if (d->allgather(my_region.data(), all_regions.data(), (int64_t)region_bytes)) { set_last_error("bootstrap allgather failed"); return -3; }
   }
   Box* d_regions = nullptr;
-  KNN_CUDA_TRY(cudaMallocAsync(&d_regions, (size_t)R * kFanout * sizeof(Box), stream));
-  for (int r = 0; r < R; ++r)
-    KNN_CUDA_TRY(cudaMemcpyAsync(d_regions + (size_t)r * kFanout, regions[r].boxes, kFanout * sizeof(Box),
-                                 cudaMemcpyHostToDevice, stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&d_regions, (size_t)R * kRegionBoxes * sizeof(Box), stream));
+  std::vector<RegionHead> heads(R);
+  for (int r = 0; r < R; ++r) {
+    memcpy(&heads[r], all_regions.data() + (size_t)r * region_bytes, sizeof(RegionHead));
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_regions + (size_t)r * kRegionBoxes, all_regions.data() + (size_t)r * region_bytes + sizeof(RegionHead),
+                                 (size_t)kRegionBoxes * sizeof(Box), cudaMemcpyHostToDevice, stream));
+  }
 
   const size_t slot = pv_slot_bytes(k);
   const size_t off_pending = d->alloc((size_t)pl.Gc * slot);
@@ -160,7 +167,10 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.R = R;
   p.rank = me;
   p.region_boxes = d_regions;
-  for (int r = 0; r < R; ++r) p.region_count[r] = regions[r].count;
+  for (int r = 0; r < R; ++r) {
+    p.region_count[r] = heads[r].count;
+    for (int a = 0; a < 6; ++a) p.rank_box[r][a] = heads[r].box[a];
+  }
   p.home_queries = idx->pts;
   p.home_n = idx->n;
   p.home_is_tree = 1;
@@ -202,8 +212,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     const double tr0 = now_ms();
     for (int j = 1; j < R; ++j) {
       const int dst = (me + j) % R, src = (me - j + R) % R;
-      if ((rc = pv_push_launch(p.pending, p.pending_count, k, d_regions + (size_t)dst * kFanout, regions[dst].count,
-                               d->peer[dst] + off_inbox,
+      if ((rc = pv_push_launch(p.pending, p.pending_count, k, d_regions + (size_t)dst * kRegionBoxes, heads[dst].count,
+                               heads[dst].box, d->peer[dst] + off_inbox,
                                out_count, idx->num_sms, stream))) return rc;
       if ((rc = pv_publish_launch(out_count, reinterpret_cast<int*>(d->peer[dst] + off_icount), stream))) return rc;
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
@@ -352,11 +362,11 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   // ---- symmetric heap: receive buffer + result landing zone + exchange slots
   const PvPlan pl = pv_plan(max_recv, k, groups_per_chunk);
   const size_t need = align256((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4)) +
-                      align256((size_t)std::max<int64_t>(max_local, 1) * sizeof(float)) + pv_heap_need(k, pl.Gc);
+                      align256((size_t)std::max<int64_t>(max_local, 1) * 8) + pv_heap_need(k, pl.Gc);
   if ((rc = ensure_heap(d, need))) return rc;
   d->bump = 0;
   const size_t off_recv = d->alloc((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4));
-  const size_t off_out = d->alloc((size_t)std::max<int64_t>(max_local, 1) * sizeof(float));
+  const size_t off_out = d->alloc((size_t)std::max<int64_t>(max_local, 1) * 8);   // (id, value) pairs land here
 
   RedistributeParams rp;
   memset(&rp, 0, sizeof(rp));
@@ -394,20 +404,55 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   if (!rc) rc = run_pv(d, idx, k, max_radius, pl, stream, rep);
   const double t3 = now_ms();
 
-  // ---- results go back to the rank that read the point
+  // ---- results go back to the rank that read the point: sort (id, value) by id, push each owner's
+  // run as contiguous pairs into its staging area, owner scatters locally into d_out
   if (!rc) {
-    ReturnParams q;
-    memset(&q, 0, sizeof(q));
-    q.pts = idx->pts;
-    q.result_sorted = idx->result_sorted;
-    q.n = idx->n;
-    q.R = R;
-    for (int r = 0; r < R; ++r) {
-      q.begin[r] = info[r].begin;
-      q.out[r] = reinterpret_cast<float*>(d->peer[r] + off_out);
+    const int64_t m = idx->n, ma = m > 0 ? m : 1;
+    uint32_t *ids = nullptr, *ids_tmp = nullptr, *vals2 = nullptr, *vals2_tmp = nullptr, *scratch2 = nullptr;
+    int64_t *d_begins = nullptr, *d_cut2 = nullptr;
+    KNN_CUDA_TRY(cudaMallocAsync(&ids, ma * sizeof(uint32_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&ids_tmp, ma * sizeof(uint32_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&vals2, ma * sizeof(uint32_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&vals2_tmp, ma * sizeof(uint32_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&scratch2, radix_sort_scratch_bytes(ma), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&d_begins, (B200KNN_MAX_RANKS + 1) * sizeof(int64_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&d_cut2, (B200KNN_MAX_RANKS + 1) * sizeof(int64_t), stream));
+    if ((rc = extract_pairs_launch(idx->pts, idx->result_sorted, m, ids, vals2, stream))) return rc;
+    int in_tmp2 = 0;
+    if ((rc = radix_sort_u32(ids, vals2, ids_tmp, vals2_tmp, scratch2, m, 0, 32, stream, &in_tmp2))) return rc;
+    const uint32_t* sids = in_tmp2 ? ids_tmp : ids;
+    const uint32_t* svals = in_tmp2 ? vals2_tmp : vals2;
+    std::vector<int64_t> begins(R + 1), cut2(R + 1, 0);
+    for (int r = 0; r < R; ++r) begins[r] = info[r].begin;
+    begins[R] = info[R - 1].begin + info[R - 1].n;
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_begins, begins.data(), (R + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+    if ((rc = lower_bounds32_launch(sids, m, d_begins, R + 1, d_cut2, stream))) return rc;
+    KNN_CUDA_TRY(cudaMemcpyAsync(cut2.data(), d_cut2, (R + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
+    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    std::vector<int64_t> send2(R), M2((size_t)R * R);
+    for (int r = 0; r < R; ++r) send2[r] = cut2[r + 1] - cut2[r];
+    if (d->allgather(send2.data(), M2.data(), R * sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
+    PushPairsParams pp;
+    memset(&pp, 0, sizeof(pp));
+    pp.ids = sids;
+    pp.vals = svals;
+    pp.n = m;
+    pp.R = R;
+    for (int r = 0; r <= R; ++r) pp.cut[r] = cut2[r];
+    for (int o = 0; o < R; ++o) {
+      pp.dst[o] = reinterpret_cast<uint2*>(d->peer[o] + off_out);
+      int64_t off = 0;
+      for (int s2 = 0; s2 < me; ++s2) off += M2[(size_t)s2 * R + o];
+      pp.dst_offset[o] = off;
     }
-    q.begin[R] = info[R - 1].begin + info[R - 1].n;
-    rc = return_results_launch(q, stream);
+    if ((rc = push_pairs_launch(pp, stream))) return rc;
+    KNN_CUDA_TRY(cudaFreeAsync(ids, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(ids_tmp, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(vals2, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(vals2_tmp, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(scratch2, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(d_begins, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(d_cut2, stream));
   }
   if (!rc) {
     cudaError_t e = cudaStreamSynchronize(stream);
@@ -415,9 +460,11 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   }
   if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
   if (!rc && n_local > 0) {
-    cudaError_t e = cudaMemcpyAsync(d_out, d->base + off_out, (size_t)n_local * sizeof(float), cudaMemcpyDeviceToDevice, stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-    if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
+    rc = scatter_pairs_launch(d->base + off_out, n_local, global_begin, d_out, stream);
+    if (!rc) {
+      cudaError_t e = cudaStreamSynchronize(stream);
+      if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
+    }
   }
   // nobody may start overwriting the landing zone (next call) before everyone has copied out
   if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
@@ -516,6 +563,48 @@ int b200knn_dist_knn(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     case B200KNN_MODE_REDISTRIBUTE:
       rc = knn_redistribute(d, d_xyz, n_local, global_begin, k, max_radius, groups_per_chunk, d_out, stream, report);
       break;
+    case B200KNN_MODE_AUTO: {
+      // Per-rank inputs: keep the points in place when the ranks' boxes are (nearly) disjoint, otherwise
+      // treat the concatenation of the inputs as one unordered cloud and redistribute. Box culling cannot
+      // separate clouds that interpenetrate (e.g. Gaussian blobs with overlapping tails): every group
+      // would visit every rank, which costs far more than one all-to-all of the points.
+      struct Info { int64_t n; float box[6]; };
+      Info mine{};
+      mine.n = n_local;
+      unsigned* d_bord = nullptr;
+      float* d_box6 = nullptr;
+      KNN_CUDA_TRY(cudaMallocAsync(&d_bord, 6 * sizeof(unsigned), stream));
+      KNN_CUDA_TRY(cudaMallocAsync(&d_box6, 6 * sizeof(float), stream));
+      if ((rc = bounds_init(d_bord, stream))) return rc;
+      if ((rc = bounds_accumulate(d_xyz, 3, n_local, d_bord, stream))) return rc;
+      if ((rc = bounds_decode(d_bord, d_box6, stream))) return rc;
+      KNN_CUDA_TRY(cudaMemcpyAsync(mine.box, d_box6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+      KNN_CUDA_TRY(cudaFreeAsync(d_bord, stream));
+      KNN_CUDA_TRY(cudaFreeAsync(d_box6, stream));
+      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      std::vector<Info> info(d->world);
+      if (d->allgather(&mine, info.data(), sizeof(Info))) { set_last_error("bootstrap allgather failed"); return -3; }
+      double worst = 0.0;
+      int64_t begin = 0;
+      for (int a = 0; a < d->world; ++a) {
+        if (a < d->rank) begin += info[a].n;
+        if (info[a].n == 0) continue;
+        double va = 1.0;
+        for (int c = 0; c < 3; ++c) va *= std::max(1e-30, (double)info[a].box[3 + c] - info[a].box[c]);
+        for (int b = 0; b < d->world; ++b) {
+          if (b == a || info[b].n == 0) continue;
+          double vi = 1.0;
+          for (int c = 0; c < 3; ++c)
+            vi *= std::max(0.0, (double)std::min(info[a].box[3 + c], info[b].box[3 + c]) - std::max(info[a].box[c], info[b].box[c]));
+          worst = std::max(worst, vi / va);
+        }
+      }
+      const bool in_place = worst < 0.02;
+      if (report) report->auto_chose_redistribute = in_place ? 0 : 1;
+      rc = in_place ? knn_prepartitioned(d, d_xyz, n_local, k, max_radius, groups_per_chunk, d_out, stream, report)
+                    : knn_redistribute(d, d_xyz, n_local, begin, k, max_radius, groups_per_chunk, d_out, stream, report);
+      break;
+    }
     default:
       set_last_error("dist_knn: unknown mode");
       rc = -2;

@@ -91,6 +91,7 @@ int ring_pick_warps_per_cta(int k);
 int ring_launch(const RingParams& p, int num_sms, cudaStream_t stream);
 
 // ---------------- culled exchange / redistribution (pv.cu) ----------------
+constexpr int kRegionBoxes = 2048;
 // A slot carries one group: heap [k][32] floats, positions [32] float4, meta [4] int32.
 KNN_HD size_t pv_slot_bytes(int k) { return (size_t)k * 128 + 512 + 16; }
 
@@ -100,8 +101,10 @@ struct PvMainParams {
   float sentinel;
   int phase;                   // 0 = LOCAL (home groups, fresh heaps), 1 = SERVE (visiting groups from the inbox)
   int R, rank;
-  const Box* region_boxes;     // [R][32]: every rank's region = the top-level boxes of its tree
+  const Box* region_boxes;     // [R][kRegionBoxes]: every rank's region = the boxes of the deepest tree
+                               // level that has at most kRegionBoxes nodes
   int region_count[kMaxRanks]; // boxes in use per rank (0 for an empty rank)
+  float rank_box[kMaxRanks][6];// every rank's overall bounding box (quick reject)
   // LOCAL
   const Float4* home_queries;
   int64_t home_n;
@@ -120,7 +123,7 @@ struct PvMainParams {
 };
 int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream);
 int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, int dst_box_count,
-                   char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
+                   const float* dst_rank_box6, char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
 int pv_publish_launch(const int* out_count, int* peer_inbox_count, cudaStream_t stream);
 int pv_final_launch(const char* pending, const int* pending_count, int k, float* result_sorted, int num_sms,
                     cudaStream_t stream);
@@ -137,15 +140,21 @@ struct RedistributeParams {
 };
 int redistribute_launch(const RedistributeParams& p, cudaStream_t stream);
 
-struct ReturnParams {
-  const Float4* pts;           // local sorted points, .w = global id
-  const float* result_sorted;
+struct PushPairsParams {
+  const uint32_t* ids;         // local results sorted by global id
+  const uint32_t* vals;        // float bits
   int64_t n;
   int R;
-  int64_t begin[kMaxRanks + 1];     // rank o originally read global ids [begin[o], begin[o+1])
-  float* out[kMaxRanks];       // owners' output arrays (peer pointers)
+  int64_t cut[kMaxRanks + 1];  // owner o takes sorted positions [cut[o], cut[o+1])
+  uint2* dst[kMaxRanks];       // owners' staging areas (peer pointers)
+  int64_t dst_offset[kMaxRanks];    // where this rank's run starts inside dst[o]
 };
-int return_results_launch(const ReturnParams& p, cudaStream_t stream);
+int extract_pairs_launch(const Float4* pts, const float* res, int64_t n, uint32_t* ids, uint32_t* vals,
+                         cudaStream_t stream);
+int lower_bounds32_launch(const uint32_t* sorted_ids, int64_t n, const int64_t* d_begins, int count, int64_t* out,
+                          cudaStream_t stream);
+int push_pairs_launch(const PushPairsParams& p, cudaStream_t stream);
+int scatter_pairs_launch(const void* pairs, int64_t n, int64_t begin, float* out, cudaStream_t stream);
 int sample_keys_launch(const uint64_t* sorted_keys, int64_t n, int samples, uint64_t* out, cudaStream_t stream);
 int lower_bounds_launch(const uint64_t* sorted_keys, int64_t n, const uint64_t* splitters, int count,
                         int64_t* out, cudaStream_t stream);

@@ -16,9 +16,9 @@
 // Rounds are separated by a host barrier (see dist.cu); all data movement is done by these kernels
 // over NVLink-mapped peer memory, never by a collective library.
 //
-// redistribute / return_results: the all-to-all scatter of points to their spatial owner and of the
-// results back to the rank that read the point — both as in-kernel peer stores (new capability;
-// the reference never redistributes).
+// redistribute / push_pairs: the all-to-all scatter of points to their spatial owner and of the
+// results back to the rank that read the point — both as contiguous in-kernel peer stores (new
+// capability; the reference never redistributes).
 #include "traverse.cuh"
 
 namespace b200knn {
@@ -99,15 +99,35 @@ pv_main_kernel(const PvMainParams p) {
         // does the group's ball still reach another rank's region? lane = one of that rank's boxes
         group_bounds(g);
         bool need = false;
-        for (int s = 0; s < p.R; ++s) {
+        for (int s = 0; s < p.R && !need; ++s) {
           if (s == p.rank) continue;
-          if (lane < p.region_count[s]) {
-            const float4* bp = reinterpret_cast<const float4*>(p.region_boxes + (size_t)s * kFanout + lane);
-            const float4 a = __ldg(bp), b = __ldg(bp + 1);
-            need = need || (box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z) < g.maxR2);
+          // quick reject against the rank's overall box (warp-uniform)
+          if (!(box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, p.rank_box[s][0], p.rank_box[s][1],
+                           p.rank_box[s][2], p.rank_box[s][3], p.rank_box[s][4], p.rank_box[s][5]) < g.maxR2))
+            continue;
+          const Box* rb = p.region_boxes + (size_t)s * kRegionBoxes;
+          for (int base = 0; base < p.region_count[s] && !need; base += 32) {
+            bool hit = false;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+            if (base + lane < p.region_count[s]) {
+              const float4* bp = reinterpret_cast<const float4*>(rb + base + lane);
+              a = __ldg(bp);
+              b = __ldg(bp + 1);
+              hit = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z) < g.maxR2;
+            }
+            // group-level hits are refined per query: lane = query, one candidate box at a time
+            unsigned hm = __ballot_sync(kFullMask, hit);
+            while (hm != 0u && !need) {
+              const int bi = __ffs(hm) - 1;
+              hm &= hm - 1;
+              const float lb = point_box_lb(g.qx, g.qy, g.qz, __shfl_sync(kFullMask, a.x, bi), __shfl_sync(kFullMask, a.y, bi),
+                                            __shfl_sync(kFullMask, a.z, bi), __shfl_sync(kFullMask, b.x, bi),
+                                            __shfl_sync(kFullMask, b.y, bi), __shfl_sync(kFullMask, b.z, bi));
+              need = __any_sync(kFullMask, g.valid && (lb < g.top));
+            }
           }
         }
-        if (__any_sync(kFullMask, need)) {
+        if (need) {
           int slot_idx = 0;
           if (lane == 0) slot_idx = atomicAdd(p.pending_count, 1);
           slot_idx = __shfl_sync(kFullMask, slot_idx, 0);
@@ -139,17 +159,12 @@ pv_main_kernel(const PvMainParams p) {
 __global__ void __launch_bounds__(256)
 pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending_count, int k,
                const Box* __restrict__ dst_boxes, int dst_box_count,
+               float rlx, float rly, float rlz, float rhx, float rhy, float rhz,
                char* __restrict__ peer_inbox, int* __restrict__ out_count) {
   const int lane = lane_id();
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const size_t slot_bytes = pv_slot_bytes(k);
   const int total = *pending_count;
-  float4 ba = make_float4(0.f, 0.f, 0.f, 0.f), bb = ba;
-  if (lane < dst_box_count) {
-    const float4* bp = reinterpret_cast<const float4*>(dst_boxes + lane);
-    ba = __ldg(bp);
-    bb = __ldg(bp + 1);
-  }
   for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < total; s += warps) {
     const char* slot = pending + (size_t)s * slot_bytes;
     const int cnt = slot_meta(slot, k)[1];
@@ -168,9 +183,28 @@ pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending
     }
     const float top = slot_heap(slot)[lane];
     const float maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, valid ? __float_as_uint(top) : 0u));
-    const bool hit = lane < dst_box_count &&
-                     box_box_lb(lx, ly, lz, hx, hy, hz, ba.x, ba.y, ba.z, bb.x, bb.y, bb.z) < maxR2;
-    if (!__any_sync(kFullMask, hit)) continue;
+    if (!(box_box_lb(lx, ly, lz, hx, hy, hz, rlx, rly, rlz, rhx, rhy, rhz) < maxR2)) continue;   // overall box
+    bool need = false;
+    for (int base = 0; base < dst_box_count && !need; base += 32) {
+      bool hit = false;
+      float4 ba = make_float4(0.f, 0.f, 0.f, 0.f), bb = ba;
+      if (base + lane < dst_box_count) {
+        const float4* bp = reinterpret_cast<const float4*>(dst_boxes + base + lane);
+        ba = __ldg(bp);
+        bb = __ldg(bp + 1);
+        hit = box_box_lb(lx, ly, lz, hx, hy, hz, ba.x, ba.y, ba.z, bb.x, bb.y, bb.z) < maxR2;
+      }
+      unsigned hm = __ballot_sync(kFullMask, hit);
+      while (hm != 0u && !need) {
+        const int bi = __ffs(hm) - 1;
+        hm &= hm - 1;
+        const float lb = point_box_lb(q.x, q.y, q.z, __shfl_sync(kFullMask, ba.x, bi), __shfl_sync(kFullMask, ba.y, bi),
+                                      __shfl_sync(kFullMask, ba.z, bi), __shfl_sync(kFullMask, bb.x, bi),
+                                      __shfl_sync(kFullMask, bb.y, bi), __shfl_sync(kFullMask, bb.z, bi));
+        need = __any_sync(kFullMask, valid && (lb < top));
+      }
+    }
+    if (!need) continue;
     int o = 0;
     if (lane == 0) o = atomicAdd(out_count, 1);
     o = __shfl_sync(kFullMask, o, 0);
@@ -228,15 +262,48 @@ redistribute_kernel(const RedistributeParams p) {
   reinterpret_cast<float4*>(p.recv[d])[p.recv_offset[d] + (i - p.cut[d])] = v;
 }
 
-// result of sorted point i goes to the rank that originally read the point: out[owner][id - begin].
+// ---- result return ------------------------------------------------------------------------------
+// Results are (global id, value) pairs. Scattering them one by one into the owners' arrays is 4-byte
+// random peer stores (measured: 1.0 s for 125 M results per GPU). Instead: sort the pairs by id (the
+// owners' id ranges are contiguous, so each owner's share becomes one run), push every run as
+// contiguous 8-byte pairs into the owner's staging area, and let the owner scatter locally.
 __global__ void __launch_bounds__(256)
-return_results_kernel(const ReturnParams p) {
+extract_pairs_kernel(const Float4* __restrict__ pts, const float* __restrict__ res, int64_t n,
+                     uint32_t* __restrict__ ids, uint32_t* __restrict__ vals) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  ids[i] = __float_as_uint(pts[i].w);
+  vals[i] = __float_as_uint(res[i]);
+}
+
+__global__ void lower_bounds32_kernel(const uint32_t* __restrict__ sorted_ids, int64_t n,
+                                      const int64_t* __restrict__ begins, int count, int64_t* __restrict__ out) {
+  const int j = threadIdx.x;
+  if (j >= count) return;
+  const int64_t s = begins[j];
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if ((int64_t)sorted_ids[mid] < s) lo = mid + 1; else hi = mid;
+  }
+  out[j] = lo;
+}
+
+__global__ void __launch_bounds__(256)
+push_pairs_kernel(const PushPairsParams p) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= p.n) return;
-  const uint32_t id = __float_as_uint(p.pts[i].w);
   int o = 0;
-  while (o + 1 < p.R && (int64_t)id >= p.begin[o + 1]) ++o;
-  p.out[o][(int64_t)id - p.begin[o]] = p.result_sorted[i];
+  while (o + 1 < p.R && i >= p.cut[o + 1]) ++o;
+  p.dst[o][p.dst_offset[o] + (i - p.cut[o])] = make_uint2(p.ids[i], p.vals[i]);
+}
+
+__global__ void __launch_bounds__(256)
+scatter_pairs_kernel(const uint2* __restrict__ pairs, int64_t n, int64_t begin, float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint2 pr = pairs[i];
+  out[(int64_t)pr.x - begin] = __uint_as_float(pr.y);
 }
 
 __global__ void __launch_bounds__(256)
@@ -285,10 +352,10 @@ int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream
 }
 
 int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, int dst_box_count,
-                   char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream) {
+                   const float* r6, char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream) {
   KNN_CUDA_TRY(cudaMemsetAsync(out_count, 0, sizeof(int), stream));
   pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, dst_boxes, dst_box_count,
-                                                 peer_inbox, out_count);
+                                                 r6[0], r6[1], r6[2], r6[3], r6[4], r6[5], peer_inbox, out_count);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;
@@ -317,9 +384,36 @@ int redistribute_launch(const RedistributeParams& p, cudaStream_t stream) {
   return 0;
 }
 
-int return_results_launch(const ReturnParams& p, cudaStream_t stream) {
+int extract_pairs_launch(const Float4* pts, const float* res, int64_t n, uint32_t* ids, uint32_t* vals,
+                         cudaStream_t stream) {
+  if (n <= 0) return 0;
+  extract_pairs_kernel<<<blocks_for(n, 256), 256, 0, stream>>>(pts, res, n, ids, vals);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int lower_bounds32_launch(const uint32_t* sorted_ids, int64_t n, const int64_t* d_begins, int count, int64_t* out,
+                          cudaStream_t stream) {
+  KNN_REQUIRE(count <= 32, "lower_bounds32: too many boundaries");
+  if (count <= 0) return 0;
+  lower_bounds32_kernel<<<1, 32, 0, stream>>>(sorted_ids, n, d_begins, count, out);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int push_pairs_launch(const PushPairsParams& p, cudaStream_t stream) {
   if (p.n <= 0) return 0;
-  return_results_kernel<<<blocks_for(p.n, 256), 256, 0, stream>>>(p);
+  push_pairs_kernel<<<blocks_for(p.n, 256), 256, 0, stream>>>(p);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int scatter_pairs_launch(const void* pairs, int64_t n, int64_t begin, float* out, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  scatter_pairs_kernel<<<blocks_for(n, 256), 256, 0, stream>>>(static_cast<const uint2*>(pairs), n, begin, out);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;

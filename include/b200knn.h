@@ -152,9 +152,12 @@ enum {
   B200KNN_MODE_RING = 0,            /* all-pairs fused ring; any input (unorderedDataVariant.cu:173-205) */
   B200KNN_MODE_PREPARTITIONED = 1,  /* keep points where they are; bbox-culled per-group exchange
                                        (prePartitionedDataVariant.cu:304-357) */
-  B200KNN_MODE_REDISTRIBUTE = 2     /* scatter points to spatial owners first, then as mode 1, then
+  B200KNN_MODE_REDISTRIBUTE = 2,    /* scatter points to spatial owners first, then as mode 1, then
                                        return results to the reading rank (no counterpart in the
                                        reference; makes unordered input scale with GPU count) */
+  B200KNN_MODE_AUTO = 3             /* per-rank inputs: mode 1 if the ranks' bounding boxes are nearly
+                                       disjoint (pairwise overlap < 2 % of a box), else mode 2 on the
+                                       concatenation of the inputs (global_begin is computed) */
 };
 
 typedef struct b200knn_dist_report {
@@ -163,6 +166,8 @@ typedef struct b200knn_dist_report {
   int64_t points_after_redistribute;
   int32_t chunks, rounds;
   double ms_local_phase, ms_host_collectives, ms_rounds;   /* breakdown of ms_query in modes 1 and 2 */
+  int32_t auto_chose_redistribute;  /* mode 3 only: 1 if the inputs overlapped and were redistributed */
+  int32_t reserved;
 } b200knn_dist_report;
 
 /* Collective over all ranks of the bootstrap. The engine keeps a symmetric, IPC-mapped heap that

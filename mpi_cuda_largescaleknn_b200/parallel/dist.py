@@ -23,7 +23,7 @@ import torch.distributed as dist
 from ..ops._lib import check, lib
 from ..ops.knn import _as_xyz, _stream_ptr
 
-MODES = {"ring": 0, "prepartitioned": 1, "redistribute": 2}
+MODES = {"ring": 0, "prepartitioned": 1, "redistribute": 2, "auto": 3}
 
 ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64)
 BARRIER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p)
@@ -38,7 +38,8 @@ class DistReport(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_redistribute", C.c_double), ("ms_build", C.c_double),
                 ("ms_query", C.c_double), ("ms_return", C.c_double), ("pending_groups", C.c_int64),
                 ("points_after_redistribute", C.c_int64), ("chunks", C.c_int32), ("rounds", C.c_int32),
-                ("ms_local_phase", C.c_double), ("ms_host_collectives", C.c_double), ("ms_rounds", C.c_double)]
+                ("ms_local_phase", C.c_double), ("ms_host_collectives", C.c_double), ("ms_rounds", C.c_double),
+                ("auto_chose_redistribute", C.c_int32), ("reserved", C.c_int32)]
 
     def as_dict(self) -> dict:
         return {name: getattr(self, name) for name, _ in self._fields_}

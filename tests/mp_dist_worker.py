@@ -61,6 +61,16 @@ def main() -> int:
         ref = bruteforce(x_all, queries=x[sel], k=20)
         got = eng.knn(xd, 20, mode="prepartitioned").cpu().numpy()
         check(f"blobs overlap={overlap}", got, ref, sel)
+        pend_inplace = eng.last_report["pending_groups"]
+        got = eng.knn(xd, 20, mode="auto").cpu().numpy()
+        check(f"blobs overlap={overlap} auto", got, ref, sel)
+        if overlap == 0.0 and eng.last_report["auto_chose_redistribute"] != 0:
+            fails += 1
+            print("AUTO FAILED: disjoint blobs must stay in place", flush=True)
+        if overlap == 1.0 and eng.last_report["auto_chose_redistribute"] != 1:
+            fails += 1
+            print("AUTO FAILED: interpenetrating blobs must be redistributed", flush=True)
+        eng.last_report["pending_groups"] = pend_inplace
         pend = torch.tensor([eng.last_report["pending_groups"]], device=dev)
         dist.all_reduce(pend)
         groups = world * ((40_000 + 31) // 32)

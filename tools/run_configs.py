@@ -91,7 +91,7 @@ def main():
         n = int(64 * 1024 * 1024 * a.scale)
         sigma = 0.5 / 2.128   # P(|x-c| > 0.5 on one axis) ~ 3.3 % -> ~10 % of a blob beyond its cell
         run("3: prePartitioned, %d files x %d Gaussian-blob points, ~10%% overlap" % (world, n),
-            blob(n, centres[rank], sigma, dev, 100 + rank), 100, "prepartitioned", 0)
+            blob(n, centres[rank], sigma, dev, 100 + rank), 100, "auto", 0)
     if "4" in only:
         N = int(1_000_000_000 * a.scale)
         b, e = N * rank // world, N * (rank + 1) // world
