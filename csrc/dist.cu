@@ -150,6 +150,15 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     KNN_CUDA_TRY(cudaMemcpyAsync(d_regions + (size_t)r * kRegionBoxes, all_regions.data() + (size_t)r * region_bytes + sizeof(RegionHead),
                                  (size_t)kRegionBoxes * sizeof(Box), cudaMemcpyHostToDevice, stream));
   }
+  if (me == 0 && getenv("B200KNN_DEBUG_REGIONS")) {
+    for (int r = 0; r < R; ++r) {
+      const Box* bx = reinterpret_cast<const Box*>(all_regions.data() + (size_t)r * region_bytes + sizeof(RegionHead));
+      fprintf(stderr, "[regions] rank %d: %d boxes, overall (%g %g %g)-(%g %g %g)\n", r, heads[r].count, heads[r].box[0],
+              heads[r].box[1], heads[r].box[2], heads[r].box[3], heads[r].box[4], heads[r].box[5]);
+      for (int i = 0; i < heads[r].count && i < 6; ++i)
+        fprintf(stderr, "   box %d: (%g %g %g)-(%g %g %g)\n", i, bx[i].lox, bx[i].loy, bx[i].loz, bx[i].hix, bx[i].hiy, bx[i].hiz);
+    }
+  }
 
   const size_t slot = pv_slot_bytes(k);
   const size_t off_pending = d->alloc((size_t)pl.Gc * slot);
