@@ -71,11 +71,21 @@ __device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned* p) {
   return v;
 }
 // Spin until *p >= want (sequence numbers only grow). Called by one lane.
+// Failure detection: a peer that died (or never launched) would otherwise leave this GPU spinning
+// forever. After ~60 s of waiting on one flag the kernel traps, which surfaces on the host as a
+// launch failure from the next synchronisation instead of a hang.
 __device__ __forceinline__ void wait_flag_ge(const unsigned* p, unsigned want) {
   unsigned ns = 32;
+  long long start = 0;
+  unsigned spins = 0;
   while ((int)(ld_acquire_sys(p) - want) < 0) {
     __nanosleep(ns);
     if (ns < 1024) ns <<= 1;
+    if ((++spins & 0xfffu) == 0u) {
+      const long long now = clock64();
+      if (start == 0) start = now;
+      else if (now - start > 120000000000ll) __trap();     // ~60 s at 2 GHz
+    }
   }
 }
 

@@ -45,6 +45,7 @@ struct b200knn_dist {
   size_t bytes = 0;
   char* peer[B200KNN_MAX_RANKS] = {};
   size_t bump = 0;
+  unsigned barrier_seq = 0;     // device barrier sequence number; identical on all ranks
   unsigned long long* task_counter = nullptr;
 
   int allgather(const void* send, void* recv, int64_t nbytes) {
@@ -101,8 +102,27 @@ int ensure_heap(b200knn_dist* d, size_t need) {
   return 0;
 }
 
+// The first bytes of the symmetric heap hold the barrier flags (one unsigned per peer); they persist
+// across calls, everything after them is re-carved by every call.
+constexpr size_t kHeapReserved = 256;
+
 size_t pv_heap_need(int k, int Gc) {
-  return 2 * align256((size_t)Gc * pv_slot_bytes(k)) + 4 * 256;
+  return kHeapReserved + 2 * align256((size_t)Gc * pv_slot_bytes(k)) + 4 * 256;
+}
+
+// Device-side barrier over all ranks, enqueued on `stream` (replaces MPI_Barrier,
+// /root/reference/prePartitionedDataVariant.cu:305). Work enqueued before it on every rank has
+// completed — including its stores into peer memory — before work enqueued after it starts anywhere.
+int device_barrier(b200knn_dist* d, cudaStream_t stream) {
+  if (d->world == 1) return 0;
+  DevBarrierParams bp;
+  memset(&bp, 0, sizeof(bp));
+  bp.R = d->world;
+  bp.rank = d->rank;
+  bp.seq = ++d->barrier_seq;
+  bp.local_flags = reinterpret_cast<const unsigned*>(d->base);
+  for (int r = 0; r < d->world; ++r) bp.peer_flags[r] = reinterpret_cast<unsigned*>(d->peer[r]);
+  return dev_barrier_launch(bp, stream);
 }
 
 struct PvPlan { int Gc; int C; int64_t max_groups; };
@@ -225,17 +245,17 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
                                heads[dst].box, d->peer[dst] + off_inbox,
                                out_count, idx->num_sms, stream))) return rc;
       if ((rc = pv_publish_launch(out_count, reinterpret_cast<int*>(d->peer[dst] + off_icount), stream))) return rc;
-      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-      if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
+      // round fences are device-side sequence-flag barriers, enqueued on the stream: the host does
+      // not synchronise between push, serve and the next round
+      if ((rc = device_barrier(d, stream))) return rc;
       p.phase = 1;
       p.src_pending = d->peer[src] + off_pending;
       if ((rc = pv_main_launch(p, pl.Gc, idx->num_sms, stream))) return rc;
-      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-      if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
+      if ((rc = device_barrier(d, stream))) return rc;
       if (rep) rep->rounds += 1;
     }
     if ((rc = pv_final_launch(p.pending, p.pending_count, k, idx->result_sorted, idx->num_sms, stream))) return rc;
-    if (rep) rep->ms_rounds += now_ms() - tr0;
+    if (rep) { KNN_CUDA_TRY(cudaStreamSynchronize(stream)); rep->ms_rounds += now_ms() - tr0; }
   }
   KNN_CUDA_TRY(cudaFreeAsync(d_regions, stream));
   return 0;
@@ -252,7 +272,7 @@ int knn_prepartitioned(b200knn_dist* d, const float* d_xyz, int64_t n_local, int
   }
   const PvPlan pl = pv_plan(max_n, k, groups_per_chunk);
   if ((rc = ensure_heap(d, pv_heap_need(k, pl.Gc)))) return rc;
-  d->bump = 0;
+  d->bump = kHeapReserved;
   const double t0 = now_ms();
   b200knn_index* idx = nullptr;
   if ((rc = b200knn_index_create(d_xyz, n_local, nullptr, 0, stream, &idx))) { b200knn_index_destroy(idx); return rc; }
@@ -373,7 +393,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   const size_t need = align256((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4)) +
                       align256((size_t)std::max<int64_t>(max_local, 1) * 8) + pv_heap_need(k, pl.Gc);
   if ((rc = ensure_heap(d, need))) return rc;
-  d->bump = 0;
+  d->bump = kHeapReserved;
   const size_t off_recv = d->alloc((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4));
   const size_t off_out = d->alloc((size_t)std::max<int64_t>(max_local, 1) * 8);   // (id, value) pairs land here
 

@@ -128,6 +128,14 @@ int pv_publish_launch(const int* out_count, int* peer_inbox_count, cudaStream_t 
 int pv_final_launch(const char* pending, const int* pending_count, int k, float* result_sorted, int num_sms,
                     cudaStream_t stream);
 
+struct DevBarrierParams {
+  unsigned* peer_flags[kMaxRanks];   // base of every rank's flag array (peer pointers); slot [rank] is ours there
+  const unsigned* local_flags;       // this rank's flag array: slot [r] is written by rank r
+  unsigned seq;
+  int rank, R;
+};
+int dev_barrier_launch(const DevBarrierParams& p, cudaStream_t stream);
+
 struct RedistributeParams {
   const float* xyz;            // local points, caller order
   const uint32_t* order;       // order[i] = caller index of the i-th point in global Morton order

@@ -224,6 +224,17 @@ pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending
   }
 }
 
+// Cross-GPU barrier as a stream-ordered kernel: lane r tells rank r "I am at sequence seq" and waits
+// until rank r has said the same. Runs as one warp; only ever waits on OTHER GPUs.
+__global__ void dev_barrier_kernel(const DevBarrierParams p) {
+  const int lane = threadIdx.x;
+  if (lane < p.R) {
+    __threadfence_system();
+    st_release_sys(p.peer_flags[lane] + p.rank, p.seq);
+    wait_flag_ge(p.local_flags + lane, p.seq);
+  }
+}
+
 __global__ void pv_publish_kernel(const int* __restrict__ out_count, int* __restrict__ peer_inbox_count) {
   if (threadIdx.x == 0) *peer_inbox_count = *out_count;
 }
@@ -356,6 +367,13 @@ int pv_push_launch(const char* pending, const int* pending_count, int k, const B
   KNN_CUDA_TRY(cudaMemsetAsync(out_count, 0, sizeof(int), stream));
   pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, dst_boxes, dst_box_count,
                                                  r6[0], r6[1], r6[2], r6[3], r6[4], r6[5], peer_inbox, out_count);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int dev_barrier_launch(const DevBarrierParams& p, cudaStream_t stream) {
+  dev_barrier_kernel<<<1, 32, 0, stream>>>(p);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;
