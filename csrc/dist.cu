@@ -153,12 +153,45 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     RegionHead* head = reinterpret_cast<RegionHead*>(my_region.data());
     memcpy(head->box, idx->h_bounds, sizeof(head->box));
     if (idx->levels > 0) {
-      int lr = 0;
-      while (idx->count[lr] > kRegionBoxes) ++lr;
-      head->count = idx->count[lr];
-      KNN_CUDA_TRY(cudaMemcpyAsync(my_region.data() + sizeof(RegionHead), idx->boxes[lr], (size_t)head->count * sizeof(Box),
-                                   cudaMemcpyDeviceToHost, stream));
+      // Adaptive description: start from the top level and keep splitting the box with the largest
+      // volume into its children until kRegionBoxes boxes are in use (never below level 1, or
+      // level 0 for small trees). A fixed level is not enough for clustered data: a node that
+      // straddles the gap between two clusters is one huge box that swallows other ranks' dense
+      // regions; splitting by volume dissolves exactly those.
+      const int lmin = idx->count[0] <= kRegionBoxes ? 0 : 1;
+      std::vector<std::vector<Box>> lv(idx->levels);
+      for (int l = lmin; l < idx->levels; ++l) {
+        lv[l].resize(idx->count[l]);
+        KNN_CUDA_TRY(cudaMemcpyAsync(lv[l].data(), idx->boxes[l], (size_t)idx->count[l] * sizeof(Box),
+                                     cudaMemcpyDeviceToHost, stream));
+      }
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      struct Item { double vol; int level; int index; };
+      auto volume = [&](int l, int i) {
+        const Box& b = lv[l][i];
+        return (double)(b.hix - b.lox) * (double)(b.hiy - b.loy) + (double)(b.hiy - b.loy) * (double)(b.hiz - b.loz) +
+               (double)(b.hiz - b.loz) * (double)(b.hix - b.lox);   // half surface area: also ranks flat boxes
+      };
+      auto smaller = [](const Item& a, const Item& b) { return a.vol < b.vol; };
+      std::vector<Item> heap, done;
+      const int top = idx->levels - 1;
+      for (int i = 0; i < idx->count[top]; ++i) heap.push_back({volume(top, i), top, i});
+      std::make_heap(heap.begin(), heap.end(), smaller);
+      while (!heap.empty()) {
+        std::pop_heap(heap.begin(), heap.end(), smaller);
+        const Item it = heap.back();
+        heap.pop_back();
+        const int c0 = it.index * kFanout;
+        const int nc = it.level > lmin ? std::min(kFanout, idx->count[it.level - 1] - c0) : 0;
+        if (nc == 0 || (int)(heap.size() + done.size()) + nc > kRegionBoxes) { done.push_back(it); continue; }
+        for (int c = 0; c < nc; ++c) {
+          heap.push_back({volume(it.level - 1, c0 + c), it.level - 1, c0 + c});
+          std::push_heap(heap.begin(), heap.end(), smaller);
+        }
+      }
+      head->count = (int32_t)done.size();
+      Box* out_boxes = reinterpret_cast<Box*>(my_region.data() + sizeof(RegionHead));
+      for (size_t i = 0; i < done.size(); ++i) out_boxes[i] = lv[done[i].level][done[i].index];
     }
     if (d->allgather(my_region.data(), all_regions.data(), (int64_t)region_bytes)) { set_last_error("bootstrap allgather failed"); return -3; }
   }
