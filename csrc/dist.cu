@@ -154,44 +154,100 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     memcpy(head->box, idx->h_bounds, sizeof(head->box));
     if (idx->levels > 0) {
       // Adaptive description: start from the top level and keep splitting the box with the largest
-      // volume into its children until kRegionBoxes boxes are in use (never below level 1, or
-      // level 0 for small trees). A fixed level is not enough for clustered data: a node that
-      // straddles the gap between two clusters is one huge box that swallows other ranks' dense
-      // regions; splitting by volume dissolves exactly those.
-      const int lmin = idx->count[0] <= kRegionBoxes ? 0 : 1;
+      // surface into its parts until kRegionBoxes boxes are in use: inner node -> its <= 32 children,
+      // leaf -> its points cut in two at the largest gap along the widest axis, and such point sets
+      // again. A fixed tree level is not enough: a node (even a single leaf) that straddles a jump of
+      // the Z-curve or the gap between two clusters has one huge box that swallows other ranks' dense
+      // regions and would send all of their groups here for nothing. Levels >= 1 are copied to the host
+      // up front (<= 2 MB); leaf boxes and points are fetched on demand for the few nodes that need it.
+      const int lfetch = idx->levels > 1 ? 1 : 0;
       std::vector<std::vector<Box>> lv(idx->levels);
-      for (int l = lmin; l < idx->levels; ++l) {
+      for (int l = lfetch; l < idx->levels; ++l) {
         lv[l].resize(idx->count[l]);
         KNN_CUDA_TRY(cudaMemcpyAsync(lv[l].data(), idx->boxes[l], (size_t)idx->count[l] * sizeof(Box),
                                      cudaMemcpyDeviceToHost, stream));
       }
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-      struct Item { double vol; int level; int index; };
-      auto volume = [&](int l, int i) {
-        const Box& b = lv[l][i];
-        return (double)(b.hix - b.lox) * (double)(b.hiy - b.loy) + (double)(b.hiy - b.loy) * (double)(b.hiz - b.loz) +
-               (double)(b.hiz - b.loz) * (double)(b.hix - b.lox);   // half surface area: also ranks flat boxes
+      struct Item { double area; int level; int index; Box box; };     // level -1: explicit point set `index`
+      std::vector<std::vector<Float4>> point_sets;
+      auto area_of = [](const Box& b) {
+        const double ex = (double)b.hix - b.lox, ey = (double)b.hiy - b.loy, ez = (double)b.hiz - b.loz;
+        return ex * ey + ey * ez + ez * ex + 1e-30 * (ex + ey + ez);    // half surface area; flat boxes still rank
       };
-      auto smaller = [](const Item& a, const Item& b) { return a.vol < b.vol; };
+      auto box_of_points = [](const std::vector<Float4>& ps) {
+        Box b;
+        b.lox = b.loy = b.loz = INFINITY; b.hix = b.hiy = b.hiz = -INFINITY; b.cnt_bits = 0.f; b.pad = 0.f;
+        for (const Float4& q : ps) {
+          b.lox = fminf(b.lox, q.x); b.loy = fminf(b.loy, q.y); b.loz = fminf(b.loz, q.z);
+          b.hix = fmaxf(b.hix, q.x); b.hiy = fmaxf(b.hiy, q.y); b.hiz = fmaxf(b.hiz, q.z);
+        }
+        return b;
+      };
+      auto smaller = [](const Item& x, const Item& y) { return x.area < y.area; };
       std::vector<Item> heap, done;
       const int top = idx->levels - 1;
-      for (int i = 0; i < idx->count[top]; ++i) heap.push_back({volume(top, i), top, i});
+      if (top >= lfetch) {
+        for (int i = 0; i < idx->count[top]; ++i) heap.push_back({area_of(lv[top][i]), top, i, lv[top][i]});
+      } else {   // single-level tree whose leaves were not fetched: cannot happen (lfetch == 0 then)
+        KNN_REQUIRE(false, "internal: region levels");
+      }
       std::make_heap(heap.begin(), heap.end(), smaller);
+      std::vector<Box> kids(kFanout);
       while (!heap.empty()) {
         std::pop_heap(heap.begin(), heap.end(), smaller);
         const Item it = heap.back();
         heap.pop_back();
-        const int c0 = it.index * kFanout;
-        const int nc = it.level > lmin ? std::min(kFanout, idx->count[it.level - 1] - c0) : 0;
-        if (nc == 0 || (int)(heap.size() + done.size()) + nc > kRegionBoxes) { done.push_back(it); continue; }
-        for (int c = 0; c < nc; ++c) {
-          heap.push_back({volume(it.level - 1, c0 + c), it.level - 1, c0 + c});
+        const int used = (int)(heap.size() + done.size());
+        if (it.level >= 1) {
+          const int c0 = it.index * kFanout;
+          const int nc = std::min(kFanout, idx->count[it.level - 1] - c0);
+          if (used + nc > kRegionBoxes) { done.push_back(it); continue; }
+          const Box* src = nullptr;
+          if (it.level - 1 >= lfetch) src = lv[it.level - 1].data() + c0;
+          else {
+            KNN_CUDA_TRY(cudaMemcpy(kids.data(), idx->boxes[0] + c0, (size_t)nc * sizeof(Box), cudaMemcpyDeviceToHost));
+            src = kids.data();
+          }
+          for (int c = 0; c < nc; ++c) {
+            heap.push_back({area_of(src[c]), it.level - 1, c0 + c, src[c]});
+            std::push_heap(heap.begin(), heap.end(), smaller);
+          }
+          continue;
+        }
+        // a leaf or an explicit point set: cut at the largest gap along the widest axis
+        if (used + 2 > kRegionBoxes) { done.push_back(it); continue; }
+        std::vector<Float4> ps;
+        if (it.level == 0) {
+          const int64_t first = (int64_t)it.index * kGroup;
+          const int cnt = (int)std::min<int64_t>(kGroup, idx->n - first);
+          ps.resize(cnt);
+          KNN_CUDA_TRY(cudaMemcpy(ps.data(), idx->pts + first, (size_t)cnt * sizeof(Float4), cudaMemcpyDeviceToHost));
+        } else {
+          ps = point_sets[it.index];
+        }
+        if (ps.size() < 2) { done.push_back(it); continue; }
+        const float ex = it.box.hix - it.box.lox, ey = it.box.hiy - it.box.loy, ez = it.box.hiz - it.box.loz;
+        const int axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
+        auto coord = [axis](const Float4& q) { return axis == 0 ? q.x : (axis == 1 ? q.y : q.z); };
+        std::sort(ps.begin(), ps.end(), [&](const Float4& x, const Float4& y) { return coord(x) < coord(y); });
+        size_t cut = 1;
+        float best_gap = -1.f;
+        for (size_t i = 1; i < ps.size(); ++i) {
+          const float gap = coord(ps[i]) - coord(ps[i - 1]);
+          if (gap > best_gap) { best_gap = gap; cut = i; }
+        }
+        if (!(best_gap > 0.f)) { done.push_back(it); continue; }      // all points identical along every axis
+        for (int half = 0; half < 2; ++half) {
+          std::vector<Float4> part(half == 0 ? ps.begin() : ps.begin() + cut, half == 0 ? ps.begin() + cut : ps.end());
+          const Box pb = box_of_points(part);
+          point_sets.push_back(std::move(part));
+          heap.push_back({area_of(pb), -1, (int)point_sets.size() - 1, pb});
           std::push_heap(heap.begin(), heap.end(), smaller);
         }
       }
       head->count = (int32_t)done.size();
       Box* out_boxes = reinterpret_cast<Box*>(my_region.data() + sizeof(RegionHead));
-      for (size_t i = 0; i < done.size(); ++i) out_boxes[i] = lv[done[i].level][done[i].index];
+      for (size_t i = 0; i < done.size(); ++i) out_boxes[i] = done[i].box;
     }
     if (d->allgather(my_region.data(), all_regions.data(), (int64_t)region_bytes)) { set_last_error("bootstrap allgather failed"); return -3; }
   }
