@@ -14,7 +14,7 @@ constexpr unsigned kNodeIdxBits = 28;  // node = level << 28 | index
 
 __host__ __device__ constexpr int heap_padded(int k) { return 4 * ((k - 1 + 3) / 4) + 1; }
 __host__ __device__ constexpr size_t warp_smem_floats(int k) {
-  return (size_t)heap_padded(k) * 32 + 128 + 2 * kQueueCap + 32;
+  return (size_t)heap_padded(k) * 32 + 128 + 2 * kQueueCap + 32 + 96;   // heap | stage | frontier | frames | soa
 }
 
 struct GroupCtx {
@@ -23,7 +23,8 @@ struct GroupCtx {
   float glx, gly, glz, ghx, ghy, ghz;   // bounding box of the group's valid queries (warp-uniform)
   float maxR2;          // max over valid lanes of top (warp-uniform)
   float* heap;          // shared: heap[i*32] is entry i of this lane
-  float4* stage;        // shared: 32 leaf points
+  float4* stage;        // shared: 32 leaf points (x,y,z,id)
+  float* soa;           // shared: the same points as x[32] | y[32] | z[32]
   unsigned* qkey;       // shared: frontier lower bounds (float bits; non-negative => uint-ordered)
   unsigned* qnode;      // shared: frontier nodes
   unsigned* frames;     // shared: frame stack of the depth-first fallback
@@ -51,21 +52,51 @@ __device__ __forceinline__ float heap_replace_padded(float* h, int kp, float e) 
   return h[0];
 }
 
+// ---- packed fp32x2 arithmetic (Blackwell FADD2/FMUL2/FFMA2) ----
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  return (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
+}
+__device__ __forceinline__ unsigned long long sub2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+
 __device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g) {
   const int lane = lane_id();
   float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);   // padding never beats any top
   if (lane < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane);
   g.stage[lane] = p;
+  g.soa[lane] = p.x;          // x[32] | y[32] | z[32]: pairs of candidates load as one 64-bit word
+  g.soa[32 + lane] = p.y;
+  g.soa[64 + lane] = p.z;
   __syncwarp();
 
-  // phase 1: convergent distance sweep
+  // phase 1: convergent distance sweep, two candidates per instruction with the packed fp32x2
+  // pipe (FADD2 / FMUL2 / FFMA2 on sm_100a): each half is an independent IEEE operation, so the
+  // result is bit-identical to dist2().
   unsigned mask = 0;
   const float top0 = g.top;
+  const unsigned long long qx2 = pack2(g.qx, g.qx), qy2 = pack2(g.qy, g.qy), qz2 = pack2(g.qz, g.qz);
+  const unsigned long long* sx = reinterpret_cast<const unsigned long long*>(g.soa);
+  const unsigned long long* sy = reinterpret_cast<const unsigned long long*>(g.soa + 32);
+  const unsigned long long* sz = reinterpret_cast<const unsigned long long*>(g.soa + 64);
 #pragma unroll
-  for (int j = 0; j < kGroup; ++j) {
-    const float4 c = g.stage[j];
-    const float d2 = dist2(g.qx, g.qy, g.qz, c.x, c.y, c.z);
-    mask |= (d2 < top0) ? (1u << j) : 0u;
+  for (int jj = 0; jj < kGroup / 2; ++jj) {
+    const unsigned long long dx = sub2(qx2, sx[jj]), dy = sub2(qy2, sy[jj]), dz = sub2(qz2, sz[jj]);
+    const unsigned long long d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
+    mask |= (__uint_as_float((unsigned)(d2 & 0xffffffffull)) < top0) ? (1u << (2 * jj)) : 0u;
+    mask |= (__uint_as_float((unsigned)(d2 >> 32)) < top0) ? (2u << (2 * jj)) : 0u;
   }
   if (!g.valid) mask = 0;
 
@@ -294,6 +325,7 @@ __device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int war
   g.qkey = reinterpret_cast<unsigned*>(warp_base + (size_t)kp * 32 + 128);
   g.qnode = g.qkey + kQueueCap;
   g.frames = g.qnode + kQueueCap;
+  g.soa = reinterpret_cast<float*>(g.frames + 32);
   g.kp = kp;
   g.n_leaves = g.n_inner = g.n_inserts = g.n_fallback = g.n_purge = 0;
 }
