@@ -9,7 +9,7 @@ namespace b200knn {
 namespace {
 
 constexpr int Q_MAX_WARPS = 16;        // per CTA
-constexpr int kQueueCap = 256;         // frontier entries per warp (2 KB)
+constexpr int kQueueCap = 128;         // frontier entries per warp (1 KB)
 constexpr unsigned kNodeIdxBits = 28;  // node = level << 28 | index
 
 __host__ __device__ constexpr int heap_padded(int k) { return 4 * ((k - 1 + 3) / 4) + 1; }
