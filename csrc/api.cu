@@ -286,6 +286,57 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   return 0;
 }
 
+// Find-closest-point: k = 1 traversal that also reports WHICH point is closest.
+// Role of cukd::stackFree::fcp (cudaKDTree/cukd/fcp.h:210-254).
+int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, float max_radius, int32_t* d_out_ids,
+                      float* d_out_dist, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  KNN_REQUIRE(idx && d_out_ids, "fcp_query: NULL argument");
+  KNN_REQUIRE(nq >= 0 && nq < (int64_t)0x7fffffff - 64, "fcp_query: nq out of range");
+  if (nq == 0) return 0;
+  const int64_t groups = div_up(nq, kGroup);
+  uint64_t *keys = nullptr, *keys_tmp = nullptr;
+  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr, *ids_sorted = nullptr;
+  Float4* qsorted = nullptr;
+  float* rsorted = nullptr;
+  KNN_CUDA_TRY(cudaMallocAsync(&keys, nq * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, nq * sizeof(uint64_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&vals, nq * sizeof(uint32_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, nq * sizeof(uint32_t), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(nq), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&qsorted, groups * kGroup * sizeof(Float4), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&rsorted, groups * kGroup * sizeof(float), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&ids_sorted, groups * kGroup * sizeof(uint32_t), stream));
+  int rc;
+  if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
+  int in_tmp = 0;
+  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
+  if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
+  if ((rc = refine_runs(qsorted, nq, stream))) return rc;
+  RingParams p;
+  fill_local_only(p, idx, 1, max_radius);
+  p.groups_per_chunk = (int)groups;
+  p.home_queries = qsorted;
+  p.home_n = nq;
+  p.result_sorted = rsorted;
+  p.result_ids = ids_sorted;
+  if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
+  // ids are 32-bit payloads: the float scatter moves them unchanged
+  if ((rc = scatter_results(qsorted, reinterpret_cast<const float*>(ids_sorted), nq, 0,
+                            reinterpret_cast<float*>(d_out_ids), stream))) return rc;
+  if (d_out_dist && (rc = scatter_results(qsorted, rsorted, nq, 0, d_out_dist, stream))) return rc;
+  KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(qsorted, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(rsorted, stream));
+  KNN_CUDA_TRY(cudaFreeAsync(ids_sorted, stream));
+  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  return 0;
+}
+
 int b200knn_index_enable_stats(b200knn_index* idx, int on) {
   KNN_REQUIRE(idx, "index_enable_stats: NULL index");
   idx->stats_on = on != 0;

@@ -82,6 +82,7 @@ struct RingParams {
   unsigned* next_flag[2];      // next rank's flag_in
   unsigned* prev_ack[2];       // prev rank's ack_in
   float* result_sorted;        // home rank's result array for the LAST hop (next rank's, or own if R==1)
+  unsigned* result_ids;        // optional (single rank, k == 1): id of the closest point, 0xffffffff if none
   unsigned long long* task_counter;   // local, zeroed before launch
   unsigned long long* stats;   // optional [4]: leaves visited, candidates tested, heap inserts, inner nodes
 };

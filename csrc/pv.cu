@@ -70,6 +70,7 @@ pv_main_kernel(const PvMainParams p) {
         const float sent = p.sentinel;
         for (int i = 0; i < k; ++i) g.heap[i * 32] = sent;
         g.top = sent;
+        g.last_id = 0xffffffffu;
       }
     } else {
       const char* slot = p.inbox + (size_t)t * slot_bytes;

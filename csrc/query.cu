@@ -72,6 +72,7 @@ knn_ring_kernel(const RingParams p) {
         const float sent = p.sentinel;
         for (int i = 0; i < k; ++i) g.heap[i * 32] = sent;
         g.top = sent;
+        g.last_id = 0xffffffffu;
       }
     } else {
       if (p.use_flags) {
@@ -105,7 +106,10 @@ knn_ring_kernel(const RingParams p) {
 
     // ------------------------------------------------------------------ output
     if (hop == R - 1) {
-      if (g.valid) p.result_sorted[home_group * kGroup + lane] = finalize_kth(g.top);
+      if (g.valid) {
+        p.result_sorted[home_group * kGroup + lane] = finalize_kth(g.top);
+        if (p.result_ids != nullptr) p.result_ids[home_group * kGroup + lane] = g.last_id;
+      }
     } else {
       const int op = par ^ 1;
       if (p.use_flags) {

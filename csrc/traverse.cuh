@@ -30,6 +30,7 @@ struct GroupCtx {
   unsigned* frames;     // shared: frame stack of the depth-first fallback
   int kp;               // padded heap size
   bool valid;
+  unsigned last_id;     // id of the most recently accepted candidate (find-closest-point uses it, k == 1)
   unsigned n_leaves, n_inner, n_inserts, n_fallback, n_purge;
 };
 
@@ -108,6 +109,7 @@ __device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cn
     const float d2 = dist2(g.qx, g.qy, g.qz, c.x, c.y, c.z);
     if (d2 < g.top) {
       g.top = heap_replace_padded(g.heap, g.kp, d2);
+      g.last_id = __float_as_uint(c.w);     // for k == 1 this is the id of the closest point so far
       ++g.n_inserts;
     }
   }

@@ -64,6 +64,12 @@ int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, 
  * Synchronises `stream` (temporary buffers). */
 int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, int k, float max_radius,
                       float* d_out, void* stream);
+/* fcp_query: find-closest-point. For every query the id of the nearest indexed point (the id given to
+ * index_create: position + id_offset, or ids[]) and optionally its distance; -1 / +inf (or max_radius)
+ * if no point lies within max_radius. Ties are broken arbitrarily. Role of cukd::stackFree::fcp
+ * (cudaKDTree/cukd/fcp.h:210-254). Synchronises `stream`. */
+int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, float max_radius,
+                      int32_t* d_out_ids, float* d_out_dist_or_null, void* stream);
 /* knn_self_noalloc: same result as index_create + knn_self for n <= B200KNN_NOALLOC_MAX_POINTS, but
  * the library allocates nothing: the sorted points, the box tree, the sort buffers and the counters
  * all live in one fixed device array inside the library (about 11.9 MB per GPU that loads it, held

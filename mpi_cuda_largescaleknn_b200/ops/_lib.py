@@ -58,6 +58,7 @@ def _proto(lib):
         "b200knn_index_copy_boxes": [vp, i32, vp, P(i32)],
         "b200knn_knn_self": [vp, i32, f32, vp, vp],
         "b200knn_knn_query": [vp, vp, i64, i32, f32, vp, vp],
+        "b200knn_fcp_query": [vp, vp, i64, f32, vp, vp, vp],
         "b200knn_index_stats": [vp, vp],
         "b200knn_index_enable_stats": [vp, i32],
         "b200knn_ring_create": [vp, i32, i32, i32, i64, i32, P(vp)],

@@ -119,6 +119,18 @@ class KnnIndex:
         return out
 
 
+def fcp(index: "KnnIndex", queries: torch.Tensor, max_radius: float = math.inf):
+    """Find-closest-point: (ids int32 [nq], distances float32 [nq]) of the nearest indexed point of
+    every query; id -1 where nothing lies within ``max_radius``. Role of ``cukd::fcp``."""
+    q = _as_xyz(queries)
+    ids = torch.empty(q.shape[0], dtype=torch.int32, device=index.device)
+    dist = torch.empty(q.shape[0], dtype=torch.float32, device=index.device)
+    with torch.cuda.device(index.device):
+        check(lib().b200knn_fcp_query(index.handle, q.data_ptr() if q.shape[0] else None, int(q.shape[0]),
+                                      float(max_radius), ids.data_ptr(), dist.data_ptr(), _stream_ptr()), "fcp_query")
+    return ids, dist
+
+
 def knn(points: torch.Tensor, k: int, max_radius: float = math.inf) -> torch.Tensor:
     """Distance from each point to its k-th nearest neighbour among ``points`` (self included)."""
     idx = KnnIndex(points)
