@@ -29,7 +29,7 @@ $(BUILD)/%.o: csrc/%.cpp csrc/*.h include/b200knn.h
 	$(CXX) $(CXXFLAGS) -c $< -o $@
 
 $(LIB): $(CU_OBJS) $(CPP_OBJS)
-	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart static -lpthread
+	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart static -lpthread -ldl
 
 clean:
 	rm -rf $(BUILD)

@@ -100,6 +100,7 @@ int b200knn_index_create_xyzw(const float* d_xyzw, int64_t n, uint32_t id_offset
 
 static int index_create_impl(const float* d_xyz, int stride, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
                              cudaStream_t stream, b200knn_index** out) {
+  NvtxRange range("b200knn:index_build");
   KNN_REQUIRE(out != nullptr, "index_create: out is NULL");
   KNN_REQUIRE(n >= 0 && n < (int64_t)0x7fffffff - 64, "index_create: n must be in [0, 2^31-64) per GPU");
   b200knn_index* idx = new b200knn_index();
@@ -224,6 +225,7 @@ static void fill_local_only(RingParams& p, b200knn_index* idx, int k, float max_
 
 int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
+  NvtxRange range("b200knn:knn_self");
   KNN_REQUIRE(idx && d_out, "knn_self: NULL argument");
   KNN_REQUIRE(k >= 1, "knn_self: k must be >= 1");
   if (idx->n == 0) return 0;

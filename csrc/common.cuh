@@ -35,6 +35,16 @@ void note_launch();                             // api.cu: counts kernel launche
     }                                                                                    \
   } while (0)
 
+}  // namespace b200knn
+#include <nvtx3/nvToolsExt.h>
+namespace b200knn {
+// Named range visible in Nsight Systems / ncu (role of the reference's getCurrentTime() brackets,
+// cukd/common.h:219-237, which exist only in its tests; the MPI programs have no timers at all).
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+
 #if defined(__CUDACC__)
 
 constexpr unsigned kFullMask = 0xffffffffu;

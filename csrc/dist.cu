@@ -142,6 +142,7 @@ PvPlan pv_plan(int64_t max_n, int k, int groups_per_chunk) {
 // are taken from d->bump (symmetric: same sequence on every rank). Results land in idx->result_sorted.
 int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const PvPlan& pl, cudaStream_t stream,
            b200knn_dist_report* rep) {
+  NvtxRange range("b200knn:culled_exchange");
   const int R = d->world, me = d->rank;
   // everyone's region: the boxes of the deepest tree level with at most kRegionBoxes nodes, plus the
   // overall box for a quick reject. One box per rank is far too coarse: a few stray points at the end
@@ -377,6 +378,7 @@ int knn_prepartitioned(b200knn_dist* d, const float* d_xyz, int64_t n_local, int
 int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64_t global_begin, int k,
                      float max_radius, int groups_per_chunk, float* d_out, cudaStream_t stream,
                      b200knn_dist_report* rep) {
+  NvtxRange range("b200knn:redistribute_pipeline");
   const int R = d->world, me = d->rank;
   int rc;
   const double t0 = now_ms();

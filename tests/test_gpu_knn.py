@@ -204,8 +204,6 @@ def test_fcp_returns_closest_point_id_and_distance():
     want = bruteforce(x, queries=q, k=1)
     assert bit_equal(dist, want)
     assert ids.min() >= 1000 and ids.max() < 1000 + len(x)
-    d = q - x[ids - 1000]
-    got_d2 = (np.float32(d[:, 2] * d[:, 2]).astype(np.float64) + 0)  # placeholder to keep dtype explicit
     # the returned point really is at the reported distance (recomputed with the oracle on that single point)
     chk = np.array([bruteforce(x[i - 1000][None, :], queries=q[j][None, :], k=1)[0] for j, i in enumerate(ids[:300])], np.float32)
     assert bit_equal(chk, dist[:300])
