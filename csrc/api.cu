@@ -414,10 +414,20 @@ int b200knn_ring_create(b200knn_index* idx, int rank, int world, int k, int64_t 
   return 0;
 }
 
-void b200knn_ring_destroy(b200knn_ring* r) {
-  if (!r) return;
+// Unmap the peers' buffers. Call on every rank, then fence (barrier), then ring_destroy: an exporter
+// must not free memory that an importer still has mapped.
+int b200knn_ring_disconnect(b200knn_ring* r) {
+  KNN_REQUIRE(r, "ring_disconnect: NULL ring");
   if (r->opened_next) cudaIpcCloseMemHandle(r->next_base);
   if (r->opened_prev) cudaIpcCloseMemHandle(r->prev_base);
+  r->opened_next = r->opened_prev = false;
+  r->next_base = r->prev_base = nullptr;
+  return 0;
+}
+
+void b200knn_ring_destroy(b200knn_ring* r) {
+  if (!r) return;
+  b200knn_ring_disconnect(r);
   cudaFree(r->base);
   delete r;
 }

@@ -58,11 +58,14 @@ struct b200knn_dist {
 
 namespace {
 
+// Collective. Every rank first unmaps its peers' heaps, then (after a fence) frees its own: an
+// exporter must not free memory that an importer still has mapped.
 int close_heap(b200knn_dist* d) {
   for (int r = 0; r < d->world; ++r) {
     if (r != d->rank && d->peer[r]) cudaIpcCloseMemHandle(d->peer[r]);
     d->peer[r] = nullptr;
   }
+  if (d->world > 1 && d->base) d->barrier();
   if (d->base) cudaFree(d->base);
   d->base = nullptr;
   d->bytes = 0;
@@ -153,7 +156,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   {
     RegionHead* head = reinterpret_cast<RegionHead*>(my_region.data());
     memcpy(head->box, idx->h_bounds, sizeof(head->box));
-    if (idx->levels > 0) {
+    if (idx->levels > 0 && R > 1) {
       // Adaptive description: start from the top level and keep splitting the box with the largest
       // surface into its parts until kRegionBoxes boxes are in use: inner node -> its <= 32 children,
       // leaf -> its points cut in two at the largest gap along the widest axis, and such point sets
@@ -626,6 +629,10 @@ int knn_ring(b200knn_dist* d, const float* d_xyz, int64_t n_local, int k, float 
   if (!rc) { cudaError_t e = cudaStreamSynchronize(stream); if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; } }
   if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
   if (rep) { rep->ms_build += t1 - t0; rep->ms_query += now_ms() - t1; }
+  if (ring) {
+    b200knn_ring_disconnect(ring);
+    d->barrier();
+  }
   b200knn_ring_destroy(ring);
   b200knn_index_destroy(idx);
   return rc;

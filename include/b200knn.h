@@ -106,6 +106,9 @@ int b200knn_index_enable_stats(b200knn_index* idx, int on);
  * in-flight candidate memory: 2 * groups_per_chunk * (k*128 + 516) bytes per GPU. */
 int b200knn_ring_create(b200knn_index* idx, int rank, int world, int k, int64_t max_points_any_rank,
                         int groups_per_chunk, b200knn_ring** out);
+/* Tear-down on every rank: ring_disconnect -> barrier -> ring_destroy (peers must unmap before the
+ * owner frees). ring_destroy alone is fine for world == 1. */
+int b200knn_ring_disconnect(b200knn_ring* ring);
 void b200knn_ring_destroy(b200knn_ring* ring);
 int b200knn_ring_export(b200knn_ring* ring, void* blob /* B200KNN_IPC_BLOB_BYTES */);
 int b200knn_ring_connect(b200knn_ring* ring, const void* all_blobs /* world * B200KNN_IPC_BLOB_BYTES */);

@@ -62,6 +62,7 @@ def _proto(lib):
         "b200knn_index_stats": [vp, vp],
         "b200knn_index_enable_stats": [vp, i32],
         "b200knn_ring_create": [vp, i32, i32, i32, i64, i32, P(vp)],
+        "b200knn_ring_disconnect": [vp],
         "b200knn_ring_export": [vp, vp],
         "b200knn_ring_connect": [vp, vp],
         "b200knn_ring_run": [vp, f32, vp],

@@ -111,6 +111,8 @@ class FusedRing:
         if self._h.value:
             torch.cuda.synchronize()
             barrier(self.group)
+            check(lib().b200knn_ring_disconnect(self._h), "ring_disconnect")
+            barrier(self.group)          # every peer has unmapped before anybody frees
             lib().b200knn_ring_destroy(self._h)
             self._h = C.c_void_p()
 
