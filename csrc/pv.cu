@@ -87,11 +87,9 @@ pv_main_kernel(const PvMainParams p) {
 
     if (cnt > 0 && p.tree.n > 0) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;
-      group_bounds(g);
-      const int seed = (p.phase == 0 && p.home_is_tree)
-                           ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1)
-                           : find_seed_l1(p.tree, g);
-      traverse(p.tree, g, seed);
+      const int own_seed = (p.phase == 0 && p.home_is_tree)
+                               ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1) : -2;
+      traverse_group(p.tree, g, cnt, own_seed);
     }
 
     if (p.phase == 0) {

@@ -97,11 +97,9 @@ knn_ring_kernel(const RingParams p) {
     // ------------------------------------------------------------------ traverse the local tree
     if (cnt > 0 && p.tree.n > 0) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;   // heap padding
-      group_bounds(g);
-      // seed = the level-1 node holding the group's own leaf (self queries at home), else the nearest
-      const int seed = (hop == 0 && p.home_is_tree) ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1)
-                                                    : find_seed_l1(p.tree, g);
-      traverse(p.tree, g, seed);
+      // seed = the level-1 node holding the group's own leaf (self queries at home), else the nearest (-2)
+      const int own_seed = (hop == 0 && p.home_is_tree) ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1) : -2;
+      traverse_group(p.tree, g, cnt, own_seed);
     }
 
     // ------------------------------------------------------------------ output

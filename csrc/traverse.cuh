@@ -14,7 +14,7 @@ constexpr unsigned kNodeIdxBits = 28;  // node = level << 28 | index
 
 __host__ __device__ constexpr int heap_padded(int k) { return 4 * ((k - 1 + 3) / 4) + 1; }
 __host__ __device__ constexpr size_t warp_smem_floats(int k) {
-  return (size_t)heap_padded(k) * 32 + 128 + 2 * kQueueCap + 32 + 96;   // heap | stage | frontier | frames | soa
+  return (size_t)heap_padded(k) * 32 + 128 + 2 * kQueueCap + 32 + 96 + 8;   // heap | stage | frontier | frames | soa | worklist
 }
 
 struct GroupCtx {
@@ -28,6 +28,7 @@ struct GroupCtx {
   unsigned* qkey;       // shared: frontier lower bounds (float bits; non-negative => uint-ordered)
   unsigned* qnode;      // shared: frontier nodes
   unsigned* frames;     // shared: frame stack of the depth-first fallback
+  unsigned* work;       // shared: lane-mask worklist of traverse_group (8 entries)
   int kp;               // padded heap size
   bool valid;
   unsigned last_id;     // id of the most recently accepted candidate (find-closest-point uses it, k == 1)
@@ -328,6 +329,7 @@ __device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int war
   g.qnode = g.qkey + kQueueCap;
   g.frames = g.qnode + kQueueCap;
   g.soa = reinterpret_cast<float*>(g.frames + 32);
+  g.work = reinterpret_cast<unsigned*>(g.soa + 96);
   g.kp = kp;
   g.n_leaves = g.n_inner = g.n_inserts = g.n_fallback = g.n_purge = 0;
 }
@@ -347,6 +349,62 @@ __device__ __forceinline__ void group_bounds(GroupCtx& g) {
   }
   g.glx = lx; g.gly = ly; g.glz = lz; g.ghx = hx; g.ghy = hy; g.ghz = hz;
   g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
+}
+
+// ---- robust entry point: split incoherent groups --------------------------------------------------
+// A group is 32 consecutive points of a k-d refined Morton run. When the run straddles a jump of the
+// Z-curve (or the gap between two clusters) a leaf can hold points from two far-apart places. As a
+// QUERY group such a leaf is poison: its box covers everything in between, so every node passes the
+// group-level test and the lanes on the far side keep a huge radius until the random walk happens to
+// reach their real neighbourhood — measured: one such group runs for tens of milliseconds and, if it
+// is claimed late, the whole GPU waits for it (local phase of one rank 188 ms instead of 131 ms).
+// Fix: before traversing, cut the lane set at the largest gap along the widest axis whenever that gap
+// is more than half of the extent, recursively, and traverse each coherent sub-group on its own
+// (the other lanes are simply not valid during that pass). Exactness is unaffected.
+__device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1) {
+  const int lane = lane_id();
+  const unsigned all = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
+  int nwork = 1;
+  __syncwarp();
+  if (lane == 0) g.work[0] = all;
+  __syncwarp();
+  while (nwork > 0) {
+    const unsigned m = g.work[--nwork];
+    __syncwarp();
+    g.valid = (m >> lane) & 1u;
+    group_bounds(g);
+    // widest axis of this lane set, largest gap between consecutive coordinates along it
+    const float ex = g.ghx - g.glx, ey = g.ghy - g.gly, ez = g.ghz - g.glz;
+    const int axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
+    const float extent = axis == 0 ? ex : (axis == 1 ? ey : ez);
+    const float c = g.valid ? (axis == 0 ? g.qx : (axis == 1 ? g.qy : g.qz)) : INFINITY;
+    float succ = INFINITY;
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) {
+      const float cj = __shfl_sync(kFullMask, c, j);
+      if (cj > c) succ = fminf(succ, cj);
+    }
+    const float gap = (g.valid && succ < INFINITY) ? succ - c : 0.f;
+    const unsigned gbits = __float_as_uint(gap);
+    const unsigned gmax = __reduce_max_sync(kFullMask, gbits);
+    if (__popc(m) >= 2 && nwork <= 6 && __uint_as_float(gmax) > 0.5f * extent) {
+      const int wl = __ffs(__ballot_sync(kFullMask, gbits == gmax)) - 1;
+      const float cut = __shfl_sync(kFullMask, c, wl);
+      const unsigned left = __ballot_sync(kFullMask, g.valid && c <= cut);
+      const unsigned right = m & ~left;
+      if (left != 0u && right != 0u) {
+        if (lane == 0) { g.work[nwork] = right; g.work[nwork + 1] = left; }
+        nwork += 2;
+        __syncwarp();
+        continue;
+      }
+    }
+    // coherent enough: one pass. The group's own level-1 node is the natural seed only for the
+    // unsplit group; a split part looks for the node nearest to it.
+    const int seed = (m == all && own_seed_l1 != -2) ? own_seed_l1 : find_seed_l1(t, g);
+    traverse(t, g, seed);
+  }
+  g.valid = lane < cnt;
 }
 
 __device__ __forceinline__ void flush_stats(const GroupCtx& g, unsigned long long* stats) {
