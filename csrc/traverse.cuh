@@ -359,7 +359,7 @@ __device__ __forceinline__ void group_bounds(GroupCtx& g) {
 // reach their real neighbourhood — measured: one such group runs for tens of milliseconds and, if it
 // is claimed late, the whole GPU waits for it (local phase of one rank 188 ms instead of 131 ms).
 // Fix: before traversing, cut the lane set at the largest gap along the widest axis whenever that gap
-// is more than half of the extent, recursively, and traverse each coherent sub-group on its own
+// is more than two thirds of the extent, recursively, and traverse each coherent sub-group on its own
 // (the other lanes are simply not valid during that pass). Exactness is unaffected.
 __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1) {
   const int lane = lane_id();
@@ -387,7 +387,7 @@ __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, i
     const float gap = (g.valid && succ < INFINITY) ? succ - c : 0.f;
     const unsigned gbits = __float_as_uint(gap);
     const unsigned gmax = __reduce_max_sync(kFullMask, gbits);
-    if (__popc(m) >= 2 && nwork <= 6 && __uint_as_float(gmax) > 0.5f * extent) {
+    if (__popc(m) >= 2 && nwork <= 6 && __uint_as_float(gmax) > 0.66f * extent) {
       const int wl = __ffs(__ballot_sync(kFullMask, gbits == gmax)) - 1;
       const float cut = __shfl_sync(kFullMask, c, wl);
       const unsigned left = __ballot_sync(kFullMask, g.valid && c <= cut);
