@@ -161,10 +161,19 @@ struct Group {
   std::vector<float> heap;   // [k][32]
   int k;
   unsigned long long leaves = 0, inserts = 0, inner = 0;
+  unsigned active = 0xffffffffu;   // lanes taking part in the current pass (see traverse_group in traverse.cuh)
+  bool on(int lane) const { return lane < cnt && ((active >> lane) & 1u); }
   float top(int lane) const { return heap[lane]; }
   void refresh_max() {
     maxR2 = 0.f;
-    for (int l = 0; l < cnt; ++l) maxR2 = fmaxf(maxR2, top(l));
+    for (int l = 0; l < cnt; ++l) if (on(l)) maxR2 = fmaxf(maxR2, top(l));
+  }
+  void refresh_box() {
+    for (int a = 0; a < 3; ++a) { glo[a] = INFINITY; ghi[a] = -INFINITY; }
+    for (int l = 0; l < cnt; ++l) {
+      if (!on(l)) continue;
+      for (int a = 0; a < 3; ++a) { glo[a] = fminf(glo[a], q[l][a]); ghi[a] = fmaxf(ghi[a], q[l][a]); }
+    }
   }
 };
 
@@ -172,9 +181,10 @@ void leaf(const CpuTree& t, int64_t leaf_idx, Group& g) {
   const Box& b = t.boxes[0][leaf_idx];
   bool any = false;
   for (int l = 0; l < g.cnt && !any; ++l)
-    any = point_box_lb(g.q[l][0], g.q[l][1], g.q[l][2], b.lox, b.loy, b.loz, b.hix, b.hiy, b.hiz) < g.top(l);
+    any = g.on(l) && point_box_lb(g.q[l][0], g.q[l][1], g.q[l][2], b.lox, b.loy, b.loz, b.hix, b.hiy, b.hiz) < g.top(l);
   if (!any) return;
   for (int l = 0; l < g.cnt; ++l) {
+    if (!g.on(l)) continue;
     for (int j = 0; j < kGroup; ++j) {
       const Float4& p = t.pts[leaf_idx * kGroup + j];
       const float d2 = dist2(g.q[l][0], g.q[l][1], g.q[l][2], p.x, p.y, p.z);
@@ -337,21 +347,42 @@ extern "C" int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries
     for (int64_t gi = gb; gi < ge; ++gi) {
       g.cnt = (int)std::min<int64_t>(kGroup, qn - gi * kGroup);
       std::fill(g.heap.begin(), g.heap.end(), sent);
-      for (int a = 0; a < 3; ++a) { g.glo[a] = INFINITY; g.ghi[a] = -INFINITY; }
       for (int l = 0; l < g.cnt; ++l) {
         const Float4& p = qs[gi * kGroup + l];
         g.q[l][0] = p.x; g.q[l][1] = p.y; g.q[l][2] = p.z;
-        for (int a = 0; a < 3; ++a) {
-          g.glo[a] = fminf(g.glo[a], g.q[l][a]);
-          g.ghi[a] = fmaxf(g.ghi[a], g.q[l][a]);
-        }
       }
-      g.refresh_max();
       if (tree.levels > 0) {
         static const bool dfs = getenv("B200KNN_CPU_DFS") != nullptr;
         const int top = tree.levels - 1;
-        if (dfs) visit(tree, top, 0, (int)tree.boxes[top].size(), g);
-        else best_first(tree, g, queries == nullptr ? gi / kFanout : -1);
+        // Same lane-set splitting as traverse_group (traverse.cuh): cut at the largest gap along the
+        // widest axis while that gap exceeds two thirds of the extent; traverse the parts separately.
+        const unsigned all = g.cnt >= 32 ? 0xffffffffu : ((1u << g.cnt) - 1u);
+        std::vector<unsigned> work{all};
+        while (!work.empty()) {
+          const unsigned m = work.back();
+          work.pop_back();
+          g.active = m;
+          g.refresh_box();
+          g.refresh_max();
+          const float ext[3] = {g.ghi[0] - g.glo[0], g.ghi[1] - g.glo[1], g.ghi[2] - g.glo[2]};
+          const int axis = (ext[0] >= ext[1] && ext[0] >= ext[2]) ? 0 : (ext[1] >= ext[2] ? 1 : 2);
+          float best_gap = 0.f, cut = 0.f;
+          for (int l = 0; l < g.cnt; ++l) {
+            if (!g.on(l)) continue;
+            float succ = INFINITY;
+            for (int o = 0; o < g.cnt; ++o) if (g.on(o) && g.q[o][axis] > g.q[l][axis]) succ = fminf(succ, g.q[o][axis]);
+            if (succ < INFINITY && succ - g.q[l][axis] > best_gap) { best_gap = succ - g.q[l][axis]; cut = g.q[l][axis]; }
+          }
+          if (best_gap > 0.66f * ext[axis] && work.size() <= 6) {
+            unsigned left = 0;
+            for (int l = 0; l < g.cnt; ++l) if (g.on(l) && g.q[l][axis] <= cut) left |= 1u << l;
+            const unsigned right = m & ~left;
+            if (left && right) { work.push_back(right); work.push_back(left); continue; }
+          }
+          if (dfs) visit(tree, top, 0, (int)tree.boxes[top].size(), g);
+          else best_first(tree, g, (queries == nullptr && m == all) ? gi / kFanout : -1);
+        }
+        g.active = 0xffffffffu;
       }
       for (int l = 0; l < g.cnt; ++l) {
         uint32_t id;
