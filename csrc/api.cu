@@ -221,6 +221,7 @@ static void fill_local_only(RingParams& p, b200knn_index* idx, int k, float max_
   p.seq_base = 0;
   p.task_counter = idx->task_counter;
   p.stats = idx->stats_on ? idx->stats : nullptr;
+  p.allow_global_heap = 1;
 }
 
 int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, void* stream_) {

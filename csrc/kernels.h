@@ -85,6 +85,8 @@ struct RingParams {
   unsigned* result_ids;        // optional (single rank, k == 1): id of the closest point, 0xffffffff if none
   unsigned long long* task_counter;   // local, zeroed before launch
   unsigned long long* stats;   // optional [4]: leaves visited, candidates tested, heap inserts, inner nodes
+  int allow_global_heap;       // 1: k beyond the shared-memory limit may use a global-memory heap (allocates)
+  float* global_heaps;         // set by ring_launch on that fallback path
 };
 
 size_t ring_smem_bytes(int k, int warps_per_cta);

@@ -33,13 +33,22 @@ namespace b200knn {
 
 namespace {
 
+// GLOBAL_HEAP = false: the product path, heaps in shared memory (k <= ~1790).
+// GLOBAL_HEAP = true : fallback for larger k, one [kp][32] heap block per resident warp in global
+//                      memory (rows are coalesced 128-byte lines); everything else is unchanged.
+template <bool GLOBAL_HEAP>
 __global__ void __launch_bounds__(Q_MAX_WARPS * 32, 1)
-knn_ring_kernel(const RingParams p) {
+knn_ring_kernel_t(const RingParams p) {
   extern __shared__ __align__(16) float q_smem[];
   const int lane = lane_id();
   const int k = p.k;
   GroupCtx g;
-  group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k);
+  if constexpr (GLOBAL_HEAP) {
+    const size_t warp_global = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k, p.global_heaps + warp_global * (size_t)heap_padded(k) * 32);
+  } else {
+    group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k);
+  }
   const int kp = g.kp;
 
   const int R = p.R;
@@ -174,26 +183,49 @@ int group_pick_warps(int k, const void* kernel) {
 }
 
 size_t ring_smem_bytes(int k, int warps_per_cta) { return group_smem_bytes(k, warps_per_cta); }
-int ring_pick_warps_per_cta(int k) { return group_pick_warps(k, (const void*)knn_ring_kernel); }
+int ring_pick_warps_per_cta(int k) { return group_pick_warps(k, (const void*)knn_ring_kernel_t<false>); }
 
-int ring_launch(const RingParams& p, int num_sms, cudaStream_t stream) {
+int ring_launch(const RingParams& p_in, int num_sms, cudaStream_t stream) {
+  RingParams p = p_in;
   KNN_REQUIRE(p.k >= 1, "k must be >= 1");
-  const int warps = ring_pick_warps_per_cta(p.k);
-  KNN_REQUIRE(warps >= 1, "k too large for the shared-memory heap (k <= 1790)");
-  const size_t smem = ring_smem_bytes(p.k, warps);
-  KNN_CUDA_TRY(cudaFuncSetAttribute(knn_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int occ = 0;
-  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn_ring_kernel, warps * 32, smem));
-  KNN_REQUIRE(occ >= 1, "query kernel does not fit on an SM");
   const unsigned long long total = (unsigned long long)(p.step_end - p.step_begin) * p.groups_per_chunk;
   if (total == 0) return 0;
+  int warps = ring_pick_warps_per_cta(p.k);
+  if (warps >= 1) {
+    const size_t smem = ring_smem_bytes(p.k, warps);
+    KNN_CUDA_TRY(cudaFuncSetAttribute(knn_ring_kernel_t<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn_ring_kernel_t<false>, warps * 32, smem));
+    KNN_REQUIRE(occ >= 1, "query kernel does not fit on an SM");
+    unsigned long long want = (total + warps - 1) / warps;
+    unsigned long long cap = (unsigned long long)num_sms * occ;
+    const int grid = (int)(want < cap ? want : cap);
+    KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
+    knn_ring_kernel_t<false><<<grid, warps * 32, smem, stream>>>(p);
+    note_launch();
+    KNN_CUDA_TRY(cudaGetLastError());
+    return 0;
+  }
+  // k does not fit the shared-memory heap: heaps go to a stream-ordered global scratch buffer
+  KNN_REQUIRE(p.allow_global_heap, "k too large for the shared-memory heap (k <= 1790) on this path");
+  warps = 8;
+  const size_t smem = (size_t)warps * warp_smem_floats_noheap() * sizeof(float);
+  int occ = 0;
+  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn_ring_kernel_t<true>, warps * 32, smem));
+  KNN_REQUIRE(occ >= 1, "query kernel does not fit on an SM");
+  if (occ > 2) occ = 2;
   unsigned long long want = (total + warps - 1) / warps;
   unsigned long long cap = (unsigned long long)num_sms * occ;
   const int grid = (int)(want < cap ? want : cap);
+  const size_t heap_bytes = (size_t)grid * warps * heap_padded(p.k) * 32 * sizeof(float);
+  float* heaps = nullptr;
+  KNN_CUDA_TRY(cudaMallocAsync(&heaps, heap_bytes, stream));
+  p.global_heaps = heaps;
   KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
-  knn_ring_kernel<<<grid, warps * 32, smem, stream>>>(p);
+  knn_ring_kernel_t<true><<<grid, warps * 32, smem, stream>>>(p);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
+  KNN_CUDA_TRY(cudaFreeAsync(heaps, stream));
   return 0;
 }
 

@@ -319,11 +319,23 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
   }
 }
 
-// Carve one warp's slice of dynamic shared memory.
-__device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int warp, int lane, int k) {
+// Shared-memory floats per warp when the heap lives in GLOBAL memory (k too large for shared memory).
+__host__ __device__ constexpr size_t warp_smem_floats_noheap() { return 128 + 2 * kQueueCap + 32 + 96 + 8; }
+
+// Carve one warp's slice of dynamic shared memory. global_heap == nullptr: the heap is the first part
+// of the slice (the fast path). Otherwise the heap is this warp's [kp][32] block of `global_heap` and
+// shared memory only holds the staging/frontier areas.
+__device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int warp, int lane, int k,
+                                               float* global_heap = nullptr) {
   const int kp = heap_padded(k);
-  float* warp_base = smem + warp * warp_smem_floats(k);
-  g.heap = warp_base + lane;
+  float* warp_base;
+  if (global_heap == nullptr) {
+    warp_base = smem + warp * warp_smem_floats(k);
+    g.heap = warp_base + lane;
+  } else {
+    warp_base = smem + warp * warp_smem_floats_noheap() - (size_t)kp * 32;   // so the offsets below still apply
+    g.heap = global_heap + lane;
+  }
   g.stage = reinterpret_cast<float4*>(warp_base + (size_t)kp * 32);
   g.qkey = reinterpret_cast<unsigned*>(warp_base + (size_t)kp * 32 + 128);
   g.qnode = g.qkey + kQueueCap;

@@ -149,6 +149,13 @@ def test_knn_large_k_uses_fewer_warps(k):
     assert bit_equal(_knn(x, k), bruteforce(x, k=k))
 
 
+def test_knn_k_beyond_shared_memory_uses_global_heaps():
+    """k > ~1790 does not fit the shared-memory heap: the kernel variant with heaps in global memory
+    must give the same bits (the reference supports any k that fits device memory)."""
+    x = gen.uniform(6000, seed=77)
+    assert bit_equal(_knn(x, 2000), bruteforce(x, k=2000))
+
+
 def test_knn_query_external_points():
     from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
     x = gen.uniform(50_000, seed=8)
