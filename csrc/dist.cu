@@ -46,6 +46,7 @@ struct b200knn_dist {
   char* peer[B200KNN_MAX_RANKS] = {};
   size_t bump = 0;
   unsigned barrier_seq = 0;     // device barrier sequence number; identical on all ranks
+  unsigned coll_seq = 0;        // device collective sequence number; identical on all ranks
   unsigned long long* task_counter = nullptr;
 
   int allgather(const void* send, void* recv, int64_t nbytes) {
@@ -105,9 +106,16 @@ int ensure_heap(b200knn_dist* d, size_t need) {
   return 0;
 }
 
-// The first bytes of the symmetric heap hold the barrier flags (one unsigned per peer); they persist
-// across calls, everything after them is re-carved by every call.
-constexpr size_t kHeapReserved = 256;
+// The first bytes of the symmetric heap persist across calls; everything after them is re-carved by
+// every call:
+//   [0, 256)       barrier flags, one unsigned per peer
+//   [256, 512)     collective flags, [parity][peer]
+//   [512, 4608)    collective mailboxes, [parity][peer][kCollWords]
+constexpr size_t kCollFlagsOff = 256;
+constexpr size_t kCollDataOff = 512;
+constexpr size_t kHeapReserved = kCollDataOff + 2 * (size_t)kMaxRanks * kCollWords * sizeof(unsigned);
+static_assert(2 * kMaxRanks * sizeof(unsigned) <= kCollDataOff - kCollFlagsOff, "collective flags overflow their area");
+static_assert(kHeapReserved % 256 == 0, "reserved area keeps the 256-byte alignment of what follows");
 
 size_t pv_heap_need(int k, int Gc) {
   return kHeapReserved + 2 * align256((size_t)Gc * pv_slot_bytes(k)) + 4 * 256;
@@ -126,6 +134,30 @@ int device_barrier(b200knn_dist* d, cudaStream_t stream) {
   bp.local_flags = reinterpret_cast<const unsigned*>(d->base);
   for (int r = 0; r < d->world; ++r) bp.peer_flags[r] = reinterpret_cast<unsigned*>(d->peer[r]);
   return dev_barrier_launch(bp, stream);
+}
+
+// All-gather (op = kCollGather: recv gets R * words words) or int64 all-reduce (recv gets words / 2
+// elements) of device-resident values, enqueued on `stream`. Collective; same arguments on every rank.
+int device_collective(b200knn_dist* d, const void* d_send, int words, int op, void* d_recv, cudaStream_t stream) {
+  DevCollParams cp;
+  memset(&cp, 0, sizeof(cp));
+  cp.R = d->world;
+  cp.rank = d->rank;
+  cp.words = words;
+  cp.op = op;
+  cp.seq = ++d->coll_seq;
+  const size_t par = cp.seq & 1u;
+  const size_t foff = kCollFlagsOff + par * kMaxRanks * sizeof(unsigned);
+  const size_t doff = kCollDataOff + par * (size_t)kMaxRanks * kCollWords * sizeof(unsigned);
+  for (int r = 0; r < d->world; ++r) {
+    cp.peer_flags[r] = reinterpret_cast<unsigned*>(d->peer[r] + foff);
+    cp.peer_data[r] = reinterpret_cast<unsigned*>(d->peer[r] + doff);
+  }
+  cp.local_flags = reinterpret_cast<const unsigned*>(d->base + foff);
+  cp.local_data = reinterpret_cast<const unsigned*>(d->base + doff);
+  cp.send = static_cast<const unsigned*>(d_send);
+  cp.recv = static_cast<unsigned*>(d_recv);
+  return dev_collective_launch(cp, stream);
 }
 
 struct PvPlan { int Gc; int C; int64_t max_groups; };
@@ -307,6 +339,12 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   const int64_t my_groups = idx->groups();
   if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
 
+  // the per-chunk vote "does anybody have groups that must travel?" is a device-side all-gather of
+  // the pending counters (B200KNN_HOST_VOTE=1: through the bootstrap, as a cross-check)
+  const bool host_vote = getenv("B200KNN_HOST_VOTE") != nullptr;
+  int* d_votes = nullptr;
+  if (R > 1 && !host_vote) KNN_CUDA_TRY(cudaMallocAsync(&d_votes, (size_t)R * sizeof(int), stream));
+
   int rc;
   for (int c = 0; c < pl.C; ++c) {
     KNN_CUDA_TRY(cudaMemsetAsync(p.pending_count, 0, sizeof(int), stream));
@@ -320,12 +358,21 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     if (R == 1) continue;
     // any work for the exchange at all? (one tiny allgather per chunk saves 2(R-1) fences when not)
     int my_pending = 0;
-    KNN_CUDA_TRY(cudaMemcpyAsync(&my_pending, p.pending_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
-    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-    const double tl1 = now_ms();
-    if (rep) rep->ms_local_phase += tl1 - tl0;
     std::vector<int> all_pending(R);
-    if (d->allgather(&my_pending, all_pending.data(), sizeof(int))) { set_last_error("bootstrap allgather failed"); return -3; }
+    double tl1;
+    if (host_vote) {
+      KNN_CUDA_TRY(cudaMemcpyAsync(&my_pending, p.pending_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
+      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      tl1 = now_ms();
+      if (d->allgather(&my_pending, all_pending.data(), sizeof(int))) { set_last_error("bootstrap allgather failed"); return -3; }
+    } else {
+      if ((rc = device_collective(d, p.pending_count, 1, kCollGather, d_votes, stream))) return rc;
+      KNN_CUDA_TRY(cudaMemcpyAsync(all_pending.data(), d_votes, (size_t)R * sizeof(int), cudaMemcpyDeviceToHost, stream));
+      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      tl1 = now_ms();
+      my_pending = all_pending[me];
+    }
+    if (rep) rep->ms_local_phase += tl1 - tl0;
     int64_t total_pending = 0;
     for (int v : all_pending) total_pending += v;
     if (rep) { rep->pending_groups += my_pending; rep->chunks += 1; }
@@ -351,6 +398,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     if (rep) { KNN_CUDA_TRY(cudaStreamSynchronize(stream)); rep->ms_rounds += now_ms() - tr0; }
   }
   KNN_CUDA_TRY(cudaFreeAsync(d_regions, stream));
+  if (d_votes) KNN_CUDA_TRY(cudaFreeAsync(d_votes, stream));
   return 0;
 }
 
@@ -669,6 +717,33 @@ void b200knn_dist_destroy(b200knn_dist* d) {
 }
 
 int64_t b200knn_dist_heap_bytes(const b200knn_dist* d) { return d ? (int64_t)d->bytes : 0; }
+
+int b200knn_dist_allgather_dev(b200knn_dist* d, const void* d_send, int nbytes, void* d_recv, void* stream) {
+  KNN_REQUIRE(d && d_send && d_recv, "dist_allgather_dev: NULL argument");
+  KNN_REQUIRE(nbytes >= 4 && nbytes % 4 == 0 && nbytes <= B200KNN_DEV_COLLECTIVE_MAX_BYTES,
+              "dist_allgather_dev: nbytes must be a multiple of 4 in [4, 128]");
+  if (d->world == 1) {
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_recv, d_send, (size_t)nbytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+  }
+  int rc;
+  if ((rc = ensure_heap(d, kHeapReserved))) return rc;
+  return device_collective(d, d_send, nbytes / 4, kCollGather, d_recv, (cudaStream_t)stream);
+}
+
+int b200knn_dist_allreduce_dev(b200knn_dist* d, const int64_t* d_send, int count, int op, int64_t* d_recv, void* stream) {
+  KNN_REQUIRE(d && d_send && d_recv, "dist_allreduce_dev: NULL argument");
+  KNN_REQUIRE(count >= 1 && count * 8 <= B200KNN_DEV_COLLECTIVE_MAX_BYTES, "dist_allreduce_dev: count must be in [1, 16]");
+  KNN_REQUIRE(op == B200KNN_OP_MAX || op == B200KNN_OP_SUM || op == B200KNN_OP_MIN, "dist_allreduce_dev: unknown op");
+  if (d->world == 1) {
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_recv, d_send, (size_t)count * 8, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+  }
+  int rc;
+  if ((rc = ensure_heap(d, kHeapReserved))) return rc;
+  const int kop = op == B200KNN_OP_MAX ? kCollMaxI64 : (op == B200KNN_OP_SUM ? kCollSumI64 : kCollMinI64);
+  return device_collective(d, d_send, 2 * count, kop, d_recv, (cudaStream_t)stream);
+}
 
 int b200knn_dist_knn(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64_t global_begin, int k,
                      float max_radius, int mode, int groups_per_chunk, float* d_out, void* stream_,

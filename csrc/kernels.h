@@ -139,6 +139,26 @@ struct DevBarrierParams {
 };
 int dev_barrier_launch(const DevBarrierParams& p, cudaStream_t stream);
 
+// Small device-side collectives over the symmetric heap: every rank pushes up to
+// kCollWords 32-bit words into a mailbox on every peer and raises a sequence flag there, then reads
+// its own mailboxes. Replaces MPI_Allgather / MPI_Allreduce on host staging buffers
+// (/root/reference/prePartitionedDataVariant.cu:253-262, 309-313) for values that are produced and
+// consumed on the device; the host never sees the payload unless it asks for it.
+constexpr int kCollWords = 32;
+enum CollOp { kCollGather = 0, kCollMaxI64 = 1, kCollSumI64 = 2, kCollMinI64 = 3 };
+struct DevCollParams {
+  unsigned* peer_flags[kMaxRanks];   // every rank's flag array of this parity; slot [rank] is ours there
+  unsigned* peer_data[kMaxRanks];    // every rank's mailboxes of this parity; [rank * kCollWords ..] is ours
+  const unsigned* local_flags;       // slot [r] is raised by rank r
+  const unsigned* local_data;        // mailbox [r] is filled by rank r
+  const unsigned* send;              // `words` 32-bit words (device)
+  unsigned* recv;                    // gather: R * words words; reductions: words words (int64 pairs)
+  int words, op;
+  unsigned seq;
+  int rank, R;
+};
+int dev_collective_launch(const DevCollParams& p, cudaStream_t stream);
+
 struct RedistributeParams {
   const float* xyz;            // local points, caller order
   const uint32_t* order;       // order[i] = caller index of the i-th point in global Morton order

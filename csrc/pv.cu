@@ -234,6 +234,50 @@ __global__ void dev_barrier_kernel(const DevBarrierParams p) {
   }
 }
 
+// All-gather / all-reduce of a few words per rank as one stream-ordered kernel. Warp w talks to rank w:
+// it pushes this rank's words into mailbox [rank] over there, raises flag [rank] there, then waits
+// for rank w's flag here and picks up rank w's words. Mailboxes are double-buffered by the parity of
+// the sequence number (the host alternates the pointers): a rank can be at most one collective
+// ahead of the slowest one, because finishing collective s needs everybody's contribution to s.
+__global__ void dev_collective_kernel(const DevCollParams p) {
+  __shared__ unsigned gathered[kMaxRanks][kCollWords];
+  const int w = threadIdx.x >> 5, lane = lane_id();
+  if (w < p.R) {
+    if (lane < p.words) {
+      volatile unsigned* box = p.peer_data[w] + (size_t)p.rank * kCollWords;
+      box[lane] = p.send[lane];
+    }
+    __threadfence_system();
+    __syncwarp();
+    if (lane == 0) {
+      st_release_sys(p.peer_flags[w] + p.rank, p.seq);
+      wait_flag_ge(p.local_flags + w, p.seq);
+    }
+    __syncwarp();
+    unsigned v = 0;
+    if (lane < p.words) v = __ldcg(p.local_data + (size_t)w * kCollWords + lane);
+    if (p.op == kCollGather) {
+      if (lane < p.words) p.recv[(size_t)w * p.words + lane] = v;
+    } else {
+      gathered[w][lane] = v;
+    }
+  }
+  if (p.op == kCollGather) return;
+  __syncthreads();
+  const int e = threadIdx.x;                       // one thread per int64 element
+  if (e < p.words / 2) {
+    auto at = [&](int r) {
+      return (long long)(((unsigned long long)gathered[r][2 * e + 1] << 32) | gathered[r][2 * e]);
+    };
+    long long acc = at(0);
+    for (int r = 1; r < p.R; ++r) {
+      const long long x = at(r);
+      acc = p.op == kCollSumI64 ? acc + x : (p.op == kCollMaxI64 ? (x > acc ? x : acc) : (x < acc ? x : acc));
+    }
+    reinterpret_cast<long long*>(p.recv)[e] = acc;
+  }
+}
+
 __global__ void pv_publish_kernel(const int* __restrict__ out_count, int* __restrict__ peer_inbox_count) {
   if (threadIdx.x == 0) *peer_inbox_count = *out_count;
 }
@@ -373,6 +417,16 @@ int pv_push_launch(const char* pending, const int* pending_count, int k, const B
 
 int dev_barrier_launch(const DevBarrierParams& p, cudaStream_t stream) {
   dev_barrier_kernel<<<1, 32, 0, stream>>>(p);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int dev_collective_launch(const DevCollParams& p, cudaStream_t stream) {
+  KNN_REQUIRE(p.R >= 1 && p.R <= kMaxRanks, "dev_collective: bad world size");
+  KNN_REQUIRE(p.words >= 1 && p.words <= kCollWords, "dev_collective: payload must be 1..32 words");
+  KNN_REQUIRE(p.op == kCollGather || p.words % 2 == 0, "dev_collective: reductions work on int64 elements");
+  dev_collective_kernel<<<1, 32 * p.R, 0, stream>>>(p);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;

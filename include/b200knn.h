@@ -191,6 +191,19 @@ int b200knn_dist_knn(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
                      float max_radius, int mode, int groups_per_chunk, float* d_out, void* stream,
                      b200knn_dist_report* report_or_null);
 
+/* Small device-side collectives over the engine's symmetric heap: payload and result live in device
+ * memory, the exchange is one kernel enqueued on `stream` (peer stores + sequence flags), the host
+ * does not wait. Role of MPI_Allgather / MPI_Allreduce on counts, boxes and radii
+ * (prePartitionedDataVariant.cu:253-262, 309-313) for values produced and consumed on the GPU.
+ * Collective: every rank calls with the same sizes, in the same order, one GPU per rank.
+ *   allgather_dev: d_recv gets world * nbytes bytes in rank order; nbytes a multiple of 4, <= 128.
+ *   allreduce_dev: element-wise over `count` <= 16 int64 values. */
+#define B200KNN_DEV_COLLECTIVE_MAX_BYTES 128
+enum { B200KNN_OP_MAX = 0, B200KNN_OP_SUM = 1, B200KNN_OP_MIN = 2 };
+int b200knn_dist_allgather_dev(b200knn_dist* d, const void* d_send, int nbytes, void* d_recv, void* stream);
+int b200knn_dist_allreduce_dev(b200knn_dist* d, const int64_t* d_send, int count, int op, int64_t* d_recv,
+                               void* stream);
+
 /* ---- CPU side (no GPU needed): oracle and mirror engine ----------------------------------------
  * cpu_bruteforce: exact O(nq*n) k-th distance with the canonical fp32 expression
  *   fmaf(dz,dz, fmaf(dx,dx, dy*dy)), d = query - point  (SURVEY.md fact 7); the test oracle.

@@ -130,6 +130,33 @@ class DistKnn:
         self.last_report = rep.as_dict()
         return out
 
+    def allgather_dev(self, send: torch.Tensor) -> torch.Tensor:
+        """Device-side all-gather of a small CUDA tensor (<= 128 bytes, 4-byte multiple): result is
+        ``[world, *send.shape]``, produced by one kernel on the current stream (no host sync)."""
+        send = send.contiguous()
+        nbytes = send.numel() * send.element_size()
+        out = torch.empty((self.world,) + tuple(send.shape), dtype=send.dtype, device=send.device)
+        fn = lib().b200knn_dist_allgather_dev
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        fn.restype = C.c_int
+        with torch.cuda.device(send.device):
+            check(fn(self._h, send.data_ptr(), nbytes, out.data_ptr(), _stream_ptr()), "dist_allgather_dev")
+        return out
+
+    def allreduce_dev(self, send: torch.Tensor, op: str = "max") -> torch.Tensor:
+        """Device-side element-wise all-reduce (max / sum / min) of up to 16 int64 values."""
+        if send.dtype != torch.int64:
+            raise TypeError("allreduce_dev works on int64 tensors")
+        send = send.contiguous()
+        out = torch.empty_like(send)
+        fn = lib().b200knn_dist_allreduce_dev
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        fn.restype = C.c_int
+        with torch.cuda.device(send.device):
+            check(fn(self._h, send.data_ptr(), send.numel(), {"max": 0, "sum": 1, "min": 2}[op], out.data_ptr(),
+                     _stream_ptr()), "dist_allreduce_dev")
+        return out
+
     def close(self) -> None:
         if self._h.value:
             fn = lib().b200knn_dist_destroy

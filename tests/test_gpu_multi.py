@@ -30,3 +30,9 @@ def test_distributed_driver_all_modes_match_oracle():
     n = min(torch.cuda.device_count(), 8)
     out = _torchrun("mp_dist_worker.py", n)
     assert out.returncode == 0 and "MP_DIST_OK" in out.stdout, out.stdout[-4000:]
+
+
+def test_device_collectives_match_torch_distributed():
+    n = min(torch.cuda.device_count(), 8)
+    out = _torchrun("mp_coll_worker.py", n, timeout=600)
+    assert out.returncode == 0 and "MP_COLL_OK" in out.stdout, out.stdout[-4000:]
