@@ -77,6 +77,16 @@ void keep_pool_memory(int device) {
   }
   done.fetch_or(bit);
 }
+
+// Convergent fill of fresh heaps (traverse.cuh::fill_leaf): on by default (measured 58.4 -> 54.5 ms for
+// 16 M points, k = 100); B200KNN_FILL=0 switches back to sifting every candidate.
+bool convergent_fill_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200KNN_FILL");
+    return e ? (e[0] != '0') : true;
+  }();
+  return on;
+}
 }  // namespace b200knn
 
 extern "C" {
@@ -209,6 +219,7 @@ int b200knn_index_copy_boxes(const b200knn_index* idx, int level, float* host_bo
 
 static void fill_local_only(RingParams& p, b200knn_index* idx, int k, float max_radius) {
   memset(&p, 0, sizeof(p));
+  p.fill = convergent_fill_enabled() ? 1 : 0;
   p.tree = idx->view();
   p.k = k;
   p.sentinel = sentinel_d2(max_radius);

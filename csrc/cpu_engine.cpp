@@ -13,6 +13,8 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <numeric>
@@ -44,6 +46,18 @@ void parallel_for(int64_t n, int num_threads, F f) {
 }
 
 std::atomic<unsigned long long> g_cpu_stats[4];   // leaves, candidates, inserts, inner nodes
+
+// Optional trace for offline modelling of the insertion phase (tools/sift_model.py). With
+// B200KNN_CPU_TRACE=<file> and a single thread, every 64th group appends one record per visited leaf:
+//   int64 group, int32 leaves so far, int32 lanes in the group, float top[32] (k-th distance per lane
+//   before the leaf), float d2[32][32] (lane-major squared distances to the leaf's points, +inf padding).
+FILE* trace_file() {
+  static FILE* f = [] {
+    const char* path = getenv("B200KNN_CPU_TRACE");
+    return path && *path ? fopen(path, "wb") : (FILE*)nullptr;
+  }();
+  return f;
+}
 
 struct CpuTree {
   std::vector<Float4> pts;                 // sorted, padded to groups*32 with +inf points
@@ -162,6 +176,7 @@ struct Group {
   int k;
   unsigned long long leaves = 0, inserts = 0, inner = 0;
   unsigned active = 0xffffffffu;   // lanes taking part in the current pass (see traverse_group in traverse.cuh)
+  int64_t trace_id = -1;           // >= 0: this group is written to the trace file
   bool on(int lane) const { return lane < cnt && ((active >> lane) & 1u); }
   float top(int lane) const { return heap[lane]; }
   void refresh_max() {
@@ -183,6 +198,22 @@ void leaf(const CpuTree& t, int64_t leaf_idx, Group& g) {
   for (int l = 0; l < g.cnt && !any; ++l)
     any = g.on(l) && point_box_lb(g.q[l][0], g.q[l][1], g.q[l][2], b.lox, b.loy, b.loz, b.hix, b.hiy, b.hiz) < g.top(l);
   if (!any) return;
+  if (g.trace_id >= 0) {
+    FILE* f = trace_file();
+    const int32_t head[2] = {(int32_t)g.leaves, (int32_t)g.cnt};
+    float tops[kGroup], d2[kGroup][kGroup];
+    for (int l = 0; l < kGroup; ++l) {
+      tops[l] = g.on(l) ? g.top(l) : -INFINITY;       // lanes that sit this pass out accept nothing
+      for (int j = 0; j < kGroup; ++j) {
+        const Float4& p = t.pts[leaf_idx * kGroup + j];
+        d2[l][j] = l < g.cnt ? dist2(g.q[l][0], g.q[l][1], g.q[l][2], p.x, p.y, p.z) : INFINITY;
+      }
+    }
+    fwrite(&g.trace_id, sizeof(int64_t), 1, f);
+    fwrite(head, sizeof(head), 1, f);
+    fwrite(tops, sizeof(tops), 1, f);
+    fwrite(d2, sizeof(d2), 1, f);
+  }
   for (int l = 0; l < g.cnt; ++l) {
     if (!g.on(l)) continue;
     for (int j = 0; j < kGroup; ++j) {
@@ -346,6 +377,7 @@ extern "C" int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries
     g.heap.resize((size_t)k * kGroup);
     for (int64_t gi = gb; gi < ge; ++gi) {
       g.cnt = (int)std::min<int64_t>(kGroup, qn - gi * kGroup);
+      g.trace_id = (num_threads == 1 && gi % 64 == 0 && trace_file()) ? gi : -1;
       std::fill(g.heap.begin(), g.heap.end(), sent);
       for (int l = 0; l < g.cnt; ++l) {
         const Float4& p = qs[gi * kGroup + l];
@@ -393,5 +425,6 @@ extern "C" int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries
     g_cpu_stats[0] += g.leaves; g_cpu_stats[1] += g.leaves * kGroup;
     g_cpu_stats[2] += g.inserts; g_cpu_stats[3] += g.inner;
   });
+  if (num_threads == 1 && trace_file()) fflush(trace_file());
   return 0;
 }

@@ -87,7 +87,9 @@ struct RingParams {
   unsigned long long* stats;   // optional [4]: leaves visited, candidates tested, heap inserts, inner nodes
   int allow_global_heap;       // 1: k beyond the shared-memory limit may use a global-memory heap (allocates)
   float* global_heaps;         // set by ring_launch on that fallback path
+  int fill;                    // 1: fresh heaps take their first floor(k/32) leaves by plain appends + heapify
 };
+bool convergent_fill_enabled();   // api.cu: host-side switch (B200KNN_FILL=0/1), read once
 
 size_t ring_smem_bytes(int k, int warps_per_cta);
 int ring_pick_warps_per_cta(int k);
@@ -103,6 +105,7 @@ struct PvMainParams {
   int k;
   float sentinel;
   int phase;                   // 0 = LOCAL (home groups, fresh heaps), 1 = SERVE (visiting groups from the inbox)
+  int fill;                    // as RingParams::fill, LOCAL phase only
   int R, rank;
   const Box* region_boxes;     // [R][kRegionBoxes]: every rank's region = the boxes of the deepest tree
                                // level that has at most kRegionBoxes nodes

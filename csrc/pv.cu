@@ -89,7 +89,7 @@ pv_main_kernel(const PvMainParams p) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;
       const int own_seed = (p.phase == 0 && p.home_is_tree)
                                ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1) : -2;
-      traverse_group(p.tree, g, cnt, own_seed);
+      traverse_group(p.tree, g, cnt, own_seed, (p.phase == 0 && p.fill) ? k / kGroup : 0);
     }
 
     if (p.phase == 0) {

@@ -108,7 +108,7 @@ knn_ring_kernel_t(const RingParams p) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;   // heap padding
       // seed = the level-1 node holding the group's own leaf (self queries at home), else the nearest (-2)
       const int own_seed = (hop == 0 && p.home_is_tree) ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1) : -2;
-      traverse_group(p.tree, g, cnt, own_seed);
+      traverse_group(p.tree, g, cnt, own_seed, (hop == 0 && p.fill) ? k / kGroup : 0);
     }
 
     // ------------------------------------------------------------------ output

@@ -35,6 +35,23 @@ struct GroupCtx {
   unsigned n_leaves, n_inner, n_inserts, n_fallback, n_purge;
 };
 
+// Sift e down from position i. Children of i: 4i+1..4i+4, all present (padding is -inf).
+__device__ __forceinline__ void heap_sift_down(float* h, int kp, int i, float e) {
+  for (;;) {
+    const int c0 = 4 * i + 1;
+    if (c0 >= kp) break;
+    const float a0 = h[c0 * 32], a1 = h[(c0 + 1) * 32], a2 = h[(c0 + 2) * 32], a3 = h[(c0 + 3) * 32];
+    const float m01 = fmaxf(a0, a1), m23 = fmaxf(a2, a3);
+    const int i01 = a1 > a0 ? c0 + 1 : c0, i23 = a3 > a2 ? c0 + 3 : c0 + 2;
+    const float best = fmaxf(m01, m23);
+    const int bi = m23 > m01 ? i23 : i01;
+    if (!(best > e)) break;
+    h[i * 32] = best;
+    i = bi;
+  }
+  h[i * 32] = e;
+}
+
 // Replace the root (precondition e < root) and sift down. Children of i: 4i+1..4i+4, all present.
 __device__ __forceinline__ float heap_replace_padded(float* h, int kp, float e) {
   int i = 0;
@@ -117,6 +134,50 @@ __device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cn
   __syncwarp();
   g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
   ++g.n_leaves;
+}
+
+// ---- convergent fill ------------------------------------------------------------------------------
+// A fresh heap (all entries = sentinel) accepts its first k candidates whatever they are, and every
+// one of them would pay a full-depth sift (the new value is smaller than the sentinels below it).
+// Instead the first floor(k/32) leaves of a fresh group are appended as they come — 32 plain stores
+// per lane, no test, no divergence — and one Floyd heapify turns the array into the heap. Values are
+// clamped to the sentinel, so a max-radius cut-off and +inf padding points behave as "no candidate".
+// The result is the same set of k smallest distances, hence bit-identical.
+__device__ __forceinline__ void fill_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g, int pos0) {
+  const int lane = lane_id();
+  float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
+  if (lane < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane);
+  g.soa[lane] = p.x;
+  g.soa[32 + lane] = p.y;
+  g.soa[64 + lane] = p.z;
+  __syncwarp();
+  if (g.valid) {
+    const float sent = g.top;          // nothing has been sifted yet: top is still the sentinel
+    const unsigned long long qx2 = pack2(g.qx, g.qx), qy2 = pack2(g.qy, g.qy), qz2 = pack2(g.qz, g.qz);
+    const unsigned long long* sx = reinterpret_cast<const unsigned long long*>(g.soa);
+    const unsigned long long* sy = reinterpret_cast<const unsigned long long*>(g.soa + 32);
+    const unsigned long long* sz = reinterpret_cast<const unsigned long long*>(g.soa + 64);
+    float* h = g.heap + (size_t)pos0 * 32;
+#pragma unroll
+    for (int jj = 0; jj < kGroup / 2; ++jj) {
+      const unsigned long long dx = sub2(qx2, sx[jj]), dy = sub2(qy2, sy[jj]), dz = sub2(qz2, sz[jj]);
+      const unsigned long long d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
+      h[(2 * jj) * 32] = fminf(__uint_as_float((unsigned)(d2 & 0xffffffffull)), sent);
+      h[(2 * jj + 1) * 32] = fminf(__uint_as_float((unsigned)(d2 >> 32)), sent);
+    }
+    g.n_inserts += kGroup;
+  }
+  __syncwarp();
+  ++g.n_leaves;
+}
+
+__device__ __forceinline__ void fill_finish(GroupCtx& g) {
+  if (g.valid) {
+    for (int start = (g.kp - 2) / 4; start >= 0; --start) heap_sift_down(g.heap, g.kp, start, g.heap[start * 32]);
+    g.top = g.heap[0];
+  }
+  __syncwarp();
+  g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
 }
 
 // Exact per-query test against the leaf box; skip the leaf if no lane can improve.
@@ -224,8 +285,11 @@ __device__ __forceinline__ void frontier_expand(const TreeView& t, int level, in
   __syncwarp();
 }
 
-__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1) {
+// fill_leaves > 0: the valid lanes' heaps are fresh; the first fill_leaves leaves that come up are
+// appended without a test (see fill_leaf). fill_leaves * 32 <= k.
+__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves = 0) {
   const int lane = lane_id();
+  int fill_pos = 0;
   unsigned* fr = g.frames;
   const int top_level = t.levels - 1;
   int depth = -1, qcount = 0;
@@ -315,8 +379,15 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       lx = a.x; ly = a.y; lz = a.z; hx = b.x; hy = b.y; hz = b.z;
       cnt = __float_as_int(a.w);
     }
+    if (fill_leaves > 0) {
+      fill_leaf(t, leaf, cnt, g, fill_pos);
+      fill_pos += kGroup;
+      if (--fill_leaves == 0) fill_finish(g);
+      continue;
+    }
     maybe_leaf(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
   }
+  if (fill_pos > 0 && fill_leaves > 0) fill_finish(g);    // the tree ran out of leaves during the fill
 }
 
 // Shared-memory floats per warp when the heap lives in GLOBAL memory (k too large for shared memory).
@@ -373,7 +444,9 @@ __device__ __forceinline__ void group_bounds(GroupCtx& g) {
 // Fix: before traversing, cut the lane set at the largest gap along the widest axis whenever that gap
 // is more than two thirds of the extent, recursively, and traverse each coherent sub-group on its own
 // (the other lanes are simply not valid during that pass). Exactness is unaffected.
-__device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1) {
+// fill_leaves: see traverse(); pass k / 32 for a group whose heaps are all fresh, else 0.
+__device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1,
+                                               int fill_leaves = 0) {
   const int lane = lane_id();
   const unsigned all = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
   int nwork = 1;
@@ -414,7 +487,7 @@ __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, i
     // coherent enough: one pass. The group's own level-1 node is the natural seed only for the
     // unsplit group; a split part looks for the node nearest to it.
     const int seed = (m == all && own_seed_l1 != -2) ? own_seed_l1 : find_seed_l1(t, g);
-    traverse(t, g, seed);
+    traverse(t, g, seed, fill_leaves);
   }
   g.valid = lane < cnt;
 }

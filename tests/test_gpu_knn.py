@@ -122,6 +122,28 @@ def test_knn_max_radius(r):
     assert bit_equal(_knn(x, 16, r), bruteforce(x, k=16, max_radius=r))
 
 
+def test_knn_max_radius_with_k_spanning_several_leaves():
+    """k >= 32 takes the convergent-fill path when it is enabled: values beyond the cut-off must be
+    clamped to r*r exactly as a sifted insert would have refused them."""
+    x = gen.uniform(20_000, seed=17)
+    for k, r in ((64, 0.05), (100, 0.02), (40, 0.3)):
+        assert bit_equal(_knn(x, k, r), bruteforce(x, k=k, max_radius=r))
+
+
+def test_dist_engine_world1_every_mode_equals_oracle():
+    """The distributed driver with a single rank (no process group): exercises the culled-exchange
+    kernels' LOCAL phase and the redistribution pipeline on one GPU."""
+    from mpi_cuda_largescaleknn_b200.parallel.dist import DistKnn
+    x = gen.uniform(60_000, seed=31)
+    sel = np.arange(0, len(x), 37)
+    ref = bruteforce(x, queries=x[sel], k=40)
+    eng = DistKnn()
+    for mode in ("ring", "prepartitioned", "redistribute", "auto"):
+        got = eng.knn(torch.from_numpy(x).to(_dev()), 40, mode=mode).cpu().numpy()
+        assert bit_equal(got[sel], ref), mode
+    eng.close()
+
+
 def test_knn_clustered_duplicates():
     x = np.concatenate([gen.clustered_surface(20_000, seed=2), np.zeros((100, 3), np.float32),
                         np.full((70, 3), 0.25, np.float32)])
