@@ -215,6 +215,8 @@ def main() -> int:
     print(f"{len(groups)} groups, {sum(len(g[1]) for g in groups) / len(groups):.1f} leaves per group, k={args.k}")
     schemes = [("per_leaf", lambda g: run_per_leaf(g, args.k)),
                ("per_leaf+fill", lambda g: run_per_leaf(g, args.k, fill=True)),
+               ("fill+pairs", lambda g: run_per_leaf(g, args.k, merge=2, fill=True)),
+               ("fill+quads", lambda g: run_per_leaf(g, args.k, merge=4, fill=True)),
                ("leaf_pairs", lambda g: run_per_leaf(g, args.k, merge=2)),
                ("leaf_quads", lambda g: run_per_leaf(g, args.k, merge=4)),
                ("deferred_48", lambda g: run_deferred(g, args.k, 48)),
