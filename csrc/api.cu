@@ -300,6 +300,75 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   return 0;
 }
 
+// k nearest neighbours with ids: pass 1 = the k-th-distance kernel with raw output, pass 2 = collect
+// (neighbors.cu). d_queries == NULL: every indexed point is a query (rows in the caller's point order;
+// the index must have been created without explicit ids, so that id - id_offset is the position).
+int b200knn_knn_neighbors(b200knn_index* idx, const float* d_queries, int64_t nq, int k, float max_radius,
+                          int32_t* d_out_ids, float* d_out_dist, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  NvtxRange range("b200knn:knn_neighbors");
+  KNN_REQUIRE(idx && d_out_ids && d_out_dist, "knn_neighbors: NULL argument");
+  KNN_REQUIRE(k >= 1, "knn_neighbors: k must be >= 1");
+  const bool self = d_queries == nullptr;
+  if (self) nq = idx->n;
+  KNN_REQUIRE(nq >= 0 && nq < (int64_t)0x7fffffff - 64, "knn_neighbors: nq out of range");
+  if (nq == 0) return 0;
+  const int64_t groups = div_up(nq, kGroup);
+  uint64_t *keys = nullptr, *keys_tmp = nullptr;
+  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr;
+  Float4* qsorted = nullptr;
+  float* limits = nullptr;
+  int rc;
+  KNN_CUDA_TRY(cudaMallocAsync(&limits, groups * kGroup * sizeof(float), stream));
+  if (!self) {
+    KNN_CUDA_TRY(cudaMallocAsync(&keys, nq * sizeof(uint64_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, nq * sizeof(uint64_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&vals, nq * sizeof(uint32_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, nq * sizeof(uint32_t), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(nq), stream));
+    KNN_CUDA_TRY(cudaMallocAsync(&qsorted, groups * kGroup * sizeof(Float4), stream));
+    if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
+    int in_tmp = 0;
+    if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
+    if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
+    if ((rc = refine_runs(qsorted, nq, stream))) return rc;
+  }
+  RingParams p;
+  fill_local_only(p, idx, k, max_radius);
+  p.groups_per_chunk = (int)groups;
+  p.home_queries = self ? idx->pts : qsorted;
+  p.home_n = nq;
+  p.home_is_tree = self ? 1 : 0;
+  p.result_sorted = limits;
+  p.raw_result = 1;
+  if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
+  CollectParams c;
+  memset(&c, 0, sizeof(c));
+  c.tree = idx->view();
+  c.k = k;
+  c.sentinel = p.sentinel;
+  c.queries = p.home_queries;
+  c.nq = nq;
+  c.row_offset = self ? idx->id_offset : 0u;
+  c.home_is_tree = p.home_is_tree;
+  c.limit_sorted = limits;
+  c.out_ids = d_out_ids;
+  c.out_dist = d_out_dist;
+  c.task_counter = idx->task_counter;
+  if ((rc = collect_launch(c, idx->num_sms, stream))) return rc;
+  KNN_CUDA_TRY(cudaFreeAsync(limits, stream));
+  if (!self) {
+    KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
+    KNN_CUDA_TRY(cudaFreeAsync(qsorted, stream));
+  }
+  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  return 0;
+}
+
 // Find-closest-point: k = 1 traversal that also reports WHICH point is closest.
 // Role of cukd::stackFree::fcp (cudaKDTree/cukd/fcp.h:210-254).
 int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, float max_radius, int32_t* d_out_ids,

@@ -338,6 +338,31 @@ extern "C" int b200knn_cpu_bruteforce(const float* xyz, int64_t n, const float* 
   return 0;
 }
 
+extern "C" int b200knn_cpu_neighbors(const float* xyz, int64_t n, const float* queries, int64_t nq, int k,
+                                     float max_radius, int32_t* out_ids, float* out_dist, int num_threads) {
+  if (k < 1 || n < 0 || nq < 0 || (!xyz && n) || (!queries && nq) || ((!out_ids || !out_dist) && nq)) {
+    set_last_error("cpu_neighbors: invalid argument");
+    return -2;
+  }
+  const float sent = sentinel_d2(max_radius);
+  parallel_for(nq, num_threads, [&](int64_t b, int64_t e) {
+    std::vector<std::pair<float, int32_t>> d(n);
+    for (int64_t qi = b; qi < e; ++qi) {
+      const float qx = queries[3 * qi], qy = queries[3 * qi + 1], qz = queries[3 * qi + 2];
+      for (int64_t i = 0; i < n; ++i)
+        d[i] = {dist2(qx, qy, qz, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]), (int32_t)i};
+      const int64_t m = std::min<int64_t>(k, n);
+      std::partial_sort(d.begin(), d.begin() + m, d.end());
+      for (int64_t s = 0; s < k; ++s) {
+        const bool have = s < m && d[s].first < sent;      // a candidate must beat the cut-off, as in the heap
+        out_ids[qi * k + s] = have ? d[s].second : -1;
+        out_dist[qi * k + s] = have ? finalize_kth(d[s].first) : INFINITY;
+      }
+    }
+  });
+  return 0;
+}
+
 extern "C" int b200knn_cpu_stats(uint64_t out4[4], int reset) {
   for (int i = 0; i < 4; ++i) { out4[i] = g_cpu_stats[i].load(); if (reset) g_cpu_stats[i] = 0; }
   return 0;

@@ -88,12 +88,31 @@ struct RingParams {
   int allow_global_heap;       // 1: k beyond the shared-memory limit may use a global-memory heap (allocates)
   float* global_heaps;         // set by ring_launch on that fallback path
   int fill;                    // 1: fresh heaps take their first floor(k/32) leaves by plain appends + heapify
+  int raw_result;              // 1: result_sorted receives the heap top itself (squared distance / sentinel)
 };
 bool convergent_fill_enabled();   // api.cu: host-side switch (B200KNN_FILL=0/1), read once
 
 size_t ring_smem_bytes(int k, int warps_per_cta);
 int ring_pick_warps_per_cta(int k);
 int ring_launch(const RingParams& p, int num_sms, cudaStream_t stream);
+
+// ---------------- neighbour lists (neighbors.cu) ----------------
+// Second pass of the k-nearest-NEIGHBOURS query: with every query's exact k-th squared distance known,
+// collect the ids and distances of all points inside it (fixed-radius traversal, no heap).
+struct CollectParams {
+  TreeView tree;
+  int k;
+  float sentinel;              // max_radius^2 or +inf: a limit equal to it means "fewer than k points in range"
+  const Float4* queries;       // sorted queries, .w = row of the output (as bits) + row_offset
+  int64_t nq;
+  uint32_t row_offset;
+  int home_is_tree;            // queries are exactly the tree's own sorted points
+  const float* limit_sorted;   // per sorted query: heap top of the first pass
+  int32_t* out_ids;            // [rows][k]
+  float* out_dist;             // [rows][k]
+  unsigned long long* task_counter;
+};
+int collect_launch(const CollectParams& p, int num_sms, cudaStream_t stream);
 
 // ---------------- culled exchange / redistribution (pv.cu) ----------------
 constexpr int kRegionBoxes = 2048;

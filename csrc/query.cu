@@ -114,7 +114,7 @@ knn_ring_kernel_t(const RingParams p) {
     // ------------------------------------------------------------------ output
     if (hop == R - 1) {
       if (g.valid) {
-        p.result_sorted[home_group * kGroup + lane] = finalize_kth(g.top);
+        p.result_sorted[home_group * kGroup + lane] = p.raw_result ? g.top : finalize_kth(g.top);
         if (p.result_ids != nullptr) p.result_ids[home_group * kGroup + lane] = g.last_id;
       }
     } else {

@@ -187,6 +187,15 @@ __device__ __forceinline__ void maybe_leaf(const TreeView& t, int leaf, float lx
   if (__any_sync(kFullMask, g.valid && (lb < g.top))) process_leaf(t, leaf, cnt, g);
 }
 
+// What traverse() does with a leaf that survives the group-level test. The default keeps the k
+// smallest distances in the lanes' heaps; other kernels (neighbors.cu) plug in their own.
+struct HeapLeafOp {
+  __device__ __forceinline__ void operator()(const TreeView& t, int leaf, float lx, float ly, float lz, float hx,
+                                             float hy, float hz, int cnt, GroupCtx& g) const {
+    maybe_leaf(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
+  }
+};
+
 // ---- traversal ------------------------------------------------------------------------------------
 // One loop, two sources of "next node", one leaf call site:
 //   * FRAMES (depth >= 0): depth-first, nearest child first, explicit frame stack in shared memory
@@ -287,7 +296,8 @@ __device__ __forceinline__ void frontier_expand(const TreeView& t, int level, in
 
 // fill_leaves > 0: the valid lanes' heaps are fresh; the first fill_leaves leaves that come up are
 // appended without a test (see fill_leaf). fill_leaves * 32 <= k.
-__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves = 0) {
+template <class LeafOp>
+__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves, LeafOp& leaf_op) {
   const int lane = lane_id();
   int fill_pos = 0;
   unsigned* fr = g.frames;
@@ -385,9 +395,14 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       if (--fill_leaves == 0) fill_finish(g);
       continue;
     }
-    maybe_leaf(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
+    leaf_op(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
   }
   if (fill_pos > 0 && fill_leaves > 0) fill_finish(g);    // the tree ran out of leaves during the fill
+}
+
+__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves = 0) {
+  HeapLeafOp op;
+  traverse(t, g, seed_l1, fill_leaves, op);
 }
 
 // Shared-memory floats per warp when the heap lives in GLOBAL memory (k too large for shared memory).
@@ -445,8 +460,9 @@ __device__ __forceinline__ void group_bounds(GroupCtx& g) {
 // is more than two thirds of the extent, recursively, and traverse each coherent sub-group on its own
 // (the other lanes are simply not valid during that pass). Exactness is unaffected.
 // fill_leaves: see traverse(); pass k / 32 for a group whose heaps are all fresh, else 0.
+template <class LeafOp>
 __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1,
-                                               int fill_leaves = 0) {
+                                               int fill_leaves, LeafOp& leaf_op) {
   const int lane = lane_id();
   const unsigned all = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
   int nwork = 1;
@@ -487,9 +503,15 @@ __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, i
     // coherent enough: one pass. The group's own level-1 node is the natural seed only for the
     // unsplit group; a split part looks for the node nearest to it.
     const int seed = (m == all && own_seed_l1 != -2) ? own_seed_l1 : find_seed_l1(t, g);
-    traverse(t, g, seed, fill_leaves);
+    traverse(t, g, seed, fill_leaves, leaf_op);
   }
   g.valid = lane < cnt;
+}
+
+__device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1,
+                                               int fill_leaves = 0) {
+  HeapLeafOp op;
+  traverse_group(t, g, cnt, own_seed_l1, fill_leaves, op);
 }
 
 __device__ __forceinline__ void flush_stats(const GroupCtx& g, unsigned long long* stats) {

@@ -70,6 +70,16 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
  * (cudaKDTree/cukd/fcp.h:210-254). Synchronises `stream`. */
 int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, float max_radius,
                       int32_t* d_out_ids, float* d_out_dist_or_null, void* stream);
+/* knn_neighbors: the k nearest indexed points of every query — their ids (as fcp_query reports them)
+ * and distances — in d_out_ids / d_out_dist, both [nq][k] row-major. Rows are NOT ordered by distance
+ * (like the reference's heap-ordered candidate lists, cukd/knn.h:311-326); slots beyond the points
+ * available within max_radius hold id -1 / distance +inf. Which of several points at exactly the k-th
+ * distance are reported is unspecified. d_queries == NULL: the indexed points themselves are the
+ * queries (nq is ignored; rows in the order the points were handed to index_create, which must have
+ * been called without explicit ids). Two passes: the k-th-distance kernel, then a fixed-radius
+ * collection; no (distance, id) heap is kept. Synchronises `stream`. */
+int b200knn_knn_neighbors(b200knn_index* idx, const float* d_queries_or_null, int64_t nq, int k, float max_radius,
+                          int32_t* d_out_ids, float* d_out_dist, void* stream);
 /* knn_self_noalloc: same result as index_create + knn_self for n <= B200KNN_NOALLOC_MAX_POINTS, but
  * the library allocates nothing: the sorted points, the box tree, the sort buffers and the counters
  * all live in one fixed device array inside the library (about 11.9 MB per GPU that loads it, held
@@ -214,6 +224,9 @@ int b200knn_cpu_bruteforce(const float* xyz, int64_t n, const float* queries, in
                            float max_radius, float* out, int num_threads);
 int b200knn_cpu_knn(const float* xyz, int64_t n, const float* queries_or_null, int64_t nq, int k,
                     float max_radius, float* out, int num_threads);
+/* cpu_neighbors: brute-force oracle of knn_neighbors; rows sorted by (distance, id). */
+int b200knn_cpu_neighbors(const float* xyz, int64_t n, const float* queries, int64_t nq, int k, float max_radius,
+                          int32_t* out_ids, float* out_dist, int num_threads);
 
 /* Traversal counters accumulated by cpu_knn calls (same meaning as b200knn_index_stats). */
 int b200knn_cpu_stats(uint64_t out4[4], int reset);

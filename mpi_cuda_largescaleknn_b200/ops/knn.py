@@ -119,6 +119,37 @@ class KnnIndex:
         return out
 
 
+def neighbors(index: "KnnIndex", queries: Optional[torch.Tensor], k: int, max_radius: float = math.inf,
+              sort: bool = True):
+    """The k nearest indexed points of every query: ``(ids int32 [nq,k], distances float32 [nq,k])``.
+
+    ``queries=None`` asks for the neighbours of the indexed points themselves (self included), rows in
+    the caller's point order. With ``sort=True`` (default) rows are ordered nearest first; the library
+    itself returns them unordered. Missing neighbours (fewer than k points, or none within
+    ``max_radius``) are id -1 / distance +inf. Role of ``cukd::knn`` with a candidate list that is read
+    back (cudaKDTree/cukd/knn.h:311-326, 617-631)."""
+    if queries is None:
+        nq, qptr = index.n, None
+    else:
+        q = _as_xyz(queries)
+        nq, qptr = int(q.shape[0]), (q.data_ptr() if q.shape[0] else None)
+        if nq == 0:
+            return (torch.empty((0, k), dtype=torch.int32, device=index.device),
+                    torch.empty((0, k), dtype=torch.float32, device=index.device))
+    ids = torch.empty((nq, int(k)), dtype=torch.int32, device=index.device)
+    dist = torch.empty((nq, int(k)), dtype=torch.float32, device=index.device)
+    fn = lib().b200knn_knn_neighbors
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    fn.restype = C.c_int
+    with torch.cuda.device(index.device):
+        check(fn(index.handle, qptr, nq, int(k), float(max_radius), ids.data_ptr(), dist.data_ptr(), _stream_ptr()),
+              "knn_neighbors")
+    if sort and nq:
+        dist, order = torch.sort(dist, dim=1, stable=True)
+        ids = torch.gather(ids, 1, order)
+    return ids, dist
+
+
 def fcp(index: "KnnIndex", queries: torch.Tensor, max_radius: float = math.inf):
     """Find-closest-point: (ids int32 [nq], distances float32 [nq]) of the nearest indexed point of
     every query; id -1 where nothing lies within ``max_radius``. Role of ``cukd::fcp``."""

@@ -7,6 +7,7 @@
 """
 from __future__ import annotations
 
+import ctypes as C
 import math
 from typing import Optional
 
@@ -40,6 +41,21 @@ def cpu_knn(points, queries: Optional[np.ndarray] = None, k: int = 1, max_radius
     check(lib().b200knn_cpu_knn(x.ctypes.data, len(x), None if q is None else q.ctypes.data, nq, int(k),
                                 float(max_radius), out.ctypes.data, int(threads)), "cpu_knn")
     return out
+
+
+def neighbors_bruteforce(points, queries=None, k: int = 1, max_radius: float = math.inf, threads: int = 0):
+    """Brute-force k nearest neighbours: (ids int32 [nq,k], distances float32 [nq,k]), rows sorted by
+    (distance, id); -1 / +inf where fewer than k points are in range."""
+    x = _f32c(points)
+    q = x if queries is None else _f32c(queries)
+    ids = np.empty((len(q), int(k)), np.int32)
+    dist = np.empty((len(q), int(k)), np.float32)
+    fn = lib().b200knn_cpu_neighbors
+    fn.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_int]
+    fn.restype = C.c_int
+    check(fn(x.ctypes.data, len(x), q.ctypes.data, len(q), int(k), float(max_radius), ids.ctypes.data,
+             dist.ctypes.data, int(threads)), "cpu_neighbors")
+    return ids, dist
 
 
 def bit_equal(a: np.ndarray, b: np.ndarray) -> bool:

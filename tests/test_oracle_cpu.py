@@ -71,3 +71,22 @@ def test_oracle_uses_canonical_fma_order():
                 found = True
     if hasattr(math, "fma"):
         assert found
+
+
+def test_neighbors_bruteforce_rows_are_the_k_smallest_sorted():
+    from mpi_cuda_largescaleknn_b200.utils.oracle import neighbors_bruteforce
+    x = gen.uniform(700, seed=41)
+    q = gen.uniform(50, seed=42)
+    ids, dist = neighbors_bruteforce(x, q, k=9)
+    d_all = np.sqrt(((q[:, None, :].astype(np.float64) - x[None, :, :]) ** 2).sum(-1))
+    want = np.sort(d_all, axis=1)[:, :9]
+    assert np.allclose(dist, want, rtol=1e-5, atol=1e-7)
+    assert np.all(np.diff(dist, axis=1) >= 0)
+    assert np.allclose(d_all[np.arange(50)[:, None], ids], dist, rtol=1e-5, atol=1e-7)
+    # the k-th column is the k-th-distance oracle, bit for bit
+    assert bit_equal(dist[:, -1], bruteforce(x, queries=q, k=9))
+    # fewer than k points / cut-off radius: padding
+    ids2, dist2 = neighbors_bruteforce(x[:5], q[:3], k=8)
+    assert np.all(ids2[:, 5:] == -1) and np.all(np.isinf(dist2[:, 5:])) and np.all(ids2[:, :5] >= 0)
+    ids3, dist3 = neighbors_bruteforce(x, q, k=9, max_radius=0.05)
+    assert np.all((dist3 < 0.05) == (ids3 >= 0))
