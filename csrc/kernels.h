@@ -88,8 +88,10 @@ struct RingParams {
   int allow_global_heap;       // 1: k beyond the shared-memory limit may use a global-memory heap (allocates)
   float* global_heaps;         // set by ring_launch on that fallback path
   int fill;                    // 1: fresh heaps take their first floor(k/32) leaves by plain appends + heapify
+  int pairs;                   // 1: experimental pair sweep (k >= 32)
 };
 bool convergent_fill_enabled();   // api.cu: host-side switch (B200KNN_FILL=0/1), read once
+bool pair_sweep_enabled();        // api.cu: host-side switch (B200KNN_PAIRS=1), read once
 
 size_t ring_smem_bytes(int k, int warps_per_cta);
 int ring_pick_warps_per_cta(int k);
