@@ -57,3 +57,15 @@ $(BUILD)/cudaMpiKNN_prePartitionedData: apps/prepartitioned.cpp $(BUILD)/backend
 	$(NVCC) $(APPFLAGS) $(ARCH) $< $(BUILD)/backend.o -o $@ -L$(BUILD) -lb200knn -Xlinker -rpath,'$$ORIGIN'
 
 .PHONY: apps
+
+# ---- examples ----
+examples: $(BUILD)/sample_knn
+$(BUILD)/sample_knn: examples/sample_knn.c $(LIB) include/b200knn.h
+	gcc -std=c99 -O2 -Iinclude -I/usr/local/cuda/include $< -o $@ -L$(BUILD) -lb200knn \
+	    -L/usr/local/cuda/lib64 -lcudart -lm -Wl,-rpath,'$$ORIGIN' -Wl,-rpath,/usr/local/cuda/lib64
+.PHONY: examples
+
+# ---- SASS listings of every kernel (profiles/sass/, no GPU needed) ----
+sass: lib
+	python tools/dump_sass.py
+.PHONY: sass

@@ -13,7 +13,7 @@
 //                          improved heaps straight back into the home GPU's pending slots (peer
 //                          stores) — the merge-back
 //   pv_final               k-th distances of pending groups
-// Rounds are separated by a host barrier (see dist.cu); all data movement is done by these kernels
+// Rounds are separated by device-side barriers (dev_barrier_kernel); all data movement is done by these kernels
 // over NVLink-mapped peer memory, never by a collective library.
 //
 // redistribute / push_pairs: the all-to-all scatter of points to their spatial owner and of the

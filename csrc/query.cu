@@ -157,7 +157,7 @@ size_t group_smem_bytes(int k, int warps_per_cta) {
 }
 
 // Shared memory decides the shape: maximise resident warps per SM over (CTAs per SM, warps per
-// CTA); prefer more, smaller CTAs on ties. k = 100 -> two 7-warp CTAs per SM. Returns 0 if not even
+// CTA); prefer more, smaller CTAs on ties. k = 100 -> three 5-warp CTAs per SM. Returns 0 if not even
 // one warp fits (k > ~1790).
 int group_pick_warps(int k, const void* kernel) {
   int reg_warps = 32;     // resident warps the register file allows for this kernel

@@ -78,5 +78,13 @@ def test_header_constants_match_python():
         assert m and int(m.group(1)) == val, name
 
 
+
+def test_c_example_builds_against_the_library():
+    """examples/sample_knn.c is plain C99 against include/b200knn.h + libb200knn.so (run it on a GPU box)."""
+    out = subprocess.run(["make", "-C", str(ROOT), "examples"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert out.returncode == 0, out.stdout[-2000:]
+    assert (ROOT / "build" / "sample_knn").exists()
+
+
 if __name__ == "__main__":
     sys.exit(pytest.main([__file__, "-q"]))
