@@ -79,6 +79,19 @@ def test_emulated_index_is_sorted_and_boxes_are_exact(sim):
     assert cnt.value == nl
     pts = np.concatenate([s[:, :3], np.full((nl * 32 - n, 3), np.nan, np.float32)]).reshape(nl, 32, 3)
     assert np.array_equal(boxes[:, 0:3], np.nanmin(pts, axis=1)) and np.array_equal(boxes[:, 4:7], np.nanmax(pts, axis=1))
+    # k-d refinement: every full 1024-point run is 5 levels of exact median splits along the widest axis
+
+    def check_kd(seg, depth):
+        if depth == 5:
+            return
+        axis = int(np.argmax(seg.max(0) - seg.min(0)))
+        half = len(seg) // 2
+        assert seg[:half, axis].max() <= seg[half:, axis].min()
+        check_kd(seg[:half], depth + 1)
+        check_kd(seg[half:], depth + 1)
+
+    for run in range(n // 1024):
+        check_kd(s[run * 1024:(run + 1) * 1024, :3], 0)
     idx.close()
 
 
