@@ -75,6 +75,19 @@ __device__ __forceinline__ float heap_replace_padded(float* h, int kp, float e) 
 __device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
   return (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
 }
+#if defined(B200KNN_SIMT_HOST)   // host emulation of the kernels (tests/simt): the same IEEE operations per half
+__device__ __forceinline__ float half_lo(unsigned long long v) { return __uint_as_float((unsigned)(v & 0xffffffffull)); }
+__device__ __forceinline__ float half_hi(unsigned long long v) { return __uint_as_float((unsigned)(v >> 32)); }
+__device__ __forceinline__ unsigned long long sub2(unsigned long long a, unsigned long long b) {
+  return pack2(half_lo(a) - half_lo(b), half_hi(a) - half_hi(b));
+}
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+  return pack2(half_lo(a) * half_lo(b), half_hi(a) * half_hi(b));
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  return pack2(fmaf(half_lo(a), half_lo(b), half_lo(c)), fmaf(half_hi(a), half_hi(b), half_hi(c)));
+}
+#else
 __device__ __forceinline__ unsigned long long sub2(unsigned long long a, unsigned long long b) {
   unsigned long long r;
   asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
@@ -90,6 +103,7 @@ __device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigne
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
   return r;
 }
+#endif
 
 __device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g) {
   const int lane = lane_id();
