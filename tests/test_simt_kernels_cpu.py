@@ -158,3 +158,15 @@ def test_emulated_distributed_driver_single_rank(sim):
         assert bit_equal(out, want), mode
     sim.b200knn_dist_destroy.argtypes = [C.c_void_p]
     sim.b200knn_dist_destroy(eng)
+
+
+def test_emulated_pair_sweep_variant(sim):
+    """The experimental two-leaves-per-insertion-phase kernels (B200KNN_PAIRS=1, read once per process):
+    same suite in a child process with the switch on."""
+    import os
+    import sys
+    env = dict(os.environ, B200KNN_PAIRS="1")
+    out = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-x", "-q", "-k",
+                          "self_knn or radius or single_rank or external"], cwd=str(ROOT), env=env,
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert out.returncode == 0, out.stdout[-3000:]
