@@ -64,3 +64,28 @@ $(BUILD)/sample_knn: examples/sample_knn.c $(LIB) include/b200knn.h
 	gcc -std=c99 -O2 -Iinclude -I/usr/local/cuda/include $< -o $@ -L$(BUILD) -lb200knn \
 	    -L/usr/local/cuda/lib64 -lcudart -lm -Wl,-rpath,'$$ORIGIN' -Wl,-rpath,/usr/local/cuda/lib64
 .PHONY: examples
+
+# ---- SASS listings of every kernel (profiles/sass/, no GPU needed) ----
+sass: lib
+	python tools/dump_sass.py
+.PHONY: sass
+
+# ---- host emulation of the kernels (tests/simt): the same sources compiled as C++, threads = fibers ----
+SIMT_DIR  := $(BUILD)/simt
+SIMT_SRCS := $(patsubst csrc/%.cu,$(SIMT_DIR)/%.cpp,$(CU_SRCS))
+SIMT_LIB  := $(BUILD)/libb200knn_simt.so
+SIMT_FLAGS := -O1 -g -std=c++17 -fPIC -ffp-contract=off -mfma -pthread -fpermissive -w -Itests/simt -Iinclude -Icsrc
+
+simt: $(SIMT_LIB)
+$(SIMT_DIR)/%.cpp: csrc/%.cu tests/simt/preprocess.py
+	@mkdir -p $(SIMT_DIR)
+	python tests/simt/preprocess.py $< $@
+$(SIMT_DIR)/%.o: $(SIMT_DIR)/%.cpp tests/simt/simt_host.h csrc/*.h csrc/*.cuh include/b200knn.h
+	$(CXX) $(SIMT_FLAGS) -c $< -o $@
+$(SIMT_DIR)/simt_runtime.o: tests/simt/simt_runtime.cpp tests/simt/simt_host.h
+	@mkdir -p $(SIMT_DIR)
+	$(CXX) $(SIMT_FLAGS) -c $< -o $@
+$(SIMT_LIB): $(patsubst %.cpp,%.o,$(SIMT_SRCS)) $(SIMT_DIR)/simt_runtime.o $(CPP_OBJS)
+	$(CXX) -shared -o $@ $^ -lpthread -ldl
+.PHONY: simt
+.SECONDARY: $(SIMT_SRCS)

@@ -202,9 +202,45 @@ k_refine_runs(Float4* __restrict__ pts, int64_t n) {
       keys[t] = ((unsigned long long)seg << 42) | ((unsigned long long)oc << 10) | (unsigned long long)t;
     }
     __syncthreads();
+    // Bitonic sort of every segment. Compare-exchange steps whose partner distance is >= 64 go through
+    // shared memory (one __syncthreads each); all steps with distance <= 32 of a merge run in registers:
+    // a warp owns 64 consecutive keys (lane holds e0 = 64w + lane and e1 = e0 + 32), distance 32 is the
+    // thread's own pair, distances 16..1 are shfl_xor partners. 35 barriers per run instead of 185.
     const int seg_size = 1 << seg_shift;
-    for (int size = 2; size <= seg_size; size <<= 1) {
-      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+    const int e0 = ((tid >> 5) << 6) + lane, e1 = e0 + 32;
+    auto cx = [](unsigned long long& x, unsigned long long y, bool keep_min) {
+      const bool y_smaller = y < x;
+      if (y_smaller == keep_min) x = y;
+    };
+    auto in_warp = [&](int size_from, int size_to) {
+      // merges of sizes size_from..size_to, restricted to distances <= 32 (size_from > 64: only the tail)
+      unsigned long long a = keys[e0], b = keys[e1];
+      for (int size = size_from; size <= size_to; size <<= 1) {
+        const bool asc0 = (size == seg_size) || ((e0 & size) == 0);
+        const bool asc1 = (size == seg_size) || ((e1 & size) == 0);
+        int stride = size >> 1;
+        if (stride > 32) stride = 32;
+        if (stride == 32) {                      // partner of e0 is e1: both in this thread, e0 is the lower index
+          const unsigned long long lo = a < b ? a : b, hi = a < b ? b : a;
+          a = asc0 ? lo : hi;
+          b = asc0 ? hi : lo;                    // (e0 & size) == (e1 & size) for size >= 64
+          stride = 16;
+        }
+        for (; stride > 0; stride >>= 1) {
+          const unsigned long long pa = __shfl_xor_sync(0xffffffffu, a, stride);
+          const unsigned long long pb = __shfl_xor_sync(0xffffffffu, b, stride);
+          const bool lower = (lane & stride) == 0;          // this lane holds the lower index of the pair
+          cx(a, pa, lower == asc0);
+          cx(b, pb, lower == asc1);
+        }
+      }
+      keys[e0] = a;
+      keys[e1] = b;
+    };
+    in_warp(2, 64 < seg_size ? 64 : seg_size);
+    __syncthreads();
+    for (int size = 128; size <= seg_size; size <<= 1) {
+      for (int stride = size >> 1; stride >= 64; stride >>= 1) {
         const int i = 2 * tid - (tid & (stride - 1));
         const int j = i + stride;
         const bool asc = (size == seg_size) || ((i & size) == 0);
@@ -212,6 +248,8 @@ k_refine_runs(Float4* __restrict__ pts, int64_t n) {
         if ((a > b) == asc) { keys[i] = b; keys[j] = a; }
         __syncthreads();
       }
+      in_warp(size, size);
+      __syncthreads();
     }
     float4 moved[2];
 #pragma unroll

@@ -67,6 +67,11 @@ __host__ __device__ __forceinline__ float ord2f(unsigned u) {
 }
 
 // ---- system-scope release/acquire flags (visible across NVLink peers) ----
+#if defined(B200KNN_SIMT_HOST)   // host emulation of the kernels (tests/simt): one thread, plain accesses
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) { *(volatile unsigned*)p = v; }
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) { return *(volatile const unsigned*)p; }
+__device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned* p) { return *(volatile const unsigned*)p; }
+#else
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -80,6 +85,7 @@ __device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned* p) {
   asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+#endif
 // Spin until *p >= want (sequence numbers only grow). Called by one lane.
 // Failure detection: a peer that died (or never launched) would otherwise leave this GPU spinning
 // forever. After ~60 s of waiting on one flag the kernel traps, which surfaces on the host as a

@@ -36,6 +36,28 @@ double now_ms() {
   return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// Opt-in step-by-step timing of the distributed pipeline (B200KNN_TRACE_PHASES=1): every mark
+// synchronises the stream and prints the time since the previous mark to stderr, so it perturbs the run
+// it measures — a diagnosis tool, not a benchmark. Without the variable a mark is one predictable branch.
+struct PhaseTrace {
+  bool on;
+  int rank;
+  cudaStream_t stream;
+  double last;
+  PhaseTrace(int rank_, cudaStream_t s) : rank(rank_), stream(s) {
+    static const bool enabled = getenv("B200KNN_TRACE_PHASES") != nullptr;
+    on = enabled;
+    last = on ? now_ms() : 0.0;
+  }
+  void mark(const char* what) {
+    if (!on) return;
+    cudaStreamSynchronize(stream);
+    const double t = now_ms();
+    fprintf(stderr, "[b200knn phase] rank %d %-28s %8.3f ms\n", rank, what, t - last);
+    last = t;
+  }
+};
+
 }  // namespace
 
 struct b200knn_dist {
@@ -179,6 +201,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
            b200knn_dist_report* rep) {
   NvtxRange range("b200knn:culled_exchange");
   const int R = d->world, me = d->rank;
+  PhaseTrace trace(me, stream);
   // everyone's region: the boxes of the deepest tree level with at most kRegionBoxes nodes, plus the
   // overall box for a quick reject. One box per rank is far too coarse: a few stray points at the end
   // of a Morton range, or the tails of a Gaussian blob, stretch it across the neighbours' regions.
@@ -285,7 +308,9 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
       Box* out_boxes = reinterpret_cast<Box*>(my_region.data() + sizeof(RegionHead));
       for (size_t i = 0; i < done.size(); ++i) out_boxes[i] = done[i].box;
     }
+    trace.mark("exchange: region boxes (host)");
     if (d->allgather(my_region.data(), all_regions.data(), (int64_t)region_bytes)) { set_last_error("bootstrap allgather failed"); return -3; }
+    trace.mark("exchange: allgather regions");
   }
   Box* d_regions = nullptr;
   KNN_CUDA_TRY(cudaMallocAsync(&d_regions, (size_t)R * kRegionBoxes * sizeof(Box), stream));
@@ -329,6 +354,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.home_n = idx->n;
   p.home_is_tree = 1;
   p.fill = convergent_fill_enabled() ? 1 : 0;
+  p.pairs = pair_sweep_enabled() ? 1 : 0;
   p.result_sorted = idx->result_sorted;
   p.pending = d->base + off_pending;
   p.pending_count = reinterpret_cast<int*>(d->base + off_pcount);
@@ -374,6 +400,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
       my_pending = all_pending[me];
     }
     if (rep) rep->ms_local_phase += tl1 - tl0;
+    trace.mark("exchange: local phase + vote");
     int64_t total_pending = 0;
     for (int v : all_pending) total_pending += v;
     if (rep) { rep->pending_groups += my_pending; rep->chunks += 1; }
@@ -397,6 +424,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     }
     if ((rc = pv_final_launch(p.pending, p.pending_count, k, idx->result_sorted, idx->num_sms, stream))) return rc;
     if (rep) { KNN_CUDA_TRY(cudaStreamSynchronize(stream)); rep->ms_rounds += now_ms() - tr0; }
+    trace.mark("exchange: rounds + final");
   }
   KNN_CUDA_TRY(cudaFreeAsync(d_regions, stream));
   if (d_votes) KNN_CUDA_TRY(cudaFreeAsync(d_votes, stream));
@@ -434,6 +462,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   const int R = d->world, me = d->rank;
   int rc;
   const double t0 = now_ms();
+  PhaseTrace trace(me, stream);
   // ---- who has what
   struct Info { int64_t n, begin; float box[6]; };
   Info mine{};
@@ -448,8 +477,10 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   if ((rc = bounds_decode(d_bord, d_box6, stream))) return rc;
   KNN_CUDA_TRY(cudaMemcpyAsync(mine.box, d_box6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  trace.mark("bounds kernel + copy");
   std::vector<Info> info(R);
   if (d->allgather(&mine, info.data(), sizeof(Info))) { set_last_error("bootstrap allgather failed"); return -3; }
+  trace.mark("allgather info");
   float gbox[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
   int64_t max_local = 0, total = 0;
   for (int r = 0; r < R; ++r) {
@@ -481,13 +512,16 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n_local, 0, 64, stream, &in_tmp))) return rc;
   const uint64_t* skeys = in_tmp ? keys_tmp : keys;
   const uint32_t* order = in_tmp ? vals_tmp : vals;
+  trace.mark("alloc + keys + 64-bit sort");
 
   // ---- splitters from evenly spaced local order statistics
   std::vector<uint64_t> my_samples(S), all_samples((size_t)S * R);
   if ((rc = sample_keys_launch(skeys, n_local, S, d_samples, stream))) return rc;
   KNN_CUDA_TRY(cudaMemcpyAsync(my_samples.data(), d_samples, S * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  trace.mark("sample kernel + copy");
   if (d->allgather(my_samples.data(), all_samples.data(), S * sizeof(uint64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
+  trace.mark("allgather samples");
   std::sort(all_samples.begin(), all_samples.end());
   uint64_t split[B200KNN_MAX_RANKS] = {};
   // Splitter j = the j/R quantile of the pooled samples, snapped to the coarsest Morton-cell
@@ -517,11 +551,13 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     KNN_CUDA_TRY(cudaStreamSynchronize(stream));
   }
   cut[R] = n_local;
+  trace.mark("host sort + splitters + cuts");
 
   // ---- count matrix
   std::vector<int64_t> send(R), M((size_t)R * R);
   for (int r = 0; r < R; ++r) send[r] = cut[r + 1] - cut[r];
   if (d->allgather(send.data(), M.data(), R * sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
+  trace.mark("allgather count matrix");
   int64_t max_recv = 0, my_recv = 0;
   std::vector<int64_t> recv_n(R, 0);
   for (int dst = 0; dst < R; ++dst) {
@@ -536,6 +572,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   const size_t need = align256((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4)) +
                       align256((size_t)std::max<int64_t>(max_local, 1) * 8) + pv_heap_need(k, pl.Gc);
   if ((rc = ensure_heap(d, need))) return rc;
+  trace.mark("ensure heap");
   d->bump = kHeapReserved;
   const size_t off_recv = d->alloc((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4));
   const size_t off_out = d->alloc((size_t)std::max<int64_t>(max_local, 1) * 8);   // (id, value) pairs land here
@@ -566,12 +603,15 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   KNN_CUDA_TRY(cudaFreeAsync(d_bord, stream));
   KNN_CUDA_TRY(cudaFreeAsync(d_box6, stream));
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  trace.mark("scatter kernel + frees");
   if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
+  trace.mark("barrier after scatter");
   const double t1 = now_ms();
 
   // ---- local index over the received (spatially compact) points, then the culled exchange
   b200knn_index* idx = nullptr;
   rc = b200knn_index_create_xyzw(reinterpret_cast<const float*>(d->base + off_recv), my_recv, 0, stream, &idx);
+  trace.mark("index build");
   const double t2 = now_ms();
   if (!rc) rc = run_pv(d, idx, k, max_radius, pl, stream, rep);
   const double t3 = now_ms();
@@ -601,9 +641,11 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     if ((rc = lower_bounds32_launch(sids, m, d_begins, R + 1, d_cut2, stream))) return rc;
     KNN_CUDA_TRY(cudaMemcpyAsync(cut2.data(), d_cut2, (R + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
     KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    trace.mark("return: pairs + 32-bit sort");
     std::vector<int64_t> send2(R), M2((size_t)R * R);
     for (int r = 0; r < R; ++r) send2[r] = cut2[r + 1] - cut2[r];
     if (d->allgather(send2.data(), M2.data(), R * sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
+    trace.mark("return: allgather matrix");
     PushPairsParams pp;
     memset(&pp, 0, sizeof(pp));
     pp.ids = sids;
@@ -630,7 +672,9 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     cudaError_t e = cudaStreamSynchronize(stream);
     if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
   }
+  trace.mark("return: push pairs");
   if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
+  trace.mark("return: barrier");
   if (!rc && n_local > 0) {
     rc = scatter_pairs_launch(d->base + off_out, n_local, global_begin, d_out, stream);
     if (!rc) {
@@ -638,8 +682,10 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
       if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
     }
   }
+  trace.mark("return: local scatter");
   // nobody may start overwriting the landing zone (next call) before everyone has copied out
   if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
+  trace.mark("return: final barrier");
   if (rep) {
     rep->ms_redistribute += t1 - t0;
     rep->ms_build += t2 - t1;

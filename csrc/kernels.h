@@ -89,8 +89,10 @@ struct RingParams {
   float* global_heaps;         // set by ring_launch on that fallback path
   int fill;                    // 1: fresh heaps take their first floor(k/32) leaves by plain appends + heapify
   int raw_result;              // 1: result_sorted receives the heap top itself (squared distance / sentinel)
+  int pairs;                   // 1: experimental pair sweep (k >= 32)
 };
 bool convergent_fill_enabled();   // api.cu: host-side switch (B200KNN_FILL=0/1), read once
+bool pair_sweep_enabled();        // api.cu: host-side switch (B200KNN_PAIRS=1), read once
 
 size_t ring_smem_bytes(int k, int warps_per_cta);
 int ring_pick_warps_per_cta(int k);
@@ -125,6 +127,7 @@ struct PvMainParams {
   float sentinel;
   int phase;                   // 0 = LOCAL (home groups, fresh heaps), 1 = SERVE (visiting groups from the inbox)
   int fill;                    // as RingParams::fill, LOCAL phase only
+  int pairs;                   // as RingParams::pairs (both phases)
   int R, rank;
   const Box* region_boxes;     // [R][kRegionBoxes]: every rank's region = the boxes of the deepest tree
                                // level that has at most kRegionBoxes nodes

@@ -111,7 +111,7 @@ knn_collect_kernel(const CollectParams p) {
     g.top = op.inclusive ? __uint_as_float(__float_as_uint(op.limit) + 1u) : op.limit;
     if (p.tree.n > 0) {
       const int own_seed = p.home_is_tree ? (p.tree.levels >= 2 ? (int)(group / kFanout) : -1) : -2;
-      traverse_group(p.tree, g, cnt, own_seed, 0, op);
+      traverse_group<false>(p.tree, g, cnt, own_seed, 0, op);
     }
     if (g.valid) {
       for (int s = op.front; s < p.k - op.ties; ++s) {     // fewer than k points in range

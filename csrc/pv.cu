@@ -13,7 +13,7 @@
 //                          improved heaps straight back into the home GPU's pending slots (peer
 //                          stores) — the merge-back
 //   pv_final               k-th distances of pending groups
-// Rounds are separated by a host barrier (see dist.cu); all data movement is done by these kernels
+// Rounds are separated by device-side barriers (dev_barrier_kernel); all data movement is done by these kernels
 // over NVLink-mapped peer memory, never by a collective library.
 //
 // redistribute / push_pairs: the all-to-all scatter of points to their spatial owner and of the
@@ -40,8 +40,9 @@ __device__ __forceinline__ const int* slot_meta(const char* slot, int k) {
   return reinterpret_cast<const int*>(slot + (size_t)k * 128 + 512);
 }
 
+template <bool PAIRS>
 __global__ void __launch_bounds__(Q_MAX_WARPS * 32, 1)
-pv_main_kernel(const PvMainParams p) {
+pv_main_kernel_t(const PvMainParams p) {
   extern __shared__ __align__(16) float q_smem[];
   const int lane = lane_id();
   const int k = p.k;
@@ -89,7 +90,7 @@ pv_main_kernel(const PvMainParams p) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;
       const int own_seed = (p.phase == 0 && p.home_is_tree)
                                ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1) : -2;
-      traverse_group(p.tree, g, cnt, own_seed, (p.phase == 0 && p.fill) ? k / kGroup : 0);
+      traverse_group<PAIRS>(p.tree, g, cnt, own_seed, (p.phase == 0 && p.fill) ? k / kGroup : 0);
     }
 
     if (p.phase == 0) {
@@ -387,19 +388,21 @@ inline int blocks_for(int64_t n, int block) { return (int)div_up(n, block); }
 
 int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream) {
   KNN_REQUIRE(p.k >= 1, "k must be >= 1");
-  const int warps = group_pick_warps(p.k, (const void*)pv_main_kernel);
+  const bool pairs = p.pairs && p.k >= kGroup;
+  auto kernel = pairs ? pv_main_kernel_t<true> : pv_main_kernel_t<false>;
+  const int warps = group_pick_warps(p.k, (const void*)kernel);
   KNN_REQUIRE(warps >= 1, "k too large for the shared-memory heap (k <= 1790)");
   const size_t smem = group_smem_bytes(p.k, warps);
-  KNN_CUDA_TRY(cudaFuncSetAttribute(pv_main_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  KNN_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
-  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pv_main_kernel, warps * 32, smem));
+  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, warps * 32, smem));
   KNN_REQUIRE(occ >= 1, "pv kernel does not fit on an SM");
   if (max_tasks <= 0) return 0;
   long long want = ((long long)max_tasks + warps - 1) / warps;
   long long cap = (long long)num_sms * occ;
   const int grid = (int)(want < cap ? want : cap);
   KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
-  pv_main_kernel<<<grid, warps * 32, smem, stream>>>(p);
+  kernel<<<grid, warps * 32, smem, stream>>>(p);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;

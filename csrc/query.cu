@@ -36,7 +36,8 @@ namespace {
 // GLOBAL_HEAP = false: the product path, heaps in shared memory (k <= ~1790).
 // GLOBAL_HEAP = true : fallback for larger k, one [kp][32] heap block per resident warp in global
 //                      memory (rows are coalesced 128-byte lines); everything else is unchanged.
-template <bool GLOBAL_HEAP>
+// PAIRS = true       : experimental pair sweep (traverse.cuh::process_leaf_pair), B200KNN_PAIRS=1, k >= 32.
+template <bool GLOBAL_HEAP, bool PAIRS = false>
 __global__ void __launch_bounds__(Q_MAX_WARPS * 32, 1)
 knn_ring_kernel_t(const RingParams p) {
   extern __shared__ __align__(16) float q_smem[];
@@ -108,7 +109,7 @@ knn_ring_kernel_t(const RingParams p) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;   // heap padding
       // seed = the level-1 node holding the group's own leaf (self queries at home), else the nearest (-2)
       const int own_seed = (hop == 0 && p.home_is_tree) ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1) : -2;
-      traverse_group(p.tree, g, cnt, own_seed, (hop == 0 && p.fill) ? k / kGroup : 0);
+      traverse_group<PAIRS>(p.tree, g, cnt, own_seed, (hop == 0 && p.fill) ? k / kGroup : 0);
     }
 
     // ------------------------------------------------------------------ output
@@ -156,7 +157,7 @@ size_t group_smem_bytes(int k, int warps_per_cta) {
 }
 
 // Shared memory decides the shape: maximise resident warps per SM over (CTAs per SM, warps per
-// CTA); prefer more, smaller CTAs on ties. k = 100 -> two 7-warp CTAs per SM. Returns 0 if not even
+// CTA); prefer more, smaller CTAs on ties. k = 100 -> three 5-warp CTAs per SM. Returns 0 if not even
 // one warp fits (k > ~1790).
 int group_pick_warps(int k, const void* kernel) {
   int reg_warps = 32;     // resident warps the register file allows for this kernel
@@ -201,7 +202,12 @@ int ring_launch(const RingParams& p_in, int num_sms, cudaStream_t stream) {
     unsigned long long cap = (unsigned long long)num_sms * occ;
     const int grid = (int)(want < cap ? want : cap);
     KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
-    knn_ring_kernel_t<false><<<grid, warps * 32, smem, stream>>>(p);
+    if (p.pairs && p.k >= kGroup) {
+      KNN_CUDA_TRY(cudaFuncSetAttribute(knn_ring_kernel_t<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      knn_ring_kernel_t<false, true><<<grid, warps * 32, smem, stream>>>(p);
+    } else {
+      knn_ring_kernel_t<false><<<grid, warps * 32, smem, stream>>>(p);
+    }
     note_launch();
     KNN_CUDA_TRY(cudaGetLastError());
     return 0;

@@ -75,6 +75,19 @@ __device__ __forceinline__ float heap_replace_padded(float* h, int kp, float e) 
 __device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
   return (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
 }
+#if defined(B200KNN_SIMT_HOST)   // host emulation of the kernels (tests/simt): the same IEEE operations per half
+__device__ __forceinline__ float half_lo(unsigned long long v) { return __uint_as_float((unsigned)(v & 0xffffffffull)); }
+__device__ __forceinline__ float half_hi(unsigned long long v) { return __uint_as_float((unsigned)(v >> 32)); }
+__device__ __forceinline__ unsigned long long sub2(unsigned long long a, unsigned long long b) {
+  return pack2(half_lo(a) - half_lo(b), half_hi(a) - half_hi(b));
+}
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+  return pack2(half_lo(a) * half_lo(b), half_hi(a) * half_hi(b));
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  return pack2(fmaf(half_lo(a), half_lo(b), half_lo(c)), fmaf(half_hi(a), half_hi(b), half_hi(c)));
+}
+#else
 __device__ __forceinline__ unsigned long long sub2(unsigned long long a, unsigned long long b) {
   unsigned long long r;
   asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
@@ -90,6 +103,7 @@ __device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigne
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
   return r;
 }
+#endif
 
 __device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g) {
   const int lane = lane_id();
@@ -134,6 +148,63 @@ __device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cn
   __syncwarp();
   g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
   ++g.n_leaves;
+}
+
+// ---- pair sweep (experimental, k >= 32 only) -------------------------------------------------------
+// Two leaves per insertion phase: lanes whose survivors sit in different leaves sift at the same time,
+// which raises the number of active lanes per sift round (tools/sift_model.py: insertion cost 0.88 ->
+// 0.78 of the per-leaf schedule). Candidates live as x[64] | y[64] in the stage area and z[64] in the
+// soa area; ids are not kept (find-closest-point needs k == 1 and never takes this path).
+__device__ __forceinline__ void process_leaf_pair(const TreeView& t, int leaf_a, int cnt_a, int leaf_b, int cnt_b,
+                                                  GroupCtx& g) {
+  const int lane = lane_id();
+  float4 pa = make_float4(INFINITY, INFINITY, INFINITY, 0.f), pb = pa;
+  if (lane < cnt_a) pa = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf_a * kGroup + lane);
+  if (lane < cnt_b) pb = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf_b * kGroup + lane);
+  float* px = reinterpret_cast<float*>(g.stage);
+  float* py = px + 64;
+  float* pz = g.soa;
+  __syncwarp();
+  px[lane] = pa.x; px[32 + lane] = pb.x;
+  py[lane] = pa.y; py[32 + lane] = pb.y;
+  pz[lane] = pa.z; pz[32 + lane] = pb.z;
+  __syncwarp();
+
+  unsigned mask_a = 0, mask_b = 0;
+  const float top0 = g.top;
+  const unsigned long long qx2 = pack2(g.qx, g.qx), qy2 = pack2(g.qy, g.qy), qz2 = pack2(g.qz, g.qz);
+  const unsigned long long* sx = reinterpret_cast<const unsigned long long*>(px);
+  const unsigned long long* sy = reinterpret_cast<const unsigned long long*>(py);
+  const unsigned long long* sz = reinterpret_cast<const unsigned long long*>(pz);
+#pragma unroll
+  for (int jj = 0; jj < kGroup / 2; ++jj) {
+    const unsigned long long dx = sub2(qx2, sx[jj]), dy = sub2(qy2, sy[jj]), dz = sub2(qz2, sz[jj]);
+    const unsigned long long d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
+    mask_a |= (__uint_as_float((unsigned)(d2 & 0xffffffffull)) < top0) ? (1u << (2 * jj)) : 0u;
+    mask_a |= (__uint_as_float((unsigned)(d2 >> 32)) < top0) ? (2u << (2 * jj)) : 0u;
+  }
+#pragma unroll
+  for (int jj = 0; jj < kGroup / 2; ++jj) {
+    const unsigned long long dx = sub2(qx2, sx[16 + jj]), dy = sub2(qy2, sy[16 + jj]), dz = sub2(qz2, sz[16 + jj]);
+    const unsigned long long d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
+    mask_b |= (__uint_as_float((unsigned)(d2 & 0xffffffffull)) < top0) ? (1u << (2 * jj)) : 0u;
+    mask_b |= (__uint_as_float((unsigned)(d2 >> 32)) < top0) ? (2u << (2 * jj)) : 0u;
+  }
+  if (!g.valid) mask_a = mask_b = 0;
+
+  while (mask_a | mask_b) {
+    int j;
+    if (mask_a) { j = __ffs(mask_a) - 1; mask_a &= mask_a - 1; }
+    else        { j = 32 + __ffs(mask_b) - 1; mask_b &= mask_b - 1; }
+    const float d2 = dist2(g.qx, g.qy, g.qz, px[j], py[j], pz[j]);
+    if (d2 < g.top) {
+      g.top = heap_replace_padded(g.heap, g.kp, d2);
+      ++g.n_inserts;
+    }
+  }
+  __syncwarp();
+  g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
+  g.n_leaves += 2;
 }
 
 // ---- convergent fill ------------------------------------------------------------------------------
@@ -296,10 +367,15 @@ __device__ __forceinline__ void frontier_expand(const TreeView& t, int level, in
 
 // fill_leaves > 0: the valid lanes' heaps are fresh; the first fill_leaves leaves that come up are
 // appended without a test (see fill_leaf). fill_leaves * 32 <= k.
-template <class LeafOp>
+// PAIRS (heap kernels only): leaves that pass the per-query test are handled two at a time
+// (process_leaf_pair); the first of a pair waits in (pend_leaf, pend_cnt) while the traversal looks for
+// the second with a radius that does not yet know about the first — a stale radius is still an upper
+// bound, so the result is exact. Otherwise every leaf goes to leaf_op.
+template <bool PAIRS, class LeafOp>
 __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves, LeafOp& leaf_op) {
   const int lane = lane_id();
   int fill_pos = 0;
+  int pend_leaf = -1, pend_cnt = 0;
   unsigned* fr = g.frames;
   const int top_level = t.levels - 1;
   int depth = -1, qcount = 0;
@@ -395,14 +471,26 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       if (--fill_leaves == 0) fill_finish(g);
       continue;
     }
-    leaf_op(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
+    if constexpr (PAIRS) {
+      const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
+      if (!__any_sync(kFullMask, g.valid && (lb < g.top))) continue;
+      if (pend_leaf < 0) { pend_leaf = leaf; pend_cnt = cnt; continue; }
+      process_leaf_pair(t, pend_leaf, pend_cnt, leaf, cnt, g);
+      pend_leaf = -1;
+    } else {
+      leaf_op(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
+    }
   }
   if (fill_pos > 0 && fill_leaves > 0) fill_finish(g);    // the tree ran out of leaves during the fill
+  if constexpr (PAIRS) {
+    if (pend_leaf >= 0) process_leaf(t, pend_leaf, pend_cnt, g);
+  }
 }
 
+template <bool PAIRS = false>
 __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves = 0) {
   HeapLeafOp op;
-  traverse(t, g, seed_l1, fill_leaves, op);
+  traverse<PAIRS>(t, g, seed_l1, fill_leaves, op);
 }
 
 // Shared-memory floats per warp when the heap lives in GLOBAL memory (k too large for shared memory).
@@ -460,7 +548,7 @@ __device__ __forceinline__ void group_bounds(GroupCtx& g) {
 // is more than two thirds of the extent, recursively, and traverse each coherent sub-group on its own
 // (the other lanes are simply not valid during that pass). Exactness is unaffected.
 // fill_leaves: see traverse(); pass k / 32 for a group whose heaps are all fresh, else 0.
-template <class LeafOp>
+template <bool PAIRS, class LeafOp>
 __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1,
                                                int fill_leaves, LeafOp& leaf_op) {
   const int lane = lane_id();
@@ -503,15 +591,16 @@ __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, i
     // coherent enough: one pass. The group's own level-1 node is the natural seed only for the
     // unsplit group; a split part looks for the node nearest to it.
     const int seed = (m == all && own_seed_l1 != -2) ? own_seed_l1 : find_seed_l1(t, g);
-    traverse(t, g, seed, fill_leaves, leaf_op);
+    traverse<PAIRS>(t, g, seed, fill_leaves, leaf_op);
   }
   g.valid = lane < cnt;
 }
 
+template <bool PAIRS = false>
 __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1,
                                                int fill_leaves = 0) {
   HeapLeafOp op;
-  traverse_group(t, g, cnt, own_seed_l1, fill_leaves, op);
+  traverse_group<PAIRS>(t, g, cnt, own_seed_l1, fill_leaves, op);
 }
 
 __device__ __forceinline__ void flush_stats(const GroupCtx& g, unsigned long long* stats) {

@@ -4,6 +4,7 @@ numbers), interleaved with kNN calls that grow the heap; then one culled-exchang
 device vote and with the host vote (B200KNN_HOST_VOTE)."""
 import os
 import sys
+import time
 from pathlib import Path
 
 import numpy as np
@@ -39,7 +40,9 @@ def main() -> int:
             fails += 1
             print(f"[rank {rank}] MISMATCH {mode} N={N}", flush=True)
 
+    skew = np.random.default_rng(1000 + rank)                # different on every rank: launch skew
     for it in range(40):
+        time.sleep(float(skew.random()) * 0.003)
         words = int(torch.randint(1, 33, (1,), generator=g))
         table = torch.randint(-2**31, 2**31 - 1, (world, words), generator=g, dtype=torch.int64).to(torch.int32)
         got = eng.allgather_dev(table[rank].to(dev))
@@ -59,11 +62,13 @@ def main() -> int:
             knn_case(120_000, 100, "redistribute")
     # back-to-back without host synchronisation in between: only stream order separates them
     acc = torch.full((4,), rank + 1, dtype=torch.int64, device=dev)
-    for _ in range(50):
+    for i in range(2000):
+        if i % 97 == rank:
+            time.sleep(float(skew.random()) * 0.002)
         acc = eng.allreduce_dev(acc, "sum") % 1_000_003
     want = torch.full((4,), 0, dtype=torch.int64)
     vals = [r + 1 for r in range(world)]
-    for _ in range(50):
+    for _ in range(2000):
         s = sum(vals) % 1_000_003
         vals = [s] * world
     want[:] = vals[0]

@@ -144,6 +144,20 @@ def test_dist_engine_world1_every_mode_equals_oracle():
     eng.close()
 
 
+def test_n_times_k_beyond_int32():
+    """n * k = 2.2e9 > 2^31: the reference overflows its int offsets here
+    (/root/reference/unorderedDataVariant.cu:80); every offset in this library is 64-bit."""
+    n, k = 22_000_000, 100
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.rand((n, 3), device=_dev(), generator=g)
+    from mpi_cuda_largescaleknn_b200.ops.knn import knn
+    got = knn(x, k)
+    sel = torch.arange(0, n, n // 96, device=_dev())
+    xh = x.cpu().numpy()
+    # 16 oracle threads: each holds all n distances of one query (88 MB)
+    assert bit_equal(got[sel].cpu().numpy(), bruteforce(xh, queries=xh[sel.cpu().numpy()], k=k, threads=16))
+
+
 def test_knn_clustered_duplicates():
     x = np.concatenate([gen.clustered_surface(20_000, seed=2), np.zeros((100, 3), np.float32),
                         np.full((70, 3), 0.25, np.float32)])

@@ -28,7 +28,6 @@ def _check(x, q, k, r=math.inf):
     # every reported id really lies at the reported distance, and no id is reported twice
     for row in range(0, len(qq), max(1, len(qq) // 200)):
         have = ids[row] >= 0
-        got = bruteforce(x[ids[row][have]], queries=qq[row][None, :].repeat(have.sum(), 0), k=1) if False else None
         d = np.array([bruteforce(x[i][None, :], queries=qq[row][None, :], k=1)[0] for i in ids[row][have]], np.float32)
         assert bit_equal(d, dist[row][have])
         assert len(set(ids[row][have].tolist())) == int(have.sum())

@@ -1,0 +1,221 @@
+"""CPU-only: the CUDA kernels themselves, run under the host SIMT emulation (tests/simt): the same
+.cu sources compiled as C++, every CUDA thread a fiber, warp collectives implemented as exchanges
+between the 32 fibers of a warp. Checks the kernels' logic — radix sort, k-d refine, box tree, the
+group traversal with its heaps, frontier and fill phase, the culled-exchange and redistribution
+kernels on one rank, the no-allocation entry point — bit for bit against the brute-force oracle,
+on the machine that has no GPU. (Memory-model behaviour and speed are what only the GPU tests see.)"""
+import ctypes as C
+import math
+import platform
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from mpi_cuda_largescaleknn_b200.ops import _lib
+from mpi_cuda_largescaleknn_b200.utils import generators as gen
+from mpi_cuda_largescaleknn_b200.utils.oracle import bit_equal, bruteforce
+
+ROOT = Path(__file__).resolve().parents[1]
+pytestmark = pytest.mark.skipif(platform.machine() != "x86_64", reason="the emulation's fiber switch is x86-64 assembly")
+
+
+@pytest.fixture(scope="module")
+def sim():
+    out = subprocess.run(["make", "-C", str(ROOT), "simt"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert out.returncode == 0, out.stdout[-3000:]
+    lib = _lib._proto(C.CDLL(str(ROOT / "build" / "libb200knn_simt.so")))
+    lib.b200knn_knn_self_noalloc.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
+    lib.b200knn_knn_self_noalloc.restype = C.c_int
+    return lib
+
+
+def ok(lib, rc):
+    assert rc == 0, lib.b200knn_last_error().decode()
+
+
+class Index:
+    def __init__(self, lib, x):
+        self.lib, self.x, self.h = lib, np.ascontiguousarray(x, np.float32), C.c_void_p()
+        ok(lib, lib.b200knn_index_create(self.x.ctypes.data, len(self.x), None, 0, None, C.byref(self.h)))
+
+    def knn_self(self, k, r=math.inf):
+        out = np.full(len(self.x), -1.0, np.float32)
+        ok(self.lib, self.lib.b200knn_knn_self(self.h, k, r, out.ctypes.data, None))
+        return out
+
+    def knn_query(self, q, k, r=math.inf):
+        q = np.ascontiguousarray(q, np.float32)
+        out = np.full(len(q), -1.0, np.float32)
+        ok(self.lib, self.lib.b200knn_knn_query(self.h, q.ctypes.data, len(q), k, r, out.ctypes.data, None))
+        return out
+
+    def close(self):
+        self.lib.b200knn_index_destroy(self.h)
+
+
+@pytest.mark.parametrize("n,k", [(1, 1), (31, 3), (33, 8), (20, 50), (1000, 10), (2500, 32), (3000, 100), (1500, 221)])
+def test_emulated_self_knn_equals_oracle(sim, n, k):
+    x = gen.uniform(n, seed=7 * n + k)
+    idx = Index(sim, x)
+    assert bit_equal(idx.knn_self(k), bruteforce(x, k=k))
+    idx.close()
+
+
+def test_emulated_index_is_sorted_and_boxes_are_exact(sim):
+    n = 5000
+    x = gen.uniform(n, seed=3)
+    idx = Index(sim, x)
+    s = np.empty((n, 4), np.float32)
+    ok(sim, sim.b200knn_index_copy_sorted(idx.h, s.ctypes.data))
+    ids = s[:, 3].copy().view(np.uint32)
+    assert np.array_equal(np.sort(ids), np.arange(n, dtype=np.uint32))
+    assert np.array_equal(s[:, :3], x[ids])
+    nl = (n + 31) // 32
+    boxes = np.empty((nl, 8), np.float32)
+    cnt = C.c_int()
+    ok(sim, sim.b200knn_index_copy_boxes(idx.h, 0, boxes.ctypes.data, C.byref(cnt)))
+    assert cnt.value == nl
+    pts = np.concatenate([s[:, :3], np.full((nl * 32 - n, 3), np.nan, np.float32)]).reshape(nl, 32, 3)
+    assert np.array_equal(boxes[:, 0:3], np.nanmin(pts, axis=1)) and np.array_equal(boxes[:, 4:7], np.nanmax(pts, axis=1))
+    # k-d refinement: every full 1024-point run is 5 levels of exact median splits along the widest axis
+
+    def check_kd(seg, depth):
+        if depth == 5:
+            return
+        axis = int(np.argmax(seg.max(0) - seg.min(0)))
+        half = len(seg) // 2
+        assert seg[:half, axis].max() <= seg[half:, axis].min()
+        check_kd(seg[:half], depth + 1)
+        check_kd(seg[half:], depth + 1)
+
+    for run in range(n // 1024):
+        check_kd(s[run * 1024:(run + 1) * 1024, :3], 0)
+    idx.close()
+
+
+def test_emulated_radius_duplicates_and_clusters(sim):
+    x = np.concatenate([gen.clustered_surface(2000, seed=2), np.zeros((60, 3), np.float32),
+                        np.full((40, 3), 0.25, np.float32)])
+    idx = Index(sim, x)
+    assert bit_equal(idx.knn_self(32), bruteforce(x, k=32))
+    assert bit_equal(idx.knn_self(40, 0.05), bruteforce(x, k=40, max_radius=0.05))      # fill path with a cut-off
+    idx.close()
+    # two far-apart clusters: query groups straddle the gap and are split before traversal
+    y = np.concatenate([gen.uniform(700, seed=4) * 0.01, gen.uniform(700, seed=5) * 0.01 + 50.0]).astype(np.float32)
+    np.random.default_rng(0).shuffle(y)
+    idx = Index(sim, y)
+    assert bit_equal(idx.knn_self(20), bruteforce(y, k=20))
+    idx.close()
+
+
+def test_emulated_external_queries_and_fcp(sim):
+    x = gen.uniform(3000, seed=8)
+    q = gen.uniform(701, seed=9) * 1.4 - 0.2
+    idx = Index(sim, x)
+    assert bit_equal(idx.knn_query(q, 12), bruteforce(x, queries=q, k=12))
+    assert bit_equal(idx.knn_query(q, 40), bruteforce(x, queries=q, k=40))
+    ids = np.empty(len(q), np.int32)
+    dist = np.empty(len(q), np.float32)
+    ok(sim, sim.b200knn_fcp_query(idx.h, q.ctypes.data, len(q), math.inf, ids.ctypes.data, dist.ctypes.data, None))
+    assert bit_equal(dist, bruteforce(x, queries=q, k=1))
+    assert np.allclose(np.sqrt(((x[ids] - q) ** 2).sum(1)), dist, rtol=1e-5)
+    idx.close()
+
+
+def test_emulated_heap_in_global_memory(sim):
+    x = gen.uniform(2300, seed=77)
+    idx = Index(sim, x)
+    assert bit_equal(idx.knn_self(1900), bruteforce(x, k=1900))
+    idx.close()
+
+
+def test_emulated_no_alloc_entry_point(sim):
+    x = gen.uniform(4000, seed=11)
+    out = np.empty(len(x), np.float32)
+    for _ in range(2):
+        ok(sim, sim.b200knn_knn_self_noalloc(x.ctypes.data, len(x), 16, math.inf, out.ctypes.data, None))
+        assert bit_equal(out, bruteforce(x, k=16))
+
+
+def test_emulated_distributed_driver_single_rank(sim):
+    """world = 1: culled-exchange kernels (LOCAL phase), redistribution scatter, result return."""
+    from mpi_cuda_largescaleknn_b200.parallel.dist import Bootstrap, ALLGATHER_FN, BARRIER_FN, DistReport, MODES
+    x = gen.uniform(6000, seed=31)
+    bs = Bootstrap(None, 0, 1, ALLGATHER_FN(lambda *a: 1), BARRIER_FN(lambda *a: 1))
+    eng = C.c_void_p()
+    sim.b200knn_dist_create.argtypes = [C.POINTER(Bootstrap), C.POINTER(C.c_void_p)]
+    ok(sim, sim.b200knn_dist_create(C.byref(bs), C.byref(eng)))
+    sim.b200knn_dist_knn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_float, C.c_int, C.c_int,
+                                     C.c_void_p, C.c_void_p, C.POINTER(DistReport)]
+    want = bruteforce(x, k=40)
+    for mode in ("prepartitioned", "redistribute", "auto"):
+        out = np.empty(len(x), np.float32)
+        rep = DistReport()
+        ok(sim, sim.b200knn_dist_knn(eng, x.ctypes.data, len(x), 0, 40, math.inf, MODES[mode], 0, out.ctypes.data, None,
+                                     C.byref(rep)))
+        assert bit_equal(out, want), mode
+    sim.b200knn_dist_destroy.argtypes = [C.c_void_p]
+    sim.b200knn_dist_destroy(eng)
+
+
+def test_emulated_pair_sweep_variant(sim):
+    """The experimental two-leaves-per-insertion-phase kernels (B200KNN_PAIRS=1, read once per process):
+    same suite in a child process with the switch on."""
+    import os
+    import sys
+    env = dict(os.environ, B200KNN_PAIRS="1")
+    out = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-x", "-q", "-k",
+                          "self_knn or radius or single_rank or external"], cwd=str(ROOT), env=env,
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert out.returncode == 0, out.stdout[-3000:]
+
+
+def _neighbors(lib, idx, q, k, r=math.inf):
+    fn = lib.b200knn_knn_neighbors
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    fn.restype = C.c_int
+    nq = len(idx.x) if q is None else len(q)
+    ids = np.full((nq, k), -7, np.int32)
+    dist = np.full((nq, k), -7.0, np.float32)
+    ok(lib, fn(idx.h, None if q is None else q.ctypes.data, nq, k, r, ids.ctypes.data, dist.ctypes.data, None))
+    order = np.argsort(dist, axis=1, kind="stable")
+    return np.take_along_axis(ids, order, 1), np.take_along_axis(dist, order, 1)
+
+
+@pytest.mark.parametrize("n,k,r", [(1, 1, math.inf), (40, 8, math.inf), (10, 16, math.inf), (3000, 1, math.inf),
+                                   (3000, 32, math.inf), (2500, 100, math.inf), (3000, 40, 0.05)])
+def test_emulated_neighbor_lists(sim, n, k, r):
+    """k nearest neighbours WITH ids: distances bit-identical to the brute-force neighbour oracle, every id lies
+    at its reported distance, no id twice, padding where fewer than k points are in range."""
+    from mpi_cuda_largescaleknn_b200.utils.oracle import neighbors_bruteforce
+    x = gen.uniform(n, seed=n + k)
+    idx = Index(sim, x)
+    for q in (None, (gen.uniform(333, seed=k) * 1.3 - 0.15).astype(np.float32)):
+        ids, dist = _neighbors(sim, idx, q, k, r)
+        qq = x if q is None else q
+        want_ids, want_dist = neighbors_bruteforce(x, qq, k=k, max_radius=r)
+        assert bit_equal(dist, want_dist)
+        assert np.array_equal(ids >= 0, want_ids >= 0)
+        for row in range(0, len(qq), max(1, len(qq) // 150)):
+            have = ids[row] >= 0
+            d = np.array([bruteforce(x[i][None, :], queries=qq[row][None, :], k=1)[0] for i in ids[row][have]], np.float32)
+            assert bit_equal(d, dist[row][have])
+            assert len(set(ids[row][have].tolist())) == int(have.sum())
+    idx.close()
+
+
+def test_emulated_neighbor_lists_with_exact_ties(sim):
+    from mpi_cuda_largescaleknn_b200.utils.oracle import neighbors_bruteforce
+    x = np.concatenate([gen.uniform(800, seed=2), np.full((300, 3), 0.5, np.float32),
+                        np.random.default_rng(1).integers(0, 3, (400, 3)).astype(np.float32)])
+    idx = Index(sim, x)
+    ids, dist = _neighbors(sim, idx, None, 64)
+    want_ids, want_dist = neighbors_bruteforce(x, x, k=64)
+    assert bit_equal(dist, want_dist)
+    for row in range(0, len(x), 11):
+        assert len(set(ids[row].tolist())) == 64
+        d = np.array([bruteforce(x[i][None, :], queries=x[row][None, :], k=1)[0] for i in ids[row]], np.float32)
+        assert bit_equal(d, dist[row])
+    idx.close()
