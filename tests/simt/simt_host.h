@@ -3,7 +3,8 @@
 // The kernels are compiled UNCHANGED as host C++ (tests/simt/preprocess.py only rewrites the
 // `kernel<<<grid, block, smem, stream>>>(args)` launch syntax and `extern __shared__` declarations).
 // Execution model:
-//   * blocks of a grid run one after the other;
+//   * one OS thread per emulated GPU (a "rank" of the multi-GPU tests; peer memory is plain shared
+//     memory, CUDA IPC handles are pointers); within it blocks of a grid run one after the other;
 //   * the threads of a block are fibers (ucontext) inside ONE operating-system thread, resumed
 //     round-robin; a fiber runs until it reaches a warp- or block-level collective (__shfl*_sync,
 //     __ballot_sync, __reduce_*_sync, __match_any_sync, __syncwarp, __syncthreads) and yields there
@@ -12,8 +13,8 @@
 //     thing), dynamic shared memory is one buffer per launch, "device" memory is host memory, streams
 //     are synchronous.
 // What it checks: the logic of the kernels — indexing, warp-collective protocols, heap and traversal
-// code, launch geometry. What it cannot check: memory-model races, performance, inter-process peer
-// memory (CUDA IPC calls fail here; single-rank paths only).
+// code, launch geometry, and the flag protocols between ranks as far as a sequentially consistent
+// x86 host exercises them. What it cannot check: the GPU memory model, performance.
 #pragma once
 #include <math.h>
 #include <stdint.h>
@@ -32,7 +33,7 @@
 #define __restrict__
 #define __launch_bounds__(...)
 #define __align__(n) __attribute__((aligned(n)))
-#define __shared__ static
+#define __shared__ static thread_local      // one OS thread per emulated GPU (rank): its blocks run one at a time
 
 // ---------------------------------------------------------------- vector types
 struct alignas(16) float4 { float x, y, z, w; };
@@ -62,6 +63,7 @@ Barrier& block_barrier();
 Warp& my_warp();
 int my_lane();
 void* dyn_smem();
+void yield_if_fiber();                  // spin loops on another rank's flags must let their own block run
 
 // Deposit one 64-bit word per lane, wait for the warp, return the buffer all lanes wrote into. Buffers
 // alternate by barrier generation: a lane can only reach collective c+2 after everybody has read c.
@@ -79,14 +81,14 @@ template <class T> inline T from_bits(uint64_t u) { T v; memcpy(&v, &u, sizeof(T
 }  // namespace simt
 
 // Built-in variables: one OS thread, so plain globals that the scheduler rewrites before every resume.
-extern dim3 threadIdx, blockIdx, blockDim, gridDim;
+extern thread_local dim3 threadIdx, blockIdx, blockDim, gridDim;
 
 // ---------------------------------------------------------------- warp / block collectives
 inline void __syncwarp(unsigned = 0xffffffffu) { simt::arrive_and_wait(simt::my_warp().bar); }
 inline void __syncthreads() { simt::arrive_and_wait(simt::block_barrier()); }
-inline void __threadfence() {}
+inline void __threadfence() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
 inline void __threadfence_block() {}
-inline void __threadfence_system() {}
+inline void __threadfence_system() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
 
 template <class T> inline T __shfl_sync(unsigned, T v, int src, int = 32) {
   const uint64_t* b = simt::exchange(simt::to_bits(v));
@@ -166,17 +168,18 @@ inline int __clzll(unsigned long long v) { return v ? __builtin_clzll(v) : 64; }
 template <class T> inline T __ldg(const T* p) { return *p; }
 template <class T> inline T __ldcg(const T* p) { return *p; }
 template <class T> inline T __ldcs(const T* p) { return *p; }
-inline void __nanosleep(unsigned) {}
+inline void __nanosleep(unsigned) { simt::yield_if_fiber(); }
 inline long long clock64() { static long long c = 0; return c += 1000; }
 inline void __trap() { fprintf(stderr, "simt: __trap()\n"); abort(); }
 
-template <class T> inline T atomicAdd(T* p, T v) { T o = *p; *p = o + v; return o; }
-inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { unsigned long long o = *p; *p = o + v; return o; }
-template <class T> inline T atomicMin(T* p, T v) { T o = *p; if (v < o) *p = v; return o; }
-template <class T> inline T atomicMax(T* p, T v) { T o = *p; if (v > o) *p = v; return o; }
-template <class T> inline T atomicExch(T* p, T v) { T o = *p; *p = v; return o; }
-template <class T> inline T atomicCAS(T* p, T cmp, T v) { T o = *p; if (o == cmp) *p = v; return o; }
-template <class T> inline T atomicOr(T* p, T v) { T o = *p; *p = o | v; return o; }
+// Atomics are real atomics: another rank's thread may touch the same word (peer memory).
+template <class T> inline T atomicAdd(T* p, T v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
+inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicExch(T* p, T v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicCAS(T* p, T cmp, T v) { __atomic_compare_exchange_n(p, &cmp, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST); return cmp; }
+template <class T> inline T atomicOr(T* p, T v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
+template <class T> inline T atomicMin(T* p, T v) { T o = __atomic_load_n(p, __ATOMIC_SEQ_CST); while (v < o && !__atomic_compare_exchange_n(p, &o, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {} return o; }
+template <class T> inline T atomicMax(T* p, T v) { T o = __atomic_load_n(p, __ATOMIC_SEQ_CST); while (v > o && !__atomic_compare_exchange_n(p, &o, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {} return o; }
 
 // ---------------------------------------------------------------- runtime API (synchronous, host memory)
 typedef int cudaError_t;
@@ -215,6 +218,7 @@ template <class F> inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute,
 template <class F> inline cudaError_t cudaFuncGetAttributes(cudaFuncAttributes* a, F) { *a = cudaFuncAttributes(); return cudaSuccess; }
 template <class F> inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, F, int, size_t) { *n = 1; return cudaSuccess; }
 template <class T> inline cudaError_t cudaGetSymbolAddress(void** p, T& symbol) { *p = (void*)&symbol; return cudaSuccess; }
-inline cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t*, void*) { return cudaErrorNotSupported; }
-inline cudaError_t cudaIpcOpenMemHandle(void**, cudaIpcMemHandle_t, unsigned) { return cudaErrorNotSupported; }
-inline cudaError_t cudaIpcCloseMemHandle(void*) { return cudaErrorNotSupported; }
+// "Peer memory": ranks are threads of one process, so a handle is the pointer itself.
+inline cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t* h, void* p) { memset(h, 0, sizeof(*h)); memcpy(h->reserved, &p, sizeof(p)); return cudaSuccess; }
+inline cudaError_t cudaIpcOpenMemHandle(void** p, cudaIpcMemHandle_t h, unsigned) { memcpy(p, h.reserved, sizeof(*p)); return cudaSuccess; }
+inline cudaError_t cudaIpcCloseMemHandle(void*) { return cudaSuccess; }

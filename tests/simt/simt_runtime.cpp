@@ -37,7 +37,7 @@ simt_switch:
 )");
 extern "C" void simt_switch(void** save_sp, void* load_sp);
 
-dim3 threadIdx, blockIdx, blockDim, gridDim;
+thread_local dim3 threadIdx, blockIdx, blockDim, gridDim;
 
 namespace simt {
 namespace {
@@ -60,12 +60,13 @@ struct State {
   unsigned long long progress = 0;       // barrier releases + fiber exits: no change over a whole round = deadlock
   const std::function<void()>* body = nullptr;
 };
-State& state() { static State s; return s; }
+State& state() { static thread_local State s; return s; }
 
 void yield() {
   State& s = state();
   simt_switch(&s.fibers[s.current].sp, s.sched_sp);
 }
+
 
 void fiber_main() {
   State& s = state();
@@ -127,6 +128,14 @@ void arrive_and_wait(Barrier& b) {
   while (b.gen == my) yield();
 }
 
+// Called from spin loops that wait for ANOTHER rank (its thread makes the progress): yield to the rest of
+// this block and tell the deadlock detector that waiting here is legitimate.
+void yield_if_fiber() {
+  State& s = state();
+  if (s.current < 0) return;
+  ++s.progress;
+  yield();
+}
 Barrier& block_barrier() { return state().block_bar; }
 Warp& my_warp() { State& s = state(); return s.warps[s.current >> 5]; }
 int my_lane() { return state().current & 31; }
