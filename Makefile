@@ -89,3 +89,24 @@ $(SIMT_LIB): $(patsubst %.cpp,%.o,$(SIMT_SRCS)) $(SIMT_DIR)/simt_runtime.o $(CPP
 	$(CXX) -shared -o $@ $^ -lpthread -ldl
 .PHONY: simt
 .SECONDARY: $(SIMT_SRCS)
+
+# ---- the same emulation under ThreadSanitizer: race detection for the protocols BETWEEN ranks ----
+#   make simt-tsan && LD_PRELOAD=$$(gcc -print-file-name=libtsan.so) B200KNN_SIMT_LIB=build/libb200knn_simt_tsan.so \
+#       python tests/simt/multirank_worker.py 2 uniform chunks
+TSAN_DIR := $(BUILD)/simt_tsan
+TSAN_LIB := $(BUILD)/libb200knn_simt_tsan.so
+TSAN_CXX ?= /usr/bin/g++
+TSAN_FLAGS := $(SIMT_FLAGS) -fsanitize=thread --param tsan-instrument-func-entry-exit=0
+simt-tsan: $(TSAN_LIB)
+$(TSAN_DIR)/%.o: $(SIMT_DIR)/%.cpp tests/simt/simt_host.h csrc/*.h csrc/*.cuh include/b200knn.h
+	@mkdir -p $(TSAN_DIR)
+	$(TSAN_CXX) $(TSAN_FLAGS) -c $< -o $@
+$(TSAN_DIR)/simt_runtime.o: tests/simt/simt_runtime.cpp tests/simt/simt_host.h
+	@mkdir -p $(TSAN_DIR)
+	$(TSAN_CXX) $(TSAN_FLAGS) -c $< -o $@
+$(TSAN_DIR)/cpu_engine.o: csrc/cpu_engine.cpp csrc/*.h include/b200knn.h
+	@mkdir -p $(TSAN_DIR)
+	$(TSAN_CXX) $(CXXFLAGS) -fsanitize=thread --param tsan-instrument-func-entry-exit=0 -c $< -o $@
+$(TSAN_LIB): $(patsubst $(SIMT_DIR)/%.cpp,$(TSAN_DIR)/%.o,$(SIMT_SRCS)) $(TSAN_DIR)/simt_runtime.o $(TSAN_DIR)/cpu_engine.o
+	$(TSAN_CXX) -shared -fsanitize=thread -o $@ $^ -lpthread -ldl
+.PHONY: simt-tsan

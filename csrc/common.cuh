@@ -67,7 +67,12 @@ __host__ __device__ __forceinline__ float ord2f(unsigned u) {
 }
 
 // ---- system-scope release/acquire flags (visible across NVLink peers) ----
-#if defined(B200KNN_SIMT_HOST)   // host emulation of the kernels (tests/simt): ranks are threads, flags are C++ atomics
+#if defined(B200KNN_SIMT_HOST) && defined(B200KNN_SIMT_BROKEN_FLAGS)
+// Self-test of the race detector (make simt-tsan-selftest): flags without release/acquire must be reported.
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) { *(volatile unsigned*)p = v; }
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) { return *(volatile const unsigned*)p; }
+__device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned* p) { return *(volatile const unsigned*)p; }
+#elif defined(B200KNN_SIMT_HOST)   // host emulation of the kernels (tests/simt): ranks are threads, flags are C++ atomics
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
 __device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }

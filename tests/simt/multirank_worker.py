@@ -25,7 +25,8 @@ from mpi_cuda_largescaleknn_b200.utils.oracle import bit_equal, bruteforce  # no
 
 
 def load():
-    lib = _lib._proto(C.CDLL(str(ROOT / "build" / "libb200knn_simt.so")))
+    import os
+    lib = _lib._proto(C.CDLL(os.environ.get("B200KNN_SIMT_LIB", str(ROOT / "build" / "libb200knn_simt.so"))))
     lib.b200knn_dist_create.argtypes = [C.POINTER(Bootstrap), C.POINTER(C.c_void_p)]
     lib.b200knn_dist_knn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_float, C.c_int, C.c_int,
                                      C.c_void_p, C.c_void_p, C.POINTER(DistReport)]

@@ -169,7 +169,7 @@ template <class T> inline T __ldg(const T* p) { return *p; }
 template <class T> inline T __ldcg(const T* p) { return *p; }
 template <class T> inline T __ldcs(const T* p) { return *p; }
 inline void __nanosleep(unsigned) { simt::yield_if_fiber(); }
-inline long long clock64() { static long long c = 0; return c += 1000; }
+inline long long clock64() { static thread_local long long c = 0; return c += 1000; }
 inline void __trap() { fprintf(stderr, "simt: __trap()\n"); abort(); }
 
 // Atomics are real atomics: another rank's thread may touch the same word (peer memory).

@@ -7,6 +7,24 @@
 #include <unistd.h>
 #include "simt_host.h"
 
+// ThreadSanitizer build (make simt-tsan). By default it is compiled without function entry/exit
+// instrumentation (--param tsan-instrument-func-entry-exit=0): the sanitizer then keeps no shadow call
+// stack that the fiber switches could upset, all fibers of a rank are simply the rank's OS thread, and what
+// is left for it to report are unordered accesses BETWEEN ranks, i.e. holes in the flag / barrier protocols.
+// With -DSIMT_TSAN_FIBERS the fibers are announced through the sanitizer's fiber interface instead (full
+// stacks in the reports, an order of magnitude slower).
+#if defined(__SANITIZE_THREAD__) && defined(SIMT_TSAN_FIBERS)
+extern "C" {
+void* __tsan_get_current_fiber(void);
+void* __tsan_create_fiber(unsigned flags);
+void __tsan_destroy_fiber(void* fiber);
+void __tsan_switch_to_fiber(void* fiber, unsigned flags);
+}
+#define SIMT_TSAN_SWITCH(f) __tsan_switch_to_fiber((f), 0)
+#else
+#define SIMT_TSAN_SWITCH(f) ((void)0)
+#endif
+
 #if !defined(__x86_64__)
 #error "the fiber switch of the host emulation is written for x86-64"
 #endif
@@ -46,11 +64,14 @@ constexpr size_t kFiberStack = 96 * 1024;
 
 struct Fiber {
   void* sp = nullptr;
+  void* tsan = nullptr;
   bool done = false;
 };
 
 struct State {
   void* sched_sp = nullptr;
+  void* sched_tsan = nullptr;
+  std::vector<void*> tsan_pool;          // sanitizer fibers are expensive to create: one pool per rank thread, reused
   std::vector<Fiber> fibers;
   std::vector<Warp> warps;
   Barrier block_bar;
@@ -64,6 +85,7 @@ State& state() { static thread_local State s; return s; }
 
 void yield() {
   State& s = state();
+  SIMT_TSAN_SWITCH(s.sched_tsan);
   simt_switch(&s.fibers[s.current].sp, s.sched_sp);
 }
 
@@ -83,6 +105,7 @@ void fiber_main() {
   if (w.bar.expected > 0 && w.bar.arrived >= w.bar.expected) { w.bar.arrived = 0; ++w.bar.gen; ++s.progress; }
   --s.block_bar.expected;
   if (s.block_bar.expected > 0 && s.block_bar.arrived >= s.block_bar.expected) { s.block_bar.arrived = 0; ++s.block_bar.gen; ++s.progress; }
+  SIMT_TSAN_SWITCH(s.sched_tsan);
   simt_switch(&f.sp, s.sched_sp);
   abort();                               // a finished fiber is never resumed
 }
@@ -171,6 +194,11 @@ void launch(const char* name, dim3 grid, dim3 block, size_t smem_bytes, const st
     s.block_bar = Barrier();
     s.block_bar.expected = nthreads;
     for (int t = 0; t < nthreads; ++t) s.fibers[t].sp = fresh_stack(s.stacks.data() + (size_t)t * kFiberStack);
+#if defined(__SANITIZE_THREAD__) && defined(SIMT_TSAN_FIBERS)
+    s.sched_tsan = __tsan_get_current_fiber();
+    while ((int)s.tsan_pool.size() < nthreads) s.tsan_pool.push_back(__tsan_create_fiber(0));
+    for (int t = 0; t < nthreads; ++t) s.fibers[t].tsan = s.tsan_pool[t];
+#endif
     int live = nthreads, stuck = 0;
     while (live > 0) {
       const unsigned long long before = s.progress;
@@ -179,6 +207,7 @@ void launch(const char* name, dim3 grid, dim3 block, size_t smem_bytes, const st
         if (f.done) continue;
         s.current = t;
         threadIdx = dim3((unsigned)t);
+        SIMT_TSAN_SWITCH(f.tsan);
         simt_switch(&s.sched_sp, f.sp);
         if (f.done) --live;
       }
@@ -187,6 +216,7 @@ void launch(const char* name, dim3 grid, dim3 block, size_t smem_bytes, const st
       stuck = (s.progress == before) ? stuck + 1 : 0;
       if (stuck > 2) { fprintf(stderr, "simt: %s, block %u: deadlock at a collective that not all lanes reach\n", name, b); abort(); }
     }
+
   }
   s.current = -1;
   s.body = nullptr;
