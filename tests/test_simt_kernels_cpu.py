@@ -219,3 +219,48 @@ def test_emulated_neighbor_lists_with_exact_ties(sim):
         d = np.array([bruteforce(x[i][None, :], queries=x[row][None, :], k=1)[0] for i in ids[row]], np.float32)
         assert bit_equal(d, dist[row])
     idx.close()
+
+
+def test_emulated_frontier_overflow_paths_are_exercised_and_exact(sim):
+    """k = 500 on 20 000 points: the 128-entry frontier overflows, stale entries are purged, and some nodes
+    fall back to the depth-first frame stack. The counters prove the paths ran; the result stays exact."""
+    x = gen.uniform(20_000, seed=1)
+    idx = Index(sim, x)
+    ok(sim, sim.b200knn_index_enable_stats(idx.h, 1))
+    got = idx.knn_self(500)
+    st = (C.c_uint64 * 8)()
+    ok(sim, sim.b200knn_index_stats(idx.h, st))
+    assert st[4] > 0 and st[5] > 0, f"fallbacks {st[4]}, purges {st[5]}"
+    sel = np.arange(0, len(x), 40)
+    assert bit_equal(got[sel], bruteforce(x, queries=x[sel], k=500))
+    idx.close()
+
+
+def test_emulated_kernels_on_degenerate_clouds(sim):
+    """Property-style sweep through the real kernel code: lines, planes, grids full of exact ties, two far
+    clusters, everything identical, huge and tiny coordinate scales."""
+    rng = np.random.default_rng(123)
+    for trial in range(24):
+        n = int(rng.integers(1, 900))
+        kind = ["random", "grid", "line", "plane", "two_clusters", "all_equal"][trial % 6]
+        if kind == "random":
+            x = rng.random((n, 3), dtype=np.float32)
+        elif kind == "grid":
+            x = rng.integers(0, 4, (n, 3)).astype(np.float32)
+        elif kind == "line":
+            x = np.zeros((n, 3), np.float32)
+            x[:, 0] = rng.random(n, dtype=np.float32)
+        elif kind == "plane":
+            x = rng.random((n, 3), dtype=np.float32)
+            x[:, 2] = np.float32(0.25)
+        elif kind == "two_clusters":
+            x = rng.normal(0, 0.01, (n, 3)).astype(np.float32)
+            x[n // 2:] += np.float32(50.0)
+        else:
+            x = np.full((n, 3), np.float32(rng.normal()), np.float32)
+        x = np.ascontiguousarray(x * np.float32([1e-3, 1.0, 1e3, 1e6][trial % 4]))
+        k = int(rng.integers(1, 70))
+        r = [math.inf, 0.3, math.inf, 10.0][trial % 4]
+        idx = Index(sim, x)
+        assert bit_equal(idx.knn_self(k, r), bruteforce(x, k=k, max_radius=r)), (trial, kind, n, k, r)
+        idx.close()
