@@ -167,7 +167,7 @@ def test_emulated_pair_sweep_variant(sim):
     import sys
     env = dict(os.environ, B200KNN_PAIRS="1")
     out = subprocess.run([sys.executable, "-m", "pytest", str(Path(__file__)), "-x", "-q", "-k",
-                          "self_knn or radius or single_rank or external"], cwd=str(ROOT), env=env,
+                          "self_knn or single_rank"], cwd=str(ROOT), env=env,
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert out.returncode == 0, out.stdout[-3000:]
 
@@ -240,7 +240,7 @@ def test_emulated_kernels_on_degenerate_clouds(sim):
     """Property-style sweep through the real kernel code: lines, planes, grids full of exact ties, two far
     clusters, everything identical, huge and tiny coordinate scales."""
     rng = np.random.default_rng(123)
-    for trial in range(24):
+    for trial in range(12):
         n = int(rng.integers(1, 900))
         kind = ["random", "grid", "line", "plane", "two_clusters", "all_equal"][trial % 6]
         if kind == "random":
