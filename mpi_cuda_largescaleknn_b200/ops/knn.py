@@ -23,11 +23,16 @@ def _stream_ptr() -> int:
 
 
 def _as_xyz(points: torch.Tensor) -> torch.Tensor:
-    if points.dim() != 2 or points.shape[1] != 3:
-        raise ValueError("points must have shape [N, 3]")
+    """[N,3] float32 contiguous. [N,2] input (the reference library's float2 trees) gets z = 0: the squared
+    distance fmaf(0,0, fmaf(dx,dx, dy*dy)) is bit for bit the 2-D expression."""
+    if points.dim() != 2 or points.shape[1] not in (2, 3):
+        raise ValueError("points must have shape [N, 3] (or [N, 2])")
     if not points.is_cuda:
         raise ValueError("points must be a CUDA tensor (use utils.oracle for CPU work)")
-    return points.detach().to(torch.float32).contiguous()
+    points = points.detach().to(torch.float32)
+    if points.shape[1] == 2:
+        points = torch.cat([points, points.new_zeros((points.shape[0], 1))], dim=1)
+    return points.contiguous()
 
 
 class KnnIndex:

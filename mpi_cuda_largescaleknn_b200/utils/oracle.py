@@ -18,8 +18,10 @@ from ..ops._lib import check, lib
 
 def _f32c(a) -> np.ndarray:
     a = np.ascontiguousarray(a, dtype=np.float32)
-    if a.ndim != 2 or a.shape[1] != 3:
-        raise ValueError("expected an [N,3] array")
+    if a.ndim != 2 or a.shape[1] not in (2, 3):
+        raise ValueError("expected an [N,3] (or [N,2]) array")
+    if a.shape[1] == 2:                      # 2-D clouds: z = 0 gives the 2-D distance bit for bit
+        a = np.ascontiguousarray(np.concatenate([a, np.zeros((len(a), 1), np.float32)], axis=1))
     return a
 
 

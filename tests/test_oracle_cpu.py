@@ -90,3 +90,16 @@ def test_neighbors_bruteforce_rows_are_the_k_smallest_sorted():
     assert np.all(ids2[:, 5:] == -1) and np.all(np.isinf(dist2[:, 5:])) and np.all(ids2[:, :5] >= 0)
     ids3, dist3 = neighbors_bruteforce(x, q, k=9, max_radius=0.05)
     assert np.all((dist3 < 0.05) == (ids3 >= 0))
+
+
+def test_two_dimensional_clouds_are_exact():
+    """[N,2] input (the reference library's float2 trees): padding z = 0 reproduces fmaf(dx,dx, dy*dy) exactly."""
+    rng = np.random.default_rng(5)
+    x = rng.random((600, 2), dtype=np.float32)
+    d2 = np.empty((600, 600), np.float32)
+    for i in range(600):
+        dx, dy = x[i, 0] - x[:, 0], x[i, 1] - x[:, 1]
+        d2[i] = (dx.astype(np.float64) * dx.astype(np.float64) + (dy * dy).astype(np.float64)).astype(np.float32)   # fmaf(dx,dx,dy*dy)
+    want = np.sqrt(np.sort(d2, axis=1)[:, 6])
+    assert bit_equal(bruteforce(x, k=7), want)
+    assert bit_equal(cpu_knn(x, k=7), want)
