@@ -110,3 +110,23 @@ $(TSAN_DIR)/cpu_engine.o: csrc/cpu_engine.cpp csrc/*.h include/b200knn.h
 $(TSAN_LIB): $(patsubst $(SIMT_DIR)/%.cpp,$(TSAN_DIR)/%.o,$(SIMT_SRCS)) $(TSAN_DIR)/simt_runtime.o $(TSAN_DIR)/cpu_engine.o
 	$(TSAN_CXX) -shared -fsanitize=thread -o $@ $^ -lpthread -ldl
 .PHONY: simt-tsan
+
+# ---- the same emulation under AddressSanitizer: out-of-bounds / use-after-free in "device" memory ----
+#   make simt-asan && LD_PRELOAD=$$(gcc -print-file-name=libasan.so) ASAN_OPTIONS=detect_leaks=0 \
+#       B200KNN_SIMT_LIB=build/libb200knn_simt_asan.so python tests/simt/multirank_worker.py 2 uniform chunks
+ASAN_DIR := $(BUILD)/simt_asan
+ASAN_LIB := $(BUILD)/libb200knn_simt_asan.so
+ASAN_FLAGS := $(SIMT_FLAGS) -fsanitize=address -fno-omit-frame-pointer
+simt-asan: $(ASAN_LIB)
+$(ASAN_DIR)/%.o: $(SIMT_DIR)/%.cpp tests/simt/simt_host.h csrc/*.h csrc/*.cuh include/b200knn.h
+	@mkdir -p $(ASAN_DIR)
+	$(TSAN_CXX) $(ASAN_FLAGS) -c $< -o $@
+$(ASAN_DIR)/simt_runtime.o: tests/simt/simt_runtime.cpp tests/simt/simt_host.h
+	@mkdir -p $(ASAN_DIR)
+	$(TSAN_CXX) $(ASAN_FLAGS) -c $< -o $@
+$(ASAN_DIR)/cpu_engine.o: csrc/cpu_engine.cpp csrc/*.h include/b200knn.h
+	@mkdir -p $(ASAN_DIR)
+	$(TSAN_CXX) $(CXXFLAGS) -fsanitize=address -c $< -o $@
+$(ASAN_LIB): $(patsubst $(SIMT_DIR)/%.cpp,$(ASAN_DIR)/%.o,$(SIMT_SRCS)) $(ASAN_DIR)/simt_runtime.o $(ASAN_DIR)/cpu_engine.o
+	$(TSAN_CXX) -shared -fsanitize=address -o $@ $^ -lpthread -ldl
+.PHONY: simt-asan

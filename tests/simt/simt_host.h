@@ -198,7 +198,9 @@ struct cudaFuncAttributes { int numRegs = 0; size_t sharedSizeBytes = 0; int max
 
 inline const char* cudaGetErrorString(cudaError_t e) { return e == cudaSuccess ? "no error" : "simt: operation not available on the host emulation"; }
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
-inline cudaError_t cudaMalloc(void** p, size_t n) { *p = aligned_alloc(256, (n + 255) / 256 * 256 + 256); return *p ? cudaSuccess : 2; }
+// exactly n bytes (256-byte aligned like the real allocator): under AddressSanitizer an access one byte past a
+// "device" buffer is reported
+inline cudaError_t cudaMalloc(void** p, size_t n) { *p = nullptr; return posix_memalign(p, 256, n ? n : 1) == 0 ? cudaSuccess : 2; }
 template <class T> inline cudaError_t cudaMalloc(T** p, size_t n) { return cudaMalloc((void**)p, n); }
 inline cudaError_t cudaFree(void* p) { free(p); return cudaSuccess; }
 template <class T> inline cudaError_t cudaMallocAsync(T** p, size_t n, cudaStream_t) { return cudaMalloc((void**)p, n); }

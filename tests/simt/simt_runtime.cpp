@@ -76,7 +76,7 @@ struct State {
   std::vector<Warp> warps;
   Barrier block_bar;
   std::vector<char> stacks;
-  std::vector<char> dyn;
+  char* dyn = nullptr;                   // dynamic shared memory of the current launch, exactly as large as requested
   int current = -1;
   unsigned long long progress = 0;       // barrier releases + fiber exits: no change over a whole round = deadlock
   const std::function<void()>* body = nullptr;
@@ -163,10 +163,7 @@ Barrier& block_barrier() { return state().block_bar; }
 Warp& my_warp() { State& s = state(); return s.warps[s.current >> 5]; }
 int my_lane() { return state().current & 31; }
 
-void* dyn_smem() {
-  const uintptr_t p = (uintptr_t)state().dyn.data();
-  return (void*)((p + 63) / 64 * 64);
-}
+void* dyn_smem() { return state().dyn; }
 
 // SIMT_DEBUG=<seconds>: print every launch, and if one launch runs longer than that, say where it is.
 void launch(const char* name, dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()>& body) {
@@ -182,7 +179,10 @@ void launch(const char* name, dim3 grid, dim3 block, size_t smem_bytes, const st
   if (block.y != 1 || block.z != 1 || grid.y != 1 || grid.z != 1) { fprintf(stderr, "simt: only 1-D launches\n"); abort(); }
   if (s.current >= 0) { fprintf(stderr, "simt: kernels cannot launch kernels\n"); abort(); }
   if (s.stacks.size() < (size_t)nthreads * kFiberStack) s.stacks.resize((size_t)nthreads * kFiberStack);
-  s.dyn.assign(smem_bytes + 64, 0);
+  free(s.dyn);
+  s.dyn = nullptr;
+  if (posix_memalign((void**)&s.dyn, 128, smem_bytes ? smem_bytes : 1)) abort();
+  memset(s.dyn, 0, smem_bytes ? smem_bytes : 1);
   s.body = &body;
   gridDim = grid;
   blockDim = block;

@@ -25,7 +25,8 @@ pytestmark = pytest.mark.skipif(platform.machine() != "x86_64", reason="the emul
 def sim():
     out = subprocess.run(["make", "-C", str(ROOT), "simt"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert out.returncode == 0, out.stdout[-3000:]
-    lib = _lib._proto(C.CDLL(str(ROOT / "build" / "libb200knn_simt.so")))
+    import os
+    lib = _lib._proto(C.CDLL(os.environ.get("B200KNN_SIMT_LIB", str(ROOT / "build" / "libb200knn_simt.so"))))
     lib.b200knn_knn_self_noalloc.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
     lib.b200knn_knn_self_noalloc.restype = C.c_int
     return lib
