@@ -128,6 +128,7 @@ struct PvMainParams {
   int phase;                   // 0 = LOCAL (home groups, fresh heaps), 1 = SERVE (visiting groups from the inbox)
   int fill;                    // as RingParams::fill, LOCAL phase only
   int pairs;                   // as RingParams::pairs (both phases)
+  float* global_heaps;         // set by pv_main_launch when k exceeds the shared-memory heap
   int R, rank;
   const Box* region_boxes;     // [R][kRegionBoxes]: every rank's region = the boxes of the deepest tree
                                // level that has at most kRegionBoxes nodes

@@ -40,14 +40,21 @@ __device__ __forceinline__ const int* slot_meta(const char* slot, int k) {
   return reinterpret_cast<const int*>(slot + (size_t)k * 128 + 512);
 }
 
-template <bool PAIRS>
+// GLOBAL_HEAP: as in query.cu — k beyond the shared-memory limit keeps the lanes' heaps in a global scratch
+// block per resident warp.
+template <bool PAIRS, bool GLOBAL_HEAP = false>
 __global__ void __launch_bounds__(Q_MAX_WARPS * 32, 1)
 pv_main_kernel_t(const PvMainParams p) {
   extern __shared__ __align__(16) float q_smem[];
   const int lane = lane_id();
   const int k = p.k;
   GroupCtx g;
-  group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k);
+  if constexpr (GLOBAL_HEAP) {
+    const size_t warp_global = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k, p.global_heaps + warp_global * (size_t)heap_padded(k) * 32);
+  } else {
+    group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k);
+  }
   const int kp = g.kp;
   const size_t slot_bytes = pv_slot_bytes(k);
   const int total = p.phase == 0 ? p.group_count : ldcg_i(p.inbox_count);
@@ -386,12 +393,33 @@ inline int blocks_for(int64_t n, int block) { return (int)div_up(n, block); }
 
 }  // namespace
 
-int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream) {
+int pv_main_launch(const PvMainParams& p_in, int max_tasks, int num_sms, cudaStream_t stream) {
+  PvMainParams p = p_in;
   KNN_REQUIRE(p.k >= 1, "k must be >= 1");
   const bool pairs = p.pairs && p.k >= kGroup;
   auto kernel = pairs ? pv_main_kernel_t<true> : pv_main_kernel_t<false>;
   const int warps = group_pick_warps(p.k, (const void*)kernel);
-  KNN_REQUIRE(warps >= 1, "k too large for the shared-memory heap (k <= 1790)");
+  if (warps < 1) {
+    // k does not fit the shared-memory heap: heaps go to a stream-ordered global scratch buffer (slower)
+    if (max_tasks <= 0) return 0;
+    const int gw = 8;
+    const size_t gsmem = (size_t)gw * warp_smem_floats_noheap() * sizeof(float);
+    int gocc = 0;
+    KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&gocc, pv_main_kernel_t<false, true>, gw * 32, gsmem));
+    KNN_REQUIRE(gocc >= 1, "pv kernel does not fit on an SM");
+    if (gocc > 2) gocc = 2;
+    const long long gwant = ((long long)max_tasks + gw - 1) / gw, gcap = (long long)num_sms * gocc;
+    const int ggrid = (int)(gwant < gcap ? gwant : gcap);
+    float* heaps = nullptr;
+    KNN_CUDA_TRY(cudaMallocAsync(&heaps, (size_t)ggrid * gw * heap_padded(p.k) * 32 * sizeof(float), stream));
+    p.global_heaps = heaps;
+    KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
+    pv_main_kernel_t<false, true><<<ggrid, gw * 32, gsmem, stream>>>(p);
+    note_launch();
+    KNN_CUDA_TRY(cudaGetLastError());
+    KNN_CUDA_TRY(cudaFreeAsync(heaps, stream));
+    return 0;
+  }
   const size_t smem = group_smem_bytes(p.k, warps);
   KNN_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;

@@ -87,9 +87,9 @@ def main() -> int:
              ("chunks", 1500 * world + 7, 40, math.inf, 13, "uniform"),       # several chunks, fill path, ragged split
              ("radius", 1800 * world, 32, 0.08, 0, "uniform"),
              ("clustered", 2000 * world, 10, math.inf, 0, "clustered"),
-             ("tiny", world * 3 + 1, 5, math.inf, 0, "uniform")]
-    if wanted:
-        cases = [c for c in cases if c[0] in wanted]
+             ("tiny", world * 3 + 1, 5, math.inf, 0, "uniform"),
+             ("hugek", 1300 * world, 1900, math.inf, 0, "uniform")]     # heaps in global memory, every group travels
+    cases = [c for c in cases if (c[0] in wanted if wanted else c[0] != "hugek")]
 
     def rank_main(rank):
         bs, keep = w.bootstrap(rank)
