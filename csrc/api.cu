@@ -162,27 +162,27 @@ static int index_create_impl(const float* d_xyz, int stride, int64_t n, const ui
   idx->levels = levels;
 
   // temporaries (stream-ordered)
-  uint64_t *keys = nullptr, *keys_tmp = nullptr;
-  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr;
-  KNN_CUDA_TRY(cudaMallocAsync(&keys, n * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, n * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&vals, n * sizeof(uint32_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, n * sizeof(uint32_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(n), stream));
+  StreamBuf<uint64_t> keys(stream), keys_tmp(stream);
+  StreamBuf<uint32_t> vals(stream), vals_tmp(stream), scratch(stream);
+  KNN_CUDA_TRY(keys.alloc_bytes(n * sizeof(uint64_t)));
+  KNN_CUDA_TRY(keys_tmp.alloc_bytes(n * sizeof(uint64_t)));
+  KNN_CUDA_TRY(vals.alloc_bytes(n * sizeof(uint32_t)));
+  KNN_CUDA_TRY(vals_tmp.alloc_bytes(n * sizeof(uint32_t)));
+  KNN_CUDA_TRY(scratch.alloc_bytes(radix_sort_scratch_bytes(n)));
   if ((rc = morton_keys(d_xyz, stride, n, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n, 0, 64, stream, &in_tmp))) return rc;
-  const uint32_t* order = in_tmp ? vals_tmp : vals;
+  const uint32_t* order = in_tmp ? vals_tmp.get() : vals.get();
   if ((rc = gather_points(d_xyz, stride, order, d_ids, id_offset, n, idx->pts, stream))) return rc;
   if ((rc = refine_runs(idx->pts, n, stream))) return rc;
   if ((rc = build_leaf_boxes(idx->pts, n, idx->boxes[0], stream))) return rc;
   for (int l = 1; l < levels; ++l)
     if ((rc = build_upper_boxes(idx->boxes[l - 1], idx->count[l - 1], idx->boxes[l], stream))) return rc;
-  KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
+  keys.release();
+  keys_tmp.release();
+  vals.release();
+  vals_tmp.release();
+  scratch.release();
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
   return 0;
 }
@@ -272,23 +272,23 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   KNN_REQUIRE(nq >= 0 && nq < (int64_t)0x7fffffff - 64, "knn_query: nq out of range");
   if (nq == 0) return 0;
   const int64_t groups = div_up(nq, kGroup);
-  uint64_t *keys = nullptr, *keys_tmp = nullptr;
-  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr;
-  Float4* qsorted = nullptr;
-  float* rsorted = nullptr;
-  KNN_CUDA_TRY(cudaMallocAsync(&keys, nq * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, nq * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&vals, nq * sizeof(uint32_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, nq * sizeof(uint32_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(nq), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&qsorted, groups * kGroup * sizeof(Float4), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&rsorted, groups * kGroup * sizeof(float), stream));
+  StreamBuf<uint64_t> keys(stream), keys_tmp(stream);
+  StreamBuf<uint32_t> vals(stream), vals_tmp(stream), scratch(stream);
+  StreamBuf<Float4> qsorted(stream);
+  StreamBuf<float> rsorted(stream);
+  KNN_CUDA_TRY(keys.alloc_bytes(nq * sizeof(uint64_t)));
+  KNN_CUDA_TRY(keys_tmp.alloc_bytes(nq * sizeof(uint64_t)));
+  KNN_CUDA_TRY(vals.alloc_bytes(nq * sizeof(uint32_t)));
+  KNN_CUDA_TRY(vals_tmp.alloc_bytes(nq * sizeof(uint32_t)));
+  KNN_CUDA_TRY(scratch.alloc_bytes(radix_sort_scratch_bytes(nq)));
+  KNN_CUDA_TRY(qsorted.alloc_bytes(groups * kGroup * sizeof(Float4)));
+  KNN_CUDA_TRY(rsorted.alloc_bytes(groups * kGroup * sizeof(float)));
   int rc;
   // Order queries along the index's own Morton grid (queries outside its box clamp to the faces).
   if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
-  if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
+  if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
   if ((rc = refine_runs(qsorted, nq, stream))) return rc;   // compact query groups, same as leaves
   RingParams p;
   fill_local_only(p, idx, k, max_radius);
@@ -299,13 +299,13 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
   if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
   if ((rc = scatter_results(qsorted, rsorted, nq, 0, d_out, stream))) return rc;
-  KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(qsorted, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(rsorted, stream));
+  keys.release();
+  keys_tmp.release();
+  vals.release();
+  vals_tmp.release();
+  scratch.release();
+  qsorted.release();
+  rsorted.release();
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
   return 0;
 }
@@ -324,23 +324,23 @@ int b200knn_knn_neighbors(b200knn_index* idx, const float* d_queries, int64_t nq
   KNN_REQUIRE(nq >= 0 && nq < (int64_t)0x7fffffff - 64, "knn_neighbors: nq out of range");
   if (nq == 0) return 0;
   const int64_t groups = div_up(nq, kGroup);
-  uint64_t *keys = nullptr, *keys_tmp = nullptr;
-  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr;
-  Float4* qsorted = nullptr;
-  float* limits = nullptr;
+  StreamBuf<uint64_t> keys(stream), keys_tmp(stream);
+  StreamBuf<uint32_t> vals(stream), vals_tmp(stream), scratch(stream);
+  StreamBuf<Float4> qsorted(stream);
+  StreamBuf<float> limits(stream);
   int rc;
-  KNN_CUDA_TRY(cudaMallocAsync(&limits, groups * kGroup * sizeof(float), stream));
+  KNN_CUDA_TRY(limits.alloc_bytes(groups * kGroup * sizeof(float)));
   if (!self) {
-    KNN_CUDA_TRY(cudaMallocAsync(&keys, nq * sizeof(uint64_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, nq * sizeof(uint64_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&vals, nq * sizeof(uint32_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, nq * sizeof(uint32_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(nq), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&qsorted, groups * kGroup * sizeof(Float4), stream));
+    KNN_CUDA_TRY(keys.alloc_bytes(nq * sizeof(uint64_t)));
+    KNN_CUDA_TRY(keys_tmp.alloc_bytes(nq * sizeof(uint64_t)));
+    KNN_CUDA_TRY(vals.alloc_bytes(nq * sizeof(uint32_t)));
+    KNN_CUDA_TRY(vals_tmp.alloc_bytes(nq * sizeof(uint32_t)));
+    KNN_CUDA_TRY(scratch.alloc_bytes(radix_sort_scratch_bytes(nq)));
+    KNN_CUDA_TRY(qsorted.alloc_bytes(groups * kGroup * sizeof(Float4)));
     if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
     int in_tmp = 0;
     if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
-    if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
+    if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
     if ((rc = refine_runs(qsorted, nq, stream))) return rc;
   }
   RingParams p;
@@ -366,14 +366,14 @@ int b200knn_knn_neighbors(b200knn_index* idx, const float* d_queries, int64_t nq
   c.out_dist = d_out_dist;
   c.task_counter = idx->task_counter;
   if ((rc = collect_launch(c, idx->num_sms, stream))) return rc;
-  KNN_CUDA_TRY(cudaFreeAsync(limits, stream));
+  limits.release();
   if (!self) {
-    KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(qsorted, stream));
+    keys.release();
+    keys_tmp.release();
+    vals.release();
+    vals_tmp.release();
+    scratch.release();
+    qsorted.release();
   }
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
   return 0;
@@ -388,23 +388,23 @@ int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, fl
   KNN_REQUIRE(nq >= 0 && nq < (int64_t)0x7fffffff - 64, "fcp_query: nq out of range");
   if (nq == 0) return 0;
   const int64_t groups = div_up(nq, kGroup);
-  uint64_t *keys = nullptr, *keys_tmp = nullptr;
-  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr, *ids_sorted = nullptr;
-  Float4* qsorted = nullptr;
-  float* rsorted = nullptr;
-  KNN_CUDA_TRY(cudaMallocAsync(&keys, nq * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, nq * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&vals, nq * sizeof(uint32_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, nq * sizeof(uint32_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(nq), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&qsorted, groups * kGroup * sizeof(Float4), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&rsorted, groups * kGroup * sizeof(float), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&ids_sorted, groups * kGroup * sizeof(uint32_t), stream));
+  StreamBuf<uint64_t> keys(stream), keys_tmp(stream);
+  StreamBuf<uint32_t> vals(stream), vals_tmp(stream), scratch(stream), ids_sorted(stream);
+  StreamBuf<Float4> qsorted(stream);
+  StreamBuf<float> rsorted(stream);
+  KNN_CUDA_TRY(keys.alloc_bytes(nq * sizeof(uint64_t)));
+  KNN_CUDA_TRY(keys_tmp.alloc_bytes(nq * sizeof(uint64_t)));
+  KNN_CUDA_TRY(vals.alloc_bytes(nq * sizeof(uint32_t)));
+  KNN_CUDA_TRY(vals_tmp.alloc_bytes(nq * sizeof(uint32_t)));
+  KNN_CUDA_TRY(scratch.alloc_bytes(radix_sort_scratch_bytes(nq)));
+  KNN_CUDA_TRY(qsorted.alloc_bytes(groups * kGroup * sizeof(Float4)));
+  KNN_CUDA_TRY(rsorted.alloc_bytes(groups * kGroup * sizeof(float)));
+  KNN_CUDA_TRY(ids_sorted.alloc_bytes(groups * kGroup * sizeof(uint32_t)));
   int rc;
   if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
-  if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp : vals, nullptr, 0, nq, qsorted, stream))) return rc;
+  if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
   if ((rc = refine_runs(qsorted, nq, stream))) return rc;
   RingParams p;
   fill_local_only(p, idx, 1, max_radius);
@@ -415,17 +415,17 @@ int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, fl
   p.result_ids = ids_sorted;
   if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
   // ids are 32-bit payloads: the float scatter moves them unchanged
-  if ((rc = scatter_results(qsorted, reinterpret_cast<const float*>(ids_sorted), nq, 0,
+  if ((rc = scatter_results(qsorted, reinterpret_cast<const float*>(ids_sorted.get()), nq, 0,
                             reinterpret_cast<float*>(d_out_ids), stream))) return rc;
   if (d_out_dist && (rc = scatter_results(qsorted, rsorted, nq, 0, d_out_dist, stream))) return rc;
-  KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(qsorted, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(rsorted, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(ids_sorted, stream));
+  keys.release();
+  keys_tmp.release();
+  vals.release();
+  vals_tmp.release();
+  scratch.release();
+  qsorted.release();
+  rsorted.release();
+  ids_sorted.release();
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
   return 0;
 }

@@ -35,6 +35,29 @@ void note_launch();                             // api.cu: counts kernel launche
     }                                                                                    \
   } while (0)
 
+// Stream-ordered device allocation that goes back to the pool on EVERY path out of a function (library code
+// returns error codes from the middle of long pipelines; without this each early return leaked its temporaries).
+// release() frees early, at the point where the pipeline is done with the buffer.
+template <class T>
+struct StreamBuf {
+  T* p = nullptr;
+  cudaStream_t stream;
+  explicit StreamBuf(cudaStream_t s) : stream(s) {}
+  StreamBuf(const StreamBuf&) = delete;
+  StreamBuf& operator=(const StreamBuf&) = delete;
+  ~StreamBuf() { release(); }
+  cudaError_t alloc_bytes(size_t bytes) {
+    release();
+    return cudaMallocAsync(&p, bytes, stream);
+  }
+  void release() {
+    if (p) cudaFreeAsync(p, stream);
+    p = nullptr;
+  }
+  T* get() const { return p; }
+  operator T*() const { return p; }
+};
+
 }  // namespace b200knn
 #include <nvtx3/nvToolsExt.h>
 namespace b200knn {

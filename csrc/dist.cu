@@ -184,6 +184,12 @@ int device_collective(b200knn_dist* d, const void* d_send, int words, int op, vo
 
 struct PvPlan { int Gc; int C; int64_t max_groups; };
 
+// Destroys a local index on every path out of a function.
+struct IndexGuard {
+  b200knn_index* p = nullptr;
+  ~IndexGuard() { b200knn_index_destroy(p); }
+};
+
 PvPlan pv_plan(int64_t max_n, int k, int groups_per_chunk) {
   PvPlan pl;
   pl.max_groups = div_up(max_n > 0 ? max_n : 1, kGroup);
@@ -312,8 +318,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     if (d->allgather(my_region.data(), all_regions.data(), (int64_t)region_bytes)) { set_last_error("bootstrap allgather failed"); return -3; }
     trace.mark("exchange: allgather regions");
   }
-  Box* d_regions = nullptr;
-  KNN_CUDA_TRY(cudaMallocAsync(&d_regions, (size_t)R * kRegionBoxes * sizeof(Box), stream));
+  StreamBuf<Box> d_regions(stream);
+  KNN_CUDA_TRY(d_regions.alloc_bytes((size_t)R * kRegionBoxes * sizeof(Box)));
   std::vector<RegionHead> heads(R);
   for (int r = 0; r < R; ++r) {
     memcpy(&heads[r], all_regions.data() + (size_t)r * region_bytes, sizeof(RegionHead));
@@ -369,8 +375,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   // the per-chunk vote "does anybody have groups that must travel?" is a device-side all-gather of
   // the pending counters (B200KNN_HOST_VOTE=1: through the bootstrap, as a cross-check)
   const bool host_vote = getenv("B200KNN_HOST_VOTE") != nullptr;
-  int* d_votes = nullptr;
-  if (R > 1 && !host_vote) KNN_CUDA_TRY(cudaMallocAsync(&d_votes, (size_t)R * sizeof(int), stream));
+  StreamBuf<int> d_votes(stream);
+  if (R > 1 && !host_vote) KNN_CUDA_TRY(d_votes.alloc_bytes((size_t)R * sizeof(int)));
 
   int rc;
   for (int c = 0; c < pl.C; ++c) {
@@ -426,8 +432,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     if (rep) { KNN_CUDA_TRY(cudaStreamSynchronize(stream)); rep->ms_rounds += now_ms() - tr0; }
     trace.mark("exchange: rounds + final");
   }
-  KNN_CUDA_TRY(cudaFreeAsync(d_regions, stream));
-  if (d_votes) KNN_CUDA_TRY(cudaFreeAsync(d_votes, stream));
+  d_regions.release();
+  if (d_votes) d_votes.release();
   return 0;
 }
 
@@ -468,10 +474,10 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   Info mine{};
   mine.n = n_local;
   mine.begin = global_begin;
-  unsigned* d_bord = nullptr;
-  float* d_box6 = nullptr;
-  KNN_CUDA_TRY(cudaMallocAsync(&d_bord, 6 * sizeof(unsigned), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&d_box6, 6 * sizeof(float), stream));
+  StreamBuf<unsigned> d_bord(stream);
+  StreamBuf<float> d_box6(stream);
+  KNN_CUDA_TRY(d_bord.alloc_bytes(6 * sizeof(unsigned)));
+  KNN_CUDA_TRY(d_box6.alloc_bytes(6 * sizeof(float)));
   if ((rc = bounds_init(d_bord, stream))) return rc;
   if ((rc = bounds_accumulate(d_xyz, 3, n_local, d_bord, stream))) return rc;
   if ((rc = bounds_decode(d_bord, d_box6, stream))) return rc;
@@ -494,24 +500,24 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   KNN_CUDA_TRY(cudaMemcpyAsync(d_box6, gbox, sizeof(gbox), cudaMemcpyHostToDevice, stream));
 
   // ---- local sort by GLOBAL Morton key
-  uint64_t *keys = nullptr, *keys_tmp = nullptr, *d_samples = nullptr, *d_split = nullptr;
-  uint32_t *vals = nullptr, *vals_tmp = nullptr, *scratch = nullptr;
-  int64_t* d_cut = nullptr;
+  StreamBuf<uint64_t> keys(stream), keys_tmp(stream), d_samples(stream), d_split(stream);
+  StreamBuf<uint32_t> vals(stream), vals_tmp(stream), scratch(stream);
+  StreamBuf<int64_t> d_cut(stream);
   const int S = 2048;
   const int64_t na = n_local > 0 ? n_local : 1;
-  KNN_CUDA_TRY(cudaMallocAsync(&keys, na * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&keys_tmp, na * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&vals, na * sizeof(uint32_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&vals_tmp, na * sizeof(uint32_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&scratch, radix_sort_scratch_bytes(na), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&d_samples, S * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&d_split, B200KNN_MAX_RANKS * sizeof(uint64_t), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&d_cut, B200KNN_MAX_RANKS * sizeof(int64_t), stream));
+  KNN_CUDA_TRY(keys.alloc_bytes(na * sizeof(uint64_t)));
+  KNN_CUDA_TRY(keys_tmp.alloc_bytes(na * sizeof(uint64_t)));
+  KNN_CUDA_TRY(vals.alloc_bytes(na * sizeof(uint32_t)));
+  KNN_CUDA_TRY(vals_tmp.alloc_bytes(na * sizeof(uint32_t)));
+  KNN_CUDA_TRY(scratch.alloc_bytes(radix_sort_scratch_bytes(na)));
+  KNN_CUDA_TRY(d_samples.alloc_bytes(S * sizeof(uint64_t)));
+  KNN_CUDA_TRY(d_split.alloc_bytes(B200KNN_MAX_RANKS * sizeof(uint64_t)));
+  KNN_CUDA_TRY(d_cut.alloc_bytes(B200KNN_MAX_RANKS * sizeof(int64_t)));
   if ((rc = morton_keys(d_xyz, 3, n_local, d_box6, keys, vals, stream))) return rc;
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n_local, 0, 64, stream, &in_tmp))) return rc;
-  const uint64_t* skeys = in_tmp ? keys_tmp : keys;
-  const uint32_t* order = in_tmp ? vals_tmp : vals;
+  const uint64_t* skeys = in_tmp ? keys_tmp.get() : keys.get();
+  const uint32_t* order = in_tmp ? vals_tmp.get() : vals.get();
   trace.mark("alloc + keys + 64-bit sort");
 
   // ---- splitters from evenly spaced local order statistics
@@ -592,16 +598,16 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     rp.recv_offset[dst] = off;
   }
   if ((rc = redistribute_launch(rp, stream))) return rc;
-  KNN_CUDA_TRY(cudaFreeAsync(keys, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(keys_tmp, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(vals, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(vals_tmp, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(scratch, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(d_samples, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(d_split, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(d_cut, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(d_bord, stream));
-  KNN_CUDA_TRY(cudaFreeAsync(d_box6, stream));
+  keys.release();
+  keys_tmp.release();
+  vals.release();
+  vals_tmp.release();
+  scratch.release();
+  d_samples.release();
+  d_split.release();
+  d_cut.release();
+  d_bord.release();
+  d_box6.release();
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
   trace.mark("scatter kernel + frees");
   if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
@@ -609,7 +615,8 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   const double t1 = now_ms();
 
   // ---- local index over the received (spatially compact) points, then the culled exchange
-  b200knn_index* idx = nullptr;
+  IndexGuard index_guard;
+  b200knn_index*& idx = index_guard.p;
   rc = b200knn_index_create_xyzw(reinterpret_cast<const float*>(d->base + off_recv), my_recv, 0, stream, &idx);
   trace.mark("index build");
   const double t2 = now_ms();
@@ -620,20 +627,20 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   // run as contiguous pairs into its staging area, owner scatters locally into d_out
   if (!rc) {
     const int64_t m = idx->n, ma = m > 0 ? m : 1;
-    uint32_t *ids = nullptr, *ids_tmp = nullptr, *vals2 = nullptr, *vals2_tmp = nullptr, *scratch2 = nullptr;
-    int64_t *d_begins = nullptr, *d_cut2 = nullptr;
-    KNN_CUDA_TRY(cudaMallocAsync(&ids, ma * sizeof(uint32_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&ids_tmp, ma * sizeof(uint32_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&vals2, ma * sizeof(uint32_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&vals2_tmp, ma * sizeof(uint32_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&scratch2, radix_sort_scratch_bytes(ma), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&d_begins, (B200KNN_MAX_RANKS + 1) * sizeof(int64_t), stream));
-    KNN_CUDA_TRY(cudaMallocAsync(&d_cut2, (B200KNN_MAX_RANKS + 1) * sizeof(int64_t), stream));
+    StreamBuf<uint32_t> ids(stream), ids_tmp(stream), vals2(stream), vals2_tmp(stream), scratch2(stream);
+    StreamBuf<int64_t> d_begins(stream), d_cut2(stream);
+    KNN_CUDA_TRY(ids.alloc_bytes(ma * sizeof(uint32_t)));
+    KNN_CUDA_TRY(ids_tmp.alloc_bytes(ma * sizeof(uint32_t)));
+    KNN_CUDA_TRY(vals2.alloc_bytes(ma * sizeof(uint32_t)));
+    KNN_CUDA_TRY(vals2_tmp.alloc_bytes(ma * sizeof(uint32_t)));
+    KNN_CUDA_TRY(scratch2.alloc_bytes(radix_sort_scratch_bytes(ma)));
+    KNN_CUDA_TRY(d_begins.alloc_bytes((B200KNN_MAX_RANKS + 1) * sizeof(int64_t)));
+    KNN_CUDA_TRY(d_cut2.alloc_bytes((B200KNN_MAX_RANKS + 1) * sizeof(int64_t)));
     if ((rc = extract_pairs_launch(idx->pts, idx->result_sorted, m, ids, vals2, stream))) return rc;
     int in_tmp2 = 0;
     if ((rc = radix_sort_u32(ids, vals2, ids_tmp, vals2_tmp, scratch2, m, 0, 32, stream, &in_tmp2))) return rc;
-    const uint32_t* sids = in_tmp2 ? ids_tmp : ids;
-    const uint32_t* svals = in_tmp2 ? vals2_tmp : vals2;
+    const uint32_t* sids = in_tmp2 ? ids_tmp.get() : ids.get();
+    const uint32_t* svals = in_tmp2 ? vals2_tmp.get() : vals2.get();
     std::vector<int64_t> begins(R + 1), cut2(R + 1, 0);
     for (int r = 0; r < R; ++r) begins[r] = info[r].begin;
     begins[R] = info[R - 1].begin + info[R - 1].n;
@@ -660,13 +667,13 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
       pp.dst_offset[o] = off;
     }
     if ((rc = push_pairs_launch(pp, stream))) return rc;
-    KNN_CUDA_TRY(cudaFreeAsync(ids, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(ids_tmp, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(vals2, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(vals2_tmp, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(scratch2, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(d_begins, stream));
-    KNN_CUDA_TRY(cudaFreeAsync(d_cut2, stream));
+    ids.release();
+    ids_tmp.release();
+    vals2.release();
+    vals2_tmp.release();
+    scratch2.release();
+    d_begins.release();
+    d_cut2.release();
   }
   if (!rc) {
     cudaError_t e = cudaStreamSynchronize(stream);
@@ -693,7 +700,6 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     rep->ms_return += now_ms() - t3;
     rep->points_after_redistribute = my_recv;
   }
-  b200knn_index_destroy(idx);
   return rc;
 }
 
@@ -820,16 +826,16 @@ int b200knn_dist_knn(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
       struct Info { int64_t n; float box[6]; };
       Info mine{};
       mine.n = n_local;
-      unsigned* d_bord = nullptr;
-      float* d_box6 = nullptr;
-      KNN_CUDA_TRY(cudaMallocAsync(&d_bord, 6 * sizeof(unsigned), stream));
-      KNN_CUDA_TRY(cudaMallocAsync(&d_box6, 6 * sizeof(float), stream));
+      StreamBuf<unsigned> d_bord(stream);
+      StreamBuf<float> d_box6(stream);
+      KNN_CUDA_TRY(d_bord.alloc_bytes(6 * sizeof(unsigned)));
+      KNN_CUDA_TRY(d_box6.alloc_bytes(6 * sizeof(float)));
       if ((rc = bounds_init(d_bord, stream))) return rc;
       if ((rc = bounds_accumulate(d_xyz, 3, n_local, d_bord, stream))) return rc;
       if ((rc = bounds_decode(d_bord, d_box6, stream))) return rc;
       KNN_CUDA_TRY(cudaMemcpyAsync(mine.box, d_box6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
-      KNN_CUDA_TRY(cudaFreeAsync(d_bord, stream));
-      KNN_CUDA_TRY(cudaFreeAsync(d_box6, stream));
+      d_bord.release();
+      d_box6.release();
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
       std::vector<Info> info(d->world);
       if (d->allgather(&mine, info.data(), sizeof(Info))) { set_last_error("bootstrap allgather failed"); return -3; }
