@@ -36,7 +36,8 @@ def main() -> int:
     # ---- unordered input: every mode, several shapes
     cases = [(20_000, 10, math.inf, 0, "uniform"), (100_003, 100, math.inf, 64, "uniform"),
              (50_001, 32, 0.05, 100, "uniform"), (60_000, 16, math.inf, 7, "clustered"),
-             (world * 3 + 1, 5, math.inf, 0, "uniform"), (300_000, 100, math.inf, 0, "uniform")]
+             (world * 3 + 1, 5, math.inf, 0, "uniform"), (300_000, 100, math.inf, 0, "uniform"),
+             (world * 1300, 1900, math.inf, 0, "uniform")]     # k beyond the shared-memory heap: global-heap kernels
     for N, k, r, gc, kind in cases:
         x_all = gen.uniform(N, seed=N) if kind == "uniform" else gen.clustered_surface(N, seed=N)
         b, e = global_slice(N, rank, world)
