@@ -182,6 +182,8 @@ int device_collective(b200knn_dist* d, const void* d_send, int words, int op, vo
   return dev_collective_launch(cp, stream);
 }
 
+constexpr int kSplitShift = 32;   // redistribution: keys are compared by their upper 64 - kSplitShift bits only
+
 struct PvPlan { int Gc; int C; int64_t max_groups; };
 
 // Destroys a local index on every path out of a function.
@@ -515,7 +517,10 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   KNN_CUDA_TRY(d_cut.alloc_bytes(B200KNN_MAX_RANKS * sizeof(int64_t)));
   if ((rc = morton_keys(d_xyz, 3, n_local, d_box6, keys, vals, stream))) return rc;
   int in_tmp = 0;
-  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n_local, 0, 64, stream, &in_tmp))) return rc;
+  // Only the upper 32 bits of the key are sorted (4 radix passes instead of 8): the owners sort what they
+  // receive by their own keys anyway, and the splitters below are multiples of 2^32, so "key < splitter" only
+  // depends on the sorted prefix. 32 bits = 10.7 bits per axis = 4.3e9 cells, far finer than any rank boundary.
+  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n_local, kSplitShift, 64, stream, &in_tmp))) return rc;
   const uint64_t* skeys = in_tmp ? keys_tmp.get() : keys.get();
   const uint32_t* order = in_tmp ? vals_tmp.get() : vals.get();
   trace.mark("alloc + keys + 64-bit sort");
@@ -531,7 +536,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   std::sort(all_samples.begin(), all_samples.end());
   uint64_t split[B200KNN_MAX_RANKS] = {};
   // Splitter j = the j/R quantile of the pooled samples, snapped to the coarsest Morton-cell
-  // boundary inside a +-0.5 % window around it. A boundary that is a whole-cell boundary keeps every
+  // boundary (of at least 2^kSplitShift keys) inside a +-0.5 % window around it. A boundary that is a whole-cell boundary keeps every
   // rank's region a union of whole cells, so a few stray points at the end of a range cannot inflate
   // a rank's bounding box across a neighbouring rank's region (which would defeat the culling).
   {
@@ -541,8 +546,8 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
       const size_t q = (size_t)j * S;
       const uint64_t lo = all_samples[q > w ? q - w : 0];
       const uint64_t hi = all_samples[std::min(total_s - 1, q + w)];
-      uint64_t best = all_samples[q];
-      for (int b = 63; b >= 0; --b) {
+      uint64_t best = (all_samples[q] >> kSplitShift) << kSplitShift;   // if the window holds no cell boundary
+      for (int b = 63; b >= kSplitShift; --b) {
         const uint64_t cand = (hi >> b) << b;
         if (cand >= lo && cand > 0) { best = cand; break; }
       }
