@@ -21,7 +21,7 @@ def built():
 
 
 @pytest.mark.parametrize("world,cases", [(2, ["chunks", "tiny", "hugek"]), (3, ["radius", "clustered"]), (8, ["uniform"]),
-                                         (16, ["tiny"])]      # 16 = B200KNN_MAX_RANKS, more than any box has GPUs)
+                                         (16, ["tiny"])])      # 16 = B200KNN_MAX_RANKS, more than any box has GPUs
 def test_emulated_ranks_every_mode_equals_oracle(built, world, cases):
     out = subprocess.run([sys.executable, str(ROOT / "tests" / "simt" / "multirank_worker.py"), str(world), *cases],
                          cwd=str(ROOT), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
