@@ -102,6 +102,8 @@ def main() -> int:
                     help="multi-GPU strategy (auto = redistribute: scatter to spatial owners + bbox-culled exchange)")
     ap.add_argument("--chunk-groups", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--verify", action="store_true",
+                    help="several GPUs: also run the (collective) counting check of sampled results; always on for 1 GPU")
     args = ap.parse_args()
 
     if args.impl == "reference":
@@ -203,6 +205,17 @@ def main() -> int:
                "h2d_bytes_per_step": int(n_local * 12), "d2h_bytes_per_step": int(n_local * 4),
                "bytes_are": "per rank"}
 
+    # Outside every timed region: check 64 sampled results of the last step against ALL points with one
+    # counting pass (independent of index, heaps and traversal). On several GPUs it is collective and only
+    # runs on request; it must never cost the bench its number.
+    verified = None
+    if world == 1 or args.verify:
+        try:
+            from mpi_cuda_largescaleknn_b200.ops.knn import verify_sample
+            verified = verify_sample(x_dev, out_dev, k, samples=64, seed=7)
+        except Exception as e:  # noqa: BLE001
+            verified = {"error": repr(e)[:200]}
+
     if rank == 0:
         line = {
             "metric": "kNN queries/sec (N=256M float3, k=100)" if (N == BASELINE_N and k == BASELINE_K)
@@ -221,6 +234,8 @@ def main() -> int:
         }
         if e2e is not None:
             line["e2e"] = e2e
+        if verified is not None:
+            line["verified"] = verified
         if engine is not None and engine.last_report:
             line["report_rank0"] = engine.last_report
         print(json.dumps(line), flush=True)

@@ -80,6 +80,14 @@ int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, fl
  * collection; no (distance, id) heap is kept. Synchronises `stream`. */
 int b200knn_knn_neighbors(b200knn_index* idx, const float* d_queries_or_null, int64_t nq, int k, float max_radius,
                           int32_t* d_out_ids, float* d_out_dist, void* stream);
+/* count_within: for up to 64 queries, how many of the n points lie strictly closer than / no farther than
+ * radius[j] (distances evaluated exactly as the query kernels do, square root included). A result r of a
+ * k-th-neighbour query is right if and only if less[j] < k <= less_equal[j], so this verifies sampled results
+ * against ALL points in one pass, at sizes where no brute-force selection is affordable; counts of several
+ * ranks add up. d_less / d_less_equal: device, nq uint64 each (zeroed by the call). Role of verifyKNN
+ * (cudaKDTree/testing/floatN-knn-and-fcp.cu:292-335). */
+int b200knn_count_within(const float* d_xyz, int64_t n, const float* d_queries, int nq, const float* d_radius,
+                         uint64_t* d_less, uint64_t* d_less_equal, void* stream);
 /* knn_self_noalloc: same result as index_create + knn_self for n <= B200KNN_NOALLOC_MAX_POINTS, but
  * the library allocates nothing: the sorted points, the box tree, the sort buffers and the counters
  * all live in one fixed device array inside the library (about 11.9 MB per GPU that loads it, held

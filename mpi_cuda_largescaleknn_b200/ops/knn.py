@@ -155,6 +155,46 @@ def neighbors(index: "KnnIndex", queries: Optional[torch.Tensor], k: int, max_ra
     return ids, dist
 
 
+def verify_sample(points: torch.Tensor, result: torch.Tensor, k: int, samples: int = 64, seed: int = 0,
+                  group=None) -> dict:
+    """Check ``samples`` (<= 64) randomly chosen entries of a self-kNN ``result`` against ALL points with one
+    counting pass on the GPU: ``result[i]`` is right iff fewer than k points are strictly closer than it and at
+    least k are no farther. With ``group`` (a torch.distributed process group whose ranks each pass their own
+    ``points`` / ``result`` slice) rank 0's sample is checked against the union of all ranks' points.
+    Returns ``{"queries": n, "violations": v}``. Independent of the index, the heaps and the traversal."""
+    import torch.distributed as dist
+    xyz = _as_xyz(points)
+    dev = xyz.device
+    multi = group is not None or (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1)
+    rank = dist.get_rank(group) if multi else 0
+    nq = max(1, min(int(samples), 64, int(xyz.shape[0]) if not multi else 64))
+    q = torch.zeros((nq, 3), dtype=torch.float32, device=dev)
+    r = torch.zeros(nq, dtype=torch.float32, device=dev)
+    if rank == 0:
+        g = torch.Generator(device="cpu").manual_seed(seed)
+        pick = torch.randint(0, int(xyz.shape[0]), (nq,), generator=g).to(dev)
+        q.copy_(xyz[pick])
+        r.copy_(result.to(torch.float32)[pick])
+    if multi:
+        dist.broadcast(q, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        dist.broadcast(r, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    less = torch.zeros(nq, dtype=torch.int64, device=dev)
+    less_equal = torch.zeros(nq, dtype=torch.int64, device=dev)
+    fn = lib().b200knn_count_within
+    fn.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    fn.restype = C.c_int
+    with torch.cuda.device(dev):
+        check(fn(xyz.data_ptr() if xyz.shape[0] else None, int(xyz.shape[0]), q.data_ptr(), nq, r.data_ptr(),
+                 less.data_ptr(), less_equal.data_ptr(), _stream_ptr()), "count_within")
+    if multi:
+        dist.all_reduce(less, group=group)
+        dist.all_reduce(less_equal, group=group)
+    bad = ((less >= k) | (less_equal < k)) & torch.isfinite(r)
+    # +inf results claim "fewer than k points exist": then every point is counted as strictly closer
+    bad |= torch.isinf(r) & (less >= k)
+    return {"queries": nq, "violations": int(bad.sum().item())}
+
+
 def fcp(index: "KnnIndex", queries: torch.Tensor, max_radius: float = math.inf):
     """Find-closest-point: (ids int32 [nq], distances float32 [nq]) of the nearest indexed point of
     every query; id -1 where nothing lies within ``max_radius``. Role of ``cukd::fcp``."""

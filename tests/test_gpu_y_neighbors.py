@@ -49,3 +49,17 @@ def test_fewer_points_than_k_and_duplicates():
     _check(gen.uniform(10, seed=1), None, 16)
     x = np.concatenate([gen.uniform(2000, seed=2), np.full((300, 3), 0.5, np.float32)])
     _check(x, None, 64)          # 300 coincident points: rows full of exact ties
+
+
+def test_counting_verifier_on_a_large_cloud():
+    """verify_sample: 64 sampled results of a 4 M-point run checked against all points by counting; a corrupted
+    result must be flagged."""
+    from mpi_cuda_largescaleknn_b200.ops.knn import knn, verify_sample
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.rand((4_000_000, 3), device=dev, generator=g)
+    res = knn(x, 50)
+    assert verify_sample(x, res, 50, samples=64, seed=3) == {"queries": 64, "violations": 0}
+    bad = res.clone()
+    bad *= 1.01
+    assert verify_sample(x, bad, 50, samples=64, seed=3)["violations"] == 64

@@ -265,3 +265,39 @@ def test_emulated_kernels_on_degenerate_clouds(sim):
         idx = Index(sim, x)
         assert bit_equal(idx.knn_self(k, r), bruteforce(x, k=k, max_radius=r)), (trial, kind, n, k, r)
         idx.close()
+
+
+def test_emulated_counting_verifier(sim):
+    """count_within proves a k-th distance right (less < k <= less_equal) and a wrong one wrong."""
+    x = np.ascontiguousarray(np.concatenate([gen.uniform(5000, seed=3), np.full((40, 3), 0.5, np.float32)]))
+    k = 25
+    pick = np.arange(0, len(x), 101)[:64]
+    q = np.ascontiguousarray(x[pick])
+    r = bruteforce(x, queries=q, k=k)
+    fn = sim.b200knn_count_within
+    fn.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    fn.restype = C.c_int
+
+    def counts(radius):
+        radius = np.ascontiguousarray(radius, np.float32)
+        less, le = np.full(len(q), 7, np.uint64), np.full(len(q), 7, np.uint64)
+        ok(sim, fn(x.ctypes.data, len(x), q.ctypes.data, len(q), radius.ctypes.data, less.ctypes.data, le.ctypes.data, None))
+        return less.astype(np.int64), le.astype(np.int64)
+
+    less, le = counts(r)
+    assert np.all(less < k) and np.all(le >= k)
+    # one float below the true answer: fewer than k points are within it (unless the answer is 0)
+    less2, le2 = counts(np.nextafter(r, np.float32(-1)))
+    assert np.all((le2 < k) | (r == 0))
+    # one float above: at least k points are strictly closer
+    less3, _ = counts(np.nextafter(r, np.float32(np.inf)))
+    assert np.all(less3 >= k)
+    # split across "ranks": the counts add up
+    la, ea = counts(r)
+    half = len(x) // 2
+    l1, e1 = np.zeros(len(q), np.uint64), np.zeros(len(q), np.uint64)
+    l2, e2 = np.zeros(len(q), np.uint64), np.zeros(len(q), np.uint64)
+    xa, xb = np.ascontiguousarray(x[:half]), np.ascontiguousarray(x[half:])
+    ok(sim, fn(xa.ctypes.data, len(xa), q.ctypes.data, len(q), r.ctypes.data, l1.ctypes.data, e1.ctypes.data, None))
+    ok(sim, fn(xb.ctypes.data, len(xb), q.ctypes.data, len(q), r.ctypes.data, l2.ctypes.data, e2.ctypes.data, None))
+    assert np.array_equal((l1 + l2).astype(np.int64), la) and np.array_equal((e1 + e2).astype(np.int64), ea)
