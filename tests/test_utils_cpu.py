@@ -51,3 +51,58 @@ def test_pretty_printers():
     assert pretty_number(999) == "999"
     assert pretty_bytes(1536) == "1.50KiB"
     assert pretty_seconds(0.0123) == "12.30ms"
+
+
+def test_host_prefetcher_schedule_with_fake_streams(monkeypatch):
+    """Control flow of ops.pipeline.HostPrefetcher without a GPU: streams and events are recorded as a trace.
+    Cloud i must be yielded from slot i % 2, its upload must wait for the computation that last used the slot,
+    and the upload of cloud i+1 must be issued before cloud i is handed to the consumer."""
+    import types
+
+    import torch
+
+    import mpi_cuda_largescaleknn_b200.ops.pipeline as pl
+    trace = []
+
+    class Event:
+        def __init__(self):
+            self.name = None
+
+        def record(self, stream=None):
+            trace.append(("record", self.name))
+
+    class Stream:
+        def __init__(self, device=None, name="copy"):
+            self.name = name
+
+        def wait_event(self, e):
+            trace.append((self.name + " waits", e.name))
+
+    class Ctx:
+        def __init__(self, s):
+            pass
+
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *a):
+            return False
+
+    fake_cuda = types.SimpleNamespace(Stream=Stream, Event=Event, stream=Ctx, current_stream=lambda d=None: Stream(name="main"))
+    monkeypatch.setattr(pl, "torch", types.SimpleNamespace(cuda=fake_cuda, empty=torch.empty, float32=torch.float32,
+                                                         device=torch.device, Tensor=torch.Tensor))
+    p = pl.HostPrefetcher(4, "cpu")
+    for i in range(2):
+        p.ready[i].name, p.free[i].name = f"ready{i}", f"free{i}"
+    clouds = [torch.full((4, 3), float(i)) for i in range(4)]
+    for c in clouds:
+        c.is_pinned = lambda: True
+    seen = []
+    for i, staged in enumerate(p.feed(clouds)):
+        trace.append(("compute", i))
+        seen.append(float(staged[0, 0]))
+    assert seen == [0.0, 1.0, 2.0, 3.0]
+    # the upload of cloud 2 (slot 0 again) waits for the computation on cloud 0, and is issued before compute 1
+    assert trace.index(("copy waits", "free0")) < trace.index(("compute", 0))          # first use: nothing to wait for yet
+    second_wait = [j for j, t in enumerate(trace) if t == ("copy waits", "free0")][1]
+    assert trace.index(("record", "free0")) < second_wait < trace.index(("compute", 1))
