@@ -88,14 +88,6 @@ bool convergent_fill_enabled() {
   return on;
 }
 
-// Experimental pair sweep (traverse.cuh::process_leaf_pair): off unless B200KNN_PAIRS=1.
-bool pair_sweep_enabled() {
-  static const bool on = [] {
-    const char* e = getenv("B200KNN_PAIRS");
-    return e ? (e[0] != '0') : false;
-  }();
-  return on;
-}
 }  // namespace b200knn
 
 extern "C" {
@@ -229,7 +221,6 @@ int b200knn_index_copy_boxes(const b200knn_index* idx, int level, float* host_bo
 static void fill_local_only(RingParams& p, b200knn_index* idx, int k, float max_radius) {
   memset(&p, 0, sizeof(p));
   p.fill = convergent_fill_enabled() ? 1 : 0;
-  p.pairs = pair_sweep_enabled() ? 1 : 0;
   p.tree = idx->view();
   p.k = k;
   p.sentinel = sentinel_d2(max_radius);

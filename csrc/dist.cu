@@ -362,7 +362,6 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.home_n = idx->n;
   p.home_is_tree = 1;
   p.fill = convergent_fill_enabled() ? 1 : 0;
-  p.pairs = pair_sweep_enabled() ? 1 : 0;
   p.result_sorted = idx->result_sorted;
   p.pending = d->base + off_pending;
   p.pending_count = reinterpret_cast<int*>(d->base + off_pcount);

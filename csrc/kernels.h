@@ -84,17 +84,17 @@ struct RingParams {
   float* result_sorted;        // home rank's result array for the LAST hop (next rank's, or own if R==1)
   unsigned* result_ids;        // optional (single rank, k == 1): id of the closest point, 0xffffffff if none
   unsigned long long* task_counter;   // local, zeroed before launch
-  unsigned long long* stats;   // optional [4]: leaves visited, candidates tested, heap inserts, inner nodes
+  unsigned long long* stats;   // optional [8]: leaves visited, candidates tested, candidates accepted, inner nodes,
+                               //               DFS fallbacks, frontier purges, list flushes
   int allow_global_heap;       // 1: k beyond the shared-memory limit may use a global-memory heap (allocates)
   float* global_heaps;         // set by ring_launch on that fallback path
-  int fill;                    // 1: fresh heaps take their first floor(k/32) leaves by plain appends + heapify
+  int fill;                    // heap kernels only. 1: fresh heaps take their first floor(k/32) leaves by plain appends + heapify
   int raw_result;              // 1: result_sorted receives the heap top itself (squared distance / sentinel)
-  int pairs;                   // 1: experimental pair sweep (k >= 32)
 };
 bool convergent_fill_enabled();   // api.cu: host-side switch (B200KNN_FILL=0/1), read once
-bool pair_sweep_enabled();        // api.cu: host-side switch (B200KNN_PAIRS=1), read once
 
-size_t ring_smem_bytes(int k, int warps_per_cta);
+// Warps per CTA the query kernel would run with for this k; 0 = k does not fit in shared memory (the
+// global-memory heap fallback, which allocates, is the only way then).
 int ring_pick_warps_per_cta(int k);
 int ring_launch(const RingParams& p, int num_sms, cudaStream_t stream);
 
@@ -127,7 +127,6 @@ struct PvMainParams {
   float sentinel;
   int phase;                   // 0 = LOCAL (home groups, fresh heaps), 1 = SERVE (visiting groups from the inbox)
   int fill;                    // as RingParams::fill, LOCAL phase only
-  int pairs;                   // as RingParams::pairs (both phases)
   float* global_heaps;         // set by pv_main_launch when k exceeds the shared-memory heap
   int R, rank;
   const Box* region_boxes;     // [R][kRegionBoxes]: every rank's region = the boxes of the deepest tree

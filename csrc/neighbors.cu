@@ -22,6 +22,7 @@ namespace {
 // Per-lane output cursor: strictly closer points are appended from the front of the row, ties with the
 // k-th distance from the back; a tie gives way when a strictly closer point needs its slot.
 struct CollectLeafOp {
+  static constexpr bool kBuffered = false;
   float limit;        // this lane's k-th squared distance (or the sentinel if fewer than k points are in range)
   bool inclusive;     // ties with `limit` are neighbours (false when limit is the sentinel)
   int k, front, ties;
@@ -111,7 +112,7 @@ knn_collect_kernel(const CollectParams p) {
     g.top = op.inclusive ? __uint_as_float(__float_as_uint(op.limit) + 1u) : op.limit;
     if (p.tree.n > 0) {
       const int own_seed = p.home_is_tree ? (p.tree.levels >= 2 ? (int)(group / kFanout) : -1) : -2;
-      traverse_group<false>(p.tree, g, cnt, own_seed, 0, op);
+      traverse_group(p.tree, g, cnt, own_seed, 0, op);
     }
     if (g.valid) {
       for (int s = op.front; s < p.k - op.ties; ++s) {     // fewer than k points in range

@@ -40,9 +40,9 @@ __device__ __forceinline__ const int* slot_meta(const char* slot, int k) {
   return reinterpret_cast<const int*>(slot + (size_t)k * 128 + 512);
 }
 
-// GLOBAL_HEAP: as in query.cu — k beyond the shared-memory limit keeps the lanes' heaps in a global scratch
-// block per resident warp.
-template <bool PAIRS, bool GLOBAL_HEAP = false>
+// SORTED / GLOBAL_HEAP: as in query.cu — sorted lists + append buffers in shared memory for 2 <= k <= ~1700,
+// the heap for k == 1 and (in a global scratch block per resident warp) for k beyond the shared-memory limit.
+template <bool GLOBAL_HEAP, bool SORTED>
 __global__ void __launch_bounds__(Q_MAX_WARPS * 32, 1)
 pv_main_kernel_t(const PvMainParams p) {
   extern __shared__ __align__(16) float q_smem[];
@@ -53,7 +53,7 @@ pv_main_kernel_t(const PvMainParams p) {
     const size_t warp_global = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k, p.global_heaps + warp_global * (size_t)heap_padded(k) * 32);
   } else {
-    group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k);
+    group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k, nullptr, SORTED);
   }
   const int kp = g.kp;
   const size_t slot_bytes = pv_slot_bytes(k);
@@ -97,7 +97,7 @@ pv_main_kernel_t(const PvMainParams p) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;
       const int own_seed = (p.phase == 0 && p.home_is_tree)
                                ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1) : -2;
-      traverse_group<PAIRS>(p.tree, g, cnt, own_seed, (p.phase == 0 && p.fill) ? k / kGroup : 0);
+      traverse_group_knn<SORTED>(p.tree, g, cnt, own_seed, k, (p.phase == 0 && p.fill) ? k / kGroup : 0);
     }
 
     if (p.phase == 0) {
@@ -393,46 +393,52 @@ inline int blocks_for(int64_t n, int block) { return (int)div_up(n, block); }
 
 }  // namespace
 
-int pv_main_launch(const PvMainParams& p_in, int max_tasks, int num_sms, cudaStream_t stream) {
-  PvMainParams p = p_in;
-  KNN_REQUIRE(p.k >= 1, "k must be >= 1");
-  const bool pairs = p.pairs && p.k >= kGroup;
-  auto kernel = pairs ? pv_main_kernel_t<true> : pv_main_kernel_t<false>;
-  const int warps = group_pick_warps(p.k, (const void*)kernel);
-  if (warps < 1) {
-    // k does not fit the shared-memory heap: heaps go to a stream-ordered global scratch buffer (slower)
-    if (max_tasks <= 0) return 0;
-    const int gw = 8;
-    const size_t gsmem = (size_t)gw * warp_smem_floats_noheap() * sizeof(float);
-    int gocc = 0;
-    KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&gocc, pv_main_kernel_t<false, true>, gw * 32, gsmem));
-    KNN_REQUIRE(gocc >= 1, "pv kernel does not fit on an SM");
-    if (gocc > 2) gocc = 2;
-    const long long gwant = ((long long)max_tasks + gw - 1) / gw, gcap = (long long)num_sms * gocc;
-    const int ggrid = (int)(gwant < gcap ? gwant : gcap);
-    float* heaps = nullptr;
-    KNN_CUDA_TRY(cudaMallocAsync(&heaps, (size_t)ggrid * gw * heap_padded(p.k) * 32 * sizeof(float), stream));
-    p.global_heaps = heaps;
-    KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
-    pv_main_kernel_t<false, true><<<ggrid, gw * 32, gsmem, stream>>>(p);
-    note_launch();
-    KNN_CUDA_TRY(cudaGetLastError());
-    KNN_CUDA_TRY(cudaFreeAsync(heaps, stream));
-    return 0;
-  }
-  const size_t smem = group_smem_bytes(p.k, warps);
+namespace {
+template <bool SORTED>
+int pv_launch_shared(PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream) {
+  auto kernel = pv_main_kernel_t<false, SORTED>;
+  const int warps = group_pick_warps(p.k, (const void*)kernel, SORTED);
+  KNN_REQUIRE(warps >= 1, "pv kernel: k does not fit in shared memory");
+  const size_t smem = group_smem_bytes(p.k, warps, SORTED);
   KNN_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, warps * 32, smem));
   KNN_REQUIRE(occ >= 1, "pv kernel does not fit on an SM");
   if (max_tasks <= 0) return 0;
-  long long want = ((long long)max_tasks + warps - 1) / warps;
-  long long cap = (long long)num_sms * occ;
+  const long long want = ((long long)max_tasks + warps - 1) / warps;
+  const long long cap = (long long)num_sms * occ;
   const int grid = (int)(want < cap ? want : cap);
   KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
   kernel<<<grid, warps * 32, smem, stream>>>(p);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+}  // namespace
+
+int pv_main_launch(const PvMainParams& p_in, int max_tasks, int num_sms, cudaStream_t stream) {
+  PvMainParams p = p_in;
+  KNN_REQUIRE(p.k >= 1, "k must be >= 1");
+  if (use_sorted_list(p.k)) return pv_launch_shared<true>(p, max_tasks, num_sms, stream);
+  if (p.k == 1) return pv_launch_shared<false>(p, max_tasks, num_sms, stream);
+  // k does not fit in shared memory: heaps go to a stream-ordered global scratch buffer (slower)
+  if (max_tasks <= 0) return 0;
+  const int gw = 8;
+  const size_t gsmem = (size_t)gw * warp_smem_floats_noheap() * sizeof(float);
+  int gocc = 0;
+  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&gocc, pv_main_kernel_t<true, false>, gw * 32, gsmem));
+  KNN_REQUIRE(gocc >= 1, "pv kernel does not fit on an SM");
+  if (gocc > 2) gocc = 2;
+  const long long gwant = ((long long)max_tasks + gw - 1) / gw, gcap = (long long)num_sms * gocc;
+  const int ggrid = (int)(gwant < gcap ? gwant : gcap);
+  float* heaps = nullptr;
+  KNN_CUDA_TRY(cudaMallocAsync(&heaps, (size_t)ggrid * gw * heap_padded(p.k) * 32 * sizeof(float), stream));
+  p.global_heaps = heaps;
+  KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
+  pv_main_kernel_t<true, false><<<ggrid, gw * 32, gsmem, stream>>>(p);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  KNN_CUDA_TRY(cudaFreeAsync(heaps, stream));
   return 0;
 }
 

@@ -15,12 +15,13 @@
 //     nearest entry is no closer than the group's k-th radius. Measured (tools/cpu_stats.py, mirror
 //     engine): 2.2x fewer leaves and 2.7x fewer heap insertions than per-node nearest-first DFS.
 //     Frontier full -> purge stale entries -> if still full, open that node depth-first (always exact).
-//   * leaf points arrive by one coalesced 128-bit load per lane and are broadcast from shared memory
-//     (LDS.128). Leaf = two phases: (1) convergent: 32 distances -> bitmask of candidates under the
-//     lane's current k-th distance; (2) divergent only over set bits: re-derive d2, sift into the heap.
-//   * every query's k-heap lives in shared memory, one column per lane (bank == lane: conflict-free
-//     at any heap index), 4-ary and padded with -inf to 4m+1 entries so a sift level is 4 unguarded
-//     loads.
+//   * leaf points arrive by one coalesced 128-bit load per lane and are broadcast from shared memory.
+//     32 distances per lane on the packed fp32x2 pipe; each one that beats the lane's k-th distance is
+//     appended to the lane's buffer by a predicated store.
+//   * every query's k candidates live in shared memory, one column per lane (bank == lane:
+//     conflict-free at any index), as a DESCENDING sorted list; buffered candidates are sorted in
+//     registers and merged in by the whole warp in lock step (traverse.cuh, "sorted list + append
+//     buffer") — no per-lane sift loops. k == 1 and k beyond shared memory keep the 4-ary heap.
 //   * ring: groups travel with their heaps. A group's state is read from the local inbox (which the
 //     previous GPU filled with plain st.global over NVLink), traversed against the local tree, and
 //     written straight into the NEXT GPU's inbox, followed by fence + st.release.sys of a sequence
@@ -33,11 +34,12 @@ namespace b200knn {
 
 namespace {
 
-// GLOBAL_HEAP = false: the product path, heaps in shared memory (k <= ~1790).
-// GLOBAL_HEAP = true : fallback for larger k, one [kp][32] heap block per resident warp in global
-//                      memory (rows are coalesced 128-byte lines); everything else is unchanged.
-// PAIRS = true       : experimental pair sweep (traverse.cuh::process_leaf_pair), B200KNN_PAIRS=1, k >= 32.
-template <bool GLOBAL_HEAP, bool PAIRS = false>
+// SORTED = true      : the product path, sorted lists + append buffers in shared memory (2 <= k <= ~1700).
+// SORTED = false     : 4-ary heaps; in shared memory for k == 1 (keeps the winner's id for
+//                      find-closest-point), or with
+// GLOBAL_HEAP = true : one [kp][32] heap block per resident warp in global memory (rows are coalesced
+//                      128-byte lines) for k beyond the shared-memory limit.
+template <bool GLOBAL_HEAP, bool SORTED>
 __global__ void __launch_bounds__(Q_MAX_WARPS * 32, 1)
 knn_ring_kernel_t(const RingParams p) {
   extern __shared__ __align__(16) float q_smem[];
@@ -48,7 +50,7 @@ knn_ring_kernel_t(const RingParams p) {
     const size_t warp_global = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k, p.global_heaps + warp_global * (size_t)heap_padded(k) * 32);
   } else {
-    group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k);
+    group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k, nullptr, SORTED);
   }
   const int kp = g.kp;
 
@@ -109,7 +111,7 @@ knn_ring_kernel_t(const RingParams p) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;   // heap padding
       // seed = the level-1 node holding the group's own leaf (self queries at home), else the nearest (-2)
       const int own_seed = (hop == 0 && p.home_is_tree) ? (p.tree.levels >= 2 ? (int)(home_group / kFanout) : -1) : -2;
-      traverse_group<PAIRS>(p.tree, g, cnt, own_seed, (hop == 0 && p.fill) ? k / kGroup : 0);
+      traverse_group_knn<SORTED>(p.tree, g, cnt, own_seed, k, (hop == 0 && p.fill) ? k / kGroup : 0);
     }
 
     // ------------------------------------------------------------------ output
@@ -152,14 +154,14 @@ knn_ring_kernel_t(const RingParams p) {
 
 }  // namespace
 
-size_t group_smem_bytes(int k, int warps_per_cta) {
-  return (size_t)warps_per_cta * warp_smem_floats(k) * sizeof(float);
+size_t group_smem_bytes(int k, int warps_per_cta, bool sorted) {
+  return (size_t)warps_per_cta * warp_smem_floats(k, sorted) * sizeof(float);
 }
 
 // Shared memory decides the shape: maximise resident warps per SM over (CTAs per SM, warps per
-// CTA); prefer more, smaller CTAs on ties. k = 100 -> three 5-warp CTAs per SM. Returns 0 if not even
-// one warp fits (k > ~1790).
-int group_pick_warps(int k, const void* kernel) {
+// CTA); prefer more, smaller CTAs on ties. k = 100 -> two 5-warp CTAs per SM. Returns 0 if not even
+// one warp fits.
+int group_pick_warps(int k, const void* kernel, bool sorted) {
   int reg_warps = 32;     // resident warps the register file allows for this kernel
   cudaFuncAttributes fa;
   if (cudaFuncGetAttributes(&fa, kernel) == cudaSuccess && fa.numRegs > 0) {
@@ -168,7 +170,7 @@ int group_pick_warps(int k, const void* kernel) {
     if (reg_warps > 32) reg_warps = 32;
     if (reg_warps < 1) reg_warps = 1;
   }
-  const size_t per_warp = group_smem_bytes(k, 1);
+  const size_t per_warp = group_smem_bytes(k, 1, sorted);
   int best_w = 0, best_total = 0;
   for (int ctas = 4; ctas >= 1; --ctas) {
     for (int w = Q_MAX_WARPS; w >= 1; --w) {
@@ -183,41 +185,47 @@ int group_pick_warps(int k, const void* kernel) {
   return best_w;
 }
 
-size_t ring_smem_bytes(int k, int warps_per_cta) { return group_smem_bytes(k, warps_per_cta); }
-int ring_pick_warps_per_cta(int k) { return group_pick_warps(k, (const void*)knn_ring_kernel_t<false>); }
+namespace {
+template <bool SORTED>
+int launch_shared(RingParams& p, unsigned long long total, int num_sms, cudaStream_t stream) {
+  auto kernel = knn_ring_kernel_t<false, SORTED>;
+  const int warps = group_pick_warps(p.k, (const void*)kernel, SORTED);
+  KNN_REQUIRE(warps >= 1, "query kernel: k does not fit in shared memory");
+  const size_t smem = group_smem_bytes(p.k, warps, SORTED);
+  KNN_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, warps * 32, smem));
+  KNN_REQUIRE(occ >= 1, "query kernel does not fit on an SM");
+  const unsigned long long want = (total + warps - 1) / warps;
+  const unsigned long long cap = (unsigned long long)num_sms * occ;
+  const int grid = (int)(want < cap ? want : cap);
+  KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
+  kernel<<<grid, warps * 32, smem, stream>>>(p);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+}  // namespace
+
+int ring_pick_warps_per_cta(int k) {
+  if (use_sorted_list(k)) return group_pick_warps(k, (const void*)knn_ring_kernel_t<false, true>, true);
+  if (k == 1) return group_pick_warps(k, (const void*)knn_ring_kernel_t<false, false>, false);
+  return 0;
+}
 
 int ring_launch(const RingParams& p_in, int num_sms, cudaStream_t stream) {
   RingParams p = p_in;
   KNN_REQUIRE(p.k >= 1, "k must be >= 1");
   const unsigned long long total = (unsigned long long)(p.step_end - p.step_begin) * p.groups_per_chunk;
   if (total == 0) return 0;
-  int warps = ring_pick_warps_per_cta(p.k);
-  if (warps >= 1) {
-    const size_t smem = ring_smem_bytes(p.k, warps);
-    KNN_CUDA_TRY(cudaFuncSetAttribute(knn_ring_kernel_t<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 0;
-    KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn_ring_kernel_t<false>, warps * 32, smem));
-    KNN_REQUIRE(occ >= 1, "query kernel does not fit on an SM");
-    unsigned long long want = (total + warps - 1) / warps;
-    unsigned long long cap = (unsigned long long)num_sms * occ;
-    const int grid = (int)(want < cap ? want : cap);
-    KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
-    if (p.pairs && p.k >= kGroup) {
-      KNN_CUDA_TRY(cudaFuncSetAttribute(knn_ring_kernel_t<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      knn_ring_kernel_t<false, true><<<grid, warps * 32, smem, stream>>>(p);
-    } else {
-      knn_ring_kernel_t<false><<<grid, warps * 32, smem, stream>>>(p);
-    }
-    note_launch();
-    KNN_CUDA_TRY(cudaGetLastError());
-    return 0;
-  }
-  // k does not fit the shared-memory heap: heaps go to a stream-ordered global scratch buffer
-  KNN_REQUIRE(p.allow_global_heap, "k too large for the shared-memory heap (k <= 1790) on this path");
-  warps = 8;
+  if (use_sorted_list(p.k)) return launch_shared<true>(p, total, num_sms, stream);
+  if (p.k == 1) return launch_shared<false>(p, total, num_sms, stream);
+  // k does not fit in shared memory: heaps go to a stream-ordered global scratch buffer
+  KNN_REQUIRE(p.allow_global_heap, "k too large for shared memory on this path");
+  const int warps = 8;
   const size_t smem = (size_t)warps * warp_smem_floats_noheap() * sizeof(float);
   int occ = 0;
-  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn_ring_kernel_t<true>, warps * 32, smem));
+  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn_ring_kernel_t<true, false>, warps * 32, smem));
   KNN_REQUIRE(occ >= 1, "query kernel does not fit on an SM");
   if (occ > 2) occ = 2;
   unsigned long long want = (total + warps - 1) / warps;
@@ -228,7 +236,7 @@ int ring_launch(const RingParams& p_in, int num_sms, cudaStream_t stream) {
   KNN_CUDA_TRY(cudaMallocAsync(&heaps, heap_bytes, stream));
   p.global_heaps = heaps;
   KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
-  knn_ring_kernel_t<true><<<grid, warps * 32, smem, stream>>>(p);
+  knn_ring_kernel_t<true, false><<<grid, warps * 32, smem, stream>>>(p);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   KNN_CUDA_TRY(cudaFreeAsync(heaps, stream));

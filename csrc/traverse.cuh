@@ -13,8 +13,14 @@ constexpr int kQueueCap = 128;         // frontier entries per warp (1 KB)
 constexpr unsigned kNodeIdxBits = 28;  // node = level << 28 | index
 
 __host__ __device__ constexpr int heap_padded(int k) { return 4 * ((k - 1 + 3) / 4) + 1; }
-__host__ __device__ constexpr size_t warp_smem_floats(int k) {
-  return (size_t)heap_padded(k) * 32 + 128 + 2 * kQueueCap + 32 + 96 + 8;   // heap | stage | frontier | frames | soa | worklist
+// Sorted candidate list (the product path, see "sorted list + append buffer" below): k rows, one -inf
+// terminator row, then the append buffer.
+constexpr int kFlushRows = 32;         // buffered candidates merged per flush (one register sort)
+constexpr int kBufRows = 2 * kFlushRows;   // a leaf (32 candidates) always fits behind a not-yet-flushed batch
+__host__ __device__ constexpr int list_rows(int k) { return k + 1; }
+__host__ __device__ constexpr size_t warp_aux_floats() { return 128 + 2 * kQueueCap + 32 + 96 + 8; }   // stage | frontier | frames | soa | worklist
+__host__ __device__ constexpr size_t warp_smem_floats(int k, bool sorted) {
+  return (size_t)(sorted ? list_rows(k) + kBufRows : heap_padded(k)) * 32 + warp_aux_floats();
 }
 
 struct GroupCtx {
@@ -29,10 +35,13 @@ struct GroupCtx {
   unsigned* qnode;      // shared: frontier nodes
   unsigned* frames;     // shared: frame stack of the depth-first fallback
   unsigned* work;       // shared: lane-mask worklist of traverse_group (8 entries)
-  int kp;               // padded heap size
+  float* buf;           // shared (sorted mode): buf[i*32] is buffered candidate i of this lane
+  int cnt;              // sorted mode: candidates in this lane's buffer
+  bool flush_pending;   // sorted mode, warp-uniform: some lane's buffer cannot take another leaf
+  int kp;               // rows of the candidate structure: padded heap size, or k + 1 in sorted mode
   bool valid;
   unsigned last_id;     // id of the most recently accepted candidate (find-closest-point uses it, k == 1)
-  unsigned n_leaves, n_inner, n_inserts, n_fallback, n_purge;
+  unsigned n_leaves, n_inner, n_inserts, n_fallback, n_purge, n_flush;
 };
 
 // Sift e down from position i. Children of i: 4i+1..4i+4, all present (padding is -inf).
@@ -150,63 +159,6 @@ __device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cn
   ++g.n_leaves;
 }
 
-// ---- pair sweep (experimental, k >= 32 only) -------------------------------------------------------
-// Two leaves per insertion phase: lanes whose survivors sit in different leaves sift at the same time,
-// which raises the number of active lanes per sift round (tools/sift_model.py: insertion cost 0.88 ->
-// 0.78 of the per-leaf schedule). Candidates live as x[64] | y[64] in the stage area and z[64] in the
-// soa area; ids are not kept (find-closest-point needs k == 1 and never takes this path).
-__device__ __forceinline__ void process_leaf_pair(const TreeView& t, int leaf_a, int cnt_a, int leaf_b, int cnt_b,
-                                                  GroupCtx& g) {
-  const int lane = lane_id();
-  float4 pa = make_float4(INFINITY, INFINITY, INFINITY, 0.f), pb = pa;
-  if (lane < cnt_a) pa = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf_a * kGroup + lane);
-  if (lane < cnt_b) pb = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf_b * kGroup + lane);
-  float* px = reinterpret_cast<float*>(g.stage);
-  float* py = px + 64;
-  float* pz = g.soa;
-  __syncwarp();
-  px[lane] = pa.x; px[32 + lane] = pb.x;
-  py[lane] = pa.y; py[32 + lane] = pb.y;
-  pz[lane] = pa.z; pz[32 + lane] = pb.z;
-  __syncwarp();
-
-  unsigned mask_a = 0, mask_b = 0;
-  const float top0 = g.top;
-  const unsigned long long qx2 = pack2(g.qx, g.qx), qy2 = pack2(g.qy, g.qy), qz2 = pack2(g.qz, g.qz);
-  const unsigned long long* sx = reinterpret_cast<const unsigned long long*>(px);
-  const unsigned long long* sy = reinterpret_cast<const unsigned long long*>(py);
-  const unsigned long long* sz = reinterpret_cast<const unsigned long long*>(pz);
-#pragma unroll
-  for (int jj = 0; jj < kGroup / 2; ++jj) {
-    const unsigned long long dx = sub2(qx2, sx[jj]), dy = sub2(qy2, sy[jj]), dz = sub2(qz2, sz[jj]);
-    const unsigned long long d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
-    mask_a |= (__uint_as_float((unsigned)(d2 & 0xffffffffull)) < top0) ? (1u << (2 * jj)) : 0u;
-    mask_a |= (__uint_as_float((unsigned)(d2 >> 32)) < top0) ? (2u << (2 * jj)) : 0u;
-  }
-#pragma unroll
-  for (int jj = 0; jj < kGroup / 2; ++jj) {
-    const unsigned long long dx = sub2(qx2, sx[16 + jj]), dy = sub2(qy2, sy[16 + jj]), dz = sub2(qz2, sz[16 + jj]);
-    const unsigned long long d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
-    mask_b |= (__uint_as_float((unsigned)(d2 & 0xffffffffull)) < top0) ? (1u << (2 * jj)) : 0u;
-    mask_b |= (__uint_as_float((unsigned)(d2 >> 32)) < top0) ? (2u << (2 * jj)) : 0u;
-  }
-  if (!g.valid) mask_a = mask_b = 0;
-
-  while (mask_a | mask_b) {
-    int j;
-    if (mask_a) { j = __ffs(mask_a) - 1; mask_a &= mask_a - 1; }
-    else        { j = 32 + __ffs(mask_b) - 1; mask_b &= mask_b - 1; }
-    const float d2 = dist2(g.qx, g.qy, g.qz, px[j], py[j], pz[j]);
-    if (d2 < g.top) {
-      g.top = heap_replace_padded(g.heap, g.kp, d2);
-      ++g.n_inserts;
-    }
-  }
-  __syncwarp();
-  g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
-  g.n_leaves += 2;
-}
-
 // ---- convergent fill ------------------------------------------------------------------------------
 // A fresh heap (all entries = sentinel) accepts its first k candidates whatever they are, and every
 // one of them would pay a full-depth sift (the new value is smaller than the sentinels below it).
@@ -251,6 +203,139 @@ __device__ __forceinline__ void fill_finish(GroupCtx& g) {
   g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
 }
 
+// ---- sorted list + append buffer (the product path, k >= 2 in shared memory) ---------------------------
+// Role of the reference's candidate lists (cukd/knn.h:214-258 FixedCandidateList / HeapCandidateList,
+// :328-389 FlexHeapCandidateList::push): keep the k smallest distances seen so far and hand back the
+// current k-th as the cull radius. The reference — and round 1 of this kernel — insert one candidate at
+// a time by sifting through a heap; on a SIMT machine that loop runs at 13 of 32 lanes (lanes differ in
+// how many survivors they have and how deep each sift goes) and was 55 % of all issued instructions.
+// Here nothing is data-dependent in control flow:
+//   * a lane's candidates live as a DESCENDING sorted column list[0..k) (list[0] = current k-th distance,
+//     list[k] = -inf terminator), one column per lane, bank == lane;
+//   * a leaf is 32 distances per lane, each compared with the lane's k-th distance as of the last flush
+//     and, if smaller, appended to the lane's buffer column by a predicated store (append_leaf): no
+//     branch, no second pass over survivors. A stale (too large) threshold only lets extra candidates
+//     in; they fall out again at the merge;
+//   * when some lane holds more than 32 buffered values (a further leaf might not fit), the whole warp
+//     flushes (sorted_flush): every lane sorts its first 32 buffered values in REGISTERS with a fixed
+//     191-comparator network (missing entries are +inf), writes them back, and merges them into its
+//     list in place — drop the 32 largest of (list, batch), then k output steps of "store the larger
+//     head, advance that side". Both loops are the same instruction stream for all lanes; only
+//     addresses and predicates differ. Values left in rows 32.. move to the front.
+// The set of the k smallest distances is the same as with any other insertion order, so the k-th
+// distance is bit-identical to the heap's.
+//
+// The two inner loops are written as predicated PTX: left to the compiler, "advance whichever side held the
+// larger head" became 14 instructions per merge step (address re-derivation and register moves on both
+// arms) and the predicated append 4 per candidate; by hand they are 6 and 3.
+#if defined(B200KNN_SIMT_HOST)   // host emulation of the kernels (tests/simt): same steps in plain C++
+typedef float* smem_col_t;
+__device__ __forceinline__ smem_col_t smem_col(float* p) { return p; }
+__device__ __forceinline__ void append_if_less(smem_col_t& p, float v, float thr) {
+  if (v < thr) { *p = v; p += 32; }
+}
+__device__ __forceinline__ float merge_step(smem_col_t& pa, smem_col_t& pb, float& ca, float& cb) {
+  const float o = fmaxf(ca, cb);
+  if (ca > cb) { pa += 32; ca = *pa; } else { pb += 32; cb = *pb; }
+  return o;
+}
+__device__ __forceinline__ int rows_between(smem_col_t from, smem_col_t to) { return (int)((to - from) >> 5); }
+#else
+typedef unsigned smem_col_t;     // 32-bit shared-window address of one lane's column; rows are 128 bytes apart
+__device__ __forceinline__ smem_col_t smem_col(float* p) { return (unsigned)__cvta_generic_to_shared(p); }
+// if (v < thr) { *p = v; next row }. Readers of the buffer sit behind a __syncwarp().
+__device__ __forceinline__ void append_if_less(smem_col_t& p, float v, float thr) {
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.lt.f32 q, %1, %2;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, 128;\n\t}"
+               : "+r"(p) : "f"(v), "f"(thr));
+}
+// Returns the larger head and advances the side it came from (ties take the b side).
+__device__ __forceinline__ float merge_step(smem_col_t& pa, smem_col_t& pb, float& ca, float& cb) {
+  float o;
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.gt.f32 q, %1, %2;\n\tmax.f32 %0, %1, %2;\n\t"
+               "@q add.u32 %3, %3, 128;\n\t@!q add.u32 %4, %4, 128;\n\t"
+               "@q ld.shared.f32 %1, [%3];\n\t@!q ld.shared.f32 %2, [%4];\n\t}"
+               : "=f"(o), "+f"(ca), "+f"(cb), "+r"(pa), "+r"(pb));
+  return o;
+}
+__device__ __forceinline__ int rows_between(smem_col_t from, smem_col_t to) { return (int)((to - from) >> 7); }
+#endif
+
+__device__ __forceinline__ void sorted_flush(GroupCtx& g, int k) {
+  float r[kFlushRows];
+  const int n = g.cnt;
+#pragma unroll
+  for (int i = 0; i < kFlushRows; ++i) r[i] = i < n ? g.buf[i * 32] : INFINITY;
+#define KNN_CE(a, b) { const float hi_ = fmaxf(r[a], r[b]); r[b] = fminf(r[a], r[b]); r[a] = hi_; }
+#include "sort32_network.inc"
+#undef KNN_CE
+#pragma unroll
+  for (int i = 0; i < kFlushRows; ++i) g.buf[i * 32] = r[i];
+  // the batch needs a terminator too; row 32 may hold a live candidate, so borrow it
+  const float saved = g.buf[kFlushRows * 32];
+  g.buf[kFlushRows * 32] = -INFINITY;
+  float ca = g.heap[0], cb = r[0];
+  __syncwarp();                             // the stores above are in place before merge_step's loads
+
+  smem_col_t pa = smem_col(g.heap), pb = smem_col(g.buf);
+  // the union has k + 32 entries (+inf fillers included): the 32 largest go, fillers first
+#pragma unroll 8
+  for (int s = 0; s < kFlushRows; ++s) (void)merge_step(pa, pb, ca, cb);
+  // Output position t never passes the list head, and whenever a load and a store meet at the same
+  // row they carry the same value (the batch side is exhausted then), so the merge is in place.
+#pragma unroll 4
+  for (int t = 0; t < k; ++t) g.heap[t * 32] = merge_step(pa, pb, ca, cb);
+  __syncwarp();
+  g.buf[kFlushRows * 32] = saved;
+
+  // what did not fit into this batch moves to the front, minus what the new k-th distance rules out
+  const float top = g.heap[0];
+  const int rest = n > kFlushRows ? n - kFlushRows : 0;
+  const int most = (int)__reduce_max_sync(kFullMask, (unsigned)rest);
+  int w = 0;
+  for (int i = 0; i < most; ++i) {
+    const float v = g.buf[(kFlushRows + i) * 32];
+    if (i < rest && v < top) { g.buf[w * 32] = v; ++w; }
+  }
+  g.cnt = w;
+  g.top = top;
+  __syncwarp();
+  g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
+  g.flush_pending = false;                  // w <= 32 on every lane
+  ++g.n_flush;
+}
+
+// One leaf against the lanes' thresholds: survivors are appended to the lanes' buffers (see above).
+// Precondition: every lane has at most 32 buffered values (the traversal flushes before the next leaf).
+__device__ __forceinline__ void append_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g) {
+  const int lane = lane_id();
+  float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);   // padding never beats any threshold
+  if (lane < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane);
+  g.soa[lane] = p.x;
+  g.soa[32 + lane] = p.y;
+  g.soa[64 + lane] = p.z;
+  __syncwarp();
+  const float top0 = g.valid ? g.top : -INFINITY;
+  const unsigned long long qx2 = pack2(g.qx, g.qx), qy2 = pack2(g.qy, g.qy), qz2 = pack2(g.qz, g.qz);
+  const unsigned long long* sx = reinterpret_cast<const unsigned long long*>(g.soa);
+  const unsigned long long* sy = reinterpret_cast<const unsigned long long*>(g.soa + 32);
+  const unsigned long long* sz = reinterpret_cast<const unsigned long long*>(g.soa + 64);
+  const smem_col_t first = smem_col(g.buf + g.cnt * 32);
+  smem_col_t pos = first;
+#pragma unroll
+  for (int jj = 0; jj < kGroup / 2; ++jj) {
+    const unsigned long long dx = sub2(qx2, sx[jj]), dy = sub2(qy2, sy[jj]), dz = sub2(qz2, sz[jj]);
+    const unsigned long long d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
+    append_if_less(pos, __uint_as_float((unsigned)(d2 & 0xffffffffull)), top0);
+    append_if_less(pos, __uint_as_float((unsigned)(d2 >> 32)), top0);
+  }
+  const int added = rows_between(first, pos);
+  g.n_inserts += (unsigned)added;
+  g.cnt += added;
+  __syncwarp();
+  ++g.n_leaves;
+  g.flush_pending = __any_sync(kFullMask, g.cnt > kFlushRows);
+}
+
 // Exact per-query test against the leaf box; skip the leaf if no lane can improve.
 __device__ __forceinline__ void maybe_leaf(const TreeView& t, int leaf, float lx, float ly, float lz,
                                            float hx, float hy, float hz, int cnt, GroupCtx& g) {
@@ -261,9 +346,24 @@ __device__ __forceinline__ void maybe_leaf(const TreeView& t, int leaf, float lx
 // What traverse() does with a leaf that survives the group-level test. The default keeps the k
 // smallest distances in the lanes' heaps; other kernels (neighbors.cu) plug in their own.
 struct HeapLeafOp {
+  static constexpr bool kBuffered = false;
+  __device__ __forceinline__ void flush(GroupCtx&) const {}
   __device__ __forceinline__ void operator()(const TreeView& t, int leaf, float lx, float ly, float lz, float hx,
                                              float hy, float hz, int cnt, GroupCtx& g) const {
     maybe_leaf(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
+  }
+};
+
+// The sorted-list variant: same per-query test, survivors go to the lanes' buffers; the traversal calls
+// flush() before the next leaf whenever g.flush_pending, and before it concludes that nothing is left.
+struct SortedLeafOp {
+  static constexpr bool kBuffered = true;
+  int k;
+  __device__ __forceinline__ void flush(GroupCtx& g) const { sorted_flush(g, k); }
+  __device__ __forceinline__ void operator()(const TreeView& t, int leaf, float lx, float ly, float lz, float hx,
+                                             float hy, float hz, int cnt, GroupCtx& g) const {
+    const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
+    if (__any_sync(kFullMask, g.valid && (lb < g.top))) append_leaf(t, leaf, cnt, g);
   }
 };
 
@@ -367,15 +467,13 @@ __device__ __forceinline__ void frontier_expand(const TreeView& t, int level, in
 
 // fill_leaves > 0: the valid lanes' heaps are fresh; the first fill_leaves leaves that come up are
 // appended without a test (see fill_leaf). fill_leaves * 32 <= k.
-// PAIRS (heap kernels only): leaves that pass the per-query test are handled two at a time
-// (process_leaf_pair); the first of a pair waits in (pend_leaf, pend_cnt) while the traversal looks for
-// the second with a radius that does not yet know about the first — a stale radius is still an upper
-// bound, so the result is exact. Otherwise every leaf goes to leaf_op.
-template <bool PAIRS, class LeafOp>
+// Buffered leaf ops (LeafOp::kBuffered) are flushed at ONE place, the top of the loop: when a buffer is
+// about to overflow, and when the traversal would otherwise stop — the flush tightens the radius, after
+// which the stop test is simply evaluated again.
+template <class LeafOp>
 __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves, LeafOp& leaf_op) {
   const int lane = lane_id();
   int fill_pos = 0;
-  int pend_leaf = -1, pend_cnt = 0;
   unsigned* fr = g.frames;
   const int top_level = t.levels - 1;
   int depth = -1, qcount = 0;
@@ -387,6 +485,9 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
     __syncwarp();
   }
   for (;;) {
+    if constexpr (LeafOp::kBuffered) {
+      if (g.flush_pending) leaf_op.flush(g);
+    }
     int leaf, cnt;
     float lx, ly, lz, hx, hy, hz;
     if (depth >= 0) {
@@ -432,7 +533,12 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         frontier_expand(t, top_level, 0, t.count[top_level], seed_l1, qcount, depth, g);
         continue;
       }
-      if (qcount == 0) break;
+      if (qcount == 0) {
+        if constexpr (LeafOp::kBuffered) {
+          if (__any_sync(kFullMask, g.cnt > 0)) { g.flush_pending = true; continue; }
+        }
+        break;
+      }
       unsigned best = 0xffffffffu;
       int bslot = 0;
       for (int s = lane; s < qcount; s += 32) {
@@ -440,7 +546,12 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         if (kx < best) { best = kx; bslot = s; }
       }
       const unsigned m = __reduce_min_sync(kFullMask, best);
-      if (m >= __float_as_uint(g.maxR2)) break;          // nothing left inside the group radius
+      if (m >= __float_as_uint(g.maxR2)) {               // nothing left inside the group radius
+        if constexpr (LeafOp::kBuffered) {
+          if (__any_sync(kFullMask, g.cnt > 0)) { g.flush_pending = true; continue; }
+        }
+        break;
+      }
       const int wl = __ffs(__ballot_sync(kFullMask, best == m)) - 1;
       const int slot = __shfl_sync(kFullMask, bslot, wl);
       const unsigned node = g.qnode[slot];
@@ -471,53 +582,47 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       if (--fill_leaves == 0) fill_finish(g);
       continue;
     }
-    if constexpr (PAIRS) {
-      const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
-      if (!__any_sync(kFullMask, g.valid && (lb < g.top))) continue;
-      if (pend_leaf < 0) { pend_leaf = leaf; pend_cnt = cnt; continue; }
-      process_leaf_pair(t, pend_leaf, pend_cnt, leaf, cnt, g);
-      pend_leaf = -1;
-    } else {
-      leaf_op(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
-    }
+    leaf_op(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
   }
   if (fill_pos > 0 && fill_leaves > 0) fill_finish(g);    // the tree ran out of leaves during the fill
-  if constexpr (PAIRS) {
-    if (pend_leaf >= 0) process_leaf(t, pend_leaf, pend_cnt, g);
-  }
-}
-
-template <bool PAIRS = false>
-__device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves = 0) {
-  HeapLeafOp op;
-  traverse<PAIRS>(t, g, seed_l1, fill_leaves, op);
 }
 
 // Shared-memory floats per warp when the heap lives in GLOBAL memory (k too large for shared memory).
-__host__ __device__ constexpr size_t warp_smem_floats_noheap() { return 128 + 2 * kQueueCap + 32 + 96 + 8; }
+__host__ __device__ constexpr size_t warp_smem_floats_noheap() { return warp_aux_floats(); }
 
-// Carve one warp's slice of dynamic shared memory. global_heap == nullptr: the heap is the first part
-// of the slice (the fast path). Otherwise the heap is this warp's [kp][32] block of `global_heap` and
-// shared memory only holds the staging/frontier areas.
+// Carve one warp's slice of dynamic shared memory: candidate structure first, then the staging and
+// frontier areas.
+//   sorted               list (k + 1 rows) | append buffer (kBufRows rows) | aux
+//   heap in shared       padded heap | aux
+//   heap in global       (global_heap != nullptr) this warp's [kp][32] block of `global_heap`; shared
+//                        memory only holds the aux areas.
 __device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int warp, int lane, int k,
-                                               float* global_heap = nullptr) {
-  const int kp = heap_padded(k);
-  float* warp_base;
-  if (global_heap == nullptr) {
-    warp_base = smem + warp * warp_smem_floats(k);
-    g.heap = warp_base + lane;
-  } else {
-    warp_base = smem + warp * warp_smem_floats_noheap() - (size_t)kp * 32;   // so the offsets below still apply
+                                               float* global_heap = nullptr, bool sorted = false) {
+  const int kp = sorted ? list_rows(k) : heap_padded(k);
+  float* aux;
+  g.buf = nullptr;
+  if (global_heap != nullptr) {
+    aux = smem + warp * warp_smem_floats_noheap();
     g.heap = global_heap + lane;
+  } else {
+    float* warp_base = smem + warp * warp_smem_floats(k, sorted);
+    g.heap = warp_base + lane;
+    aux = warp_base + (size_t)kp * 32;
+    if (sorted) {
+      g.buf = aux + lane;
+      aux += (size_t)kBufRows * 32;
+    }
   }
-  g.stage = reinterpret_cast<float4*>(warp_base + (size_t)kp * 32);
-  g.qkey = reinterpret_cast<unsigned*>(warp_base + (size_t)kp * 32 + 128);
+  g.stage = reinterpret_cast<float4*>(aux);
+  g.qkey = reinterpret_cast<unsigned*>(aux + 128);
   g.qnode = g.qkey + kQueueCap;
   g.frames = g.qnode + kQueueCap;
   g.soa = reinterpret_cast<float*>(g.frames + 32);
   g.work = reinterpret_cast<unsigned*>(g.soa + 96);
   g.kp = kp;
-  g.n_leaves = g.n_inner = g.n_inserts = g.n_fallback = g.n_purge = 0;
+  g.cnt = 0;
+  g.flush_pending = false;
+  g.n_leaves = g.n_inner = g.n_inserts = g.n_fallback = g.n_purge = g.n_flush = 0;
 }
 
 // Group bounding box + group radius from the lanes' queries and heap tops.
@@ -548,7 +653,7 @@ __device__ __forceinline__ void group_bounds(GroupCtx& g) {
 // is more than two thirds of the extent, recursively, and traverse each coherent sub-group on its own
 // (the other lanes are simply not valid during that pass). Exactness is unaffected.
 // fill_leaves: see traverse(); pass k / 32 for a group whose heaps are all fresh, else 0.
-template <bool PAIRS, class LeafOp>
+template <class LeafOp>
 __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1,
                                                int fill_leaves, LeafOp& leaf_op) {
   const int lane = lane_id();
@@ -591,16 +696,23 @@ __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, i
     // coherent enough: one pass. The group's own level-1 node is the natural seed only for the
     // unsplit group; a split part looks for the node nearest to it.
     const int seed = (m == all && own_seed_l1 != -2) ? own_seed_l1 : find_seed_l1(t, g);
-    traverse<PAIRS>(t, g, seed, fill_leaves, leaf_op);
+    traverse(t, g, seed, fill_leaves, leaf_op);
   }
   g.valid = lane < cnt;
 }
 
-template <bool PAIRS = false>
-__device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1,
-                                               int fill_leaves = 0) {
-  HeapLeafOp op;
-  traverse_group<PAIRS>(t, g, cnt, own_seed_l1, fill_leaves, op);
+// SORTED = true: candidates in sorted lists behind append buffers (k >= 2, shared memory);
+// SORTED = false: the heap (k == 1 with ids, or the global-memory fallback for very large k).
+template <bool SORTED>
+__device__ __forceinline__ void traverse_group_knn(const TreeView& t, GroupCtx& g, int cnt, int own_seed_l1, int k,
+                                                   int fill_leaves) {
+  if constexpr (SORTED) {
+    SortedLeafOp op{k};
+    traverse_group(t, g, cnt, own_seed_l1, 0, op);
+  } else {
+    HeapLeafOp op;
+    traverse_group(t, g, cnt, own_seed_l1, fill_leaves, op);
+  }
 }
 
 __device__ __forceinline__ void flush_stats(const GroupCtx& g, unsigned long long* stats) {
@@ -615,6 +727,7 @@ __device__ __forceinline__ void flush_stats(const GroupCtx& g, unsigned long lon
     atomicAdd(stats + 3, (unsigned long long)g.n_inner);
     atomicAdd(stats + 4, (unsigned long long)g.n_fallback);
     atomicAdd(stats + 5, (unsigned long long)g.n_purge);
+    atomicAdd(stats + 6, (unsigned long long)g.n_flush);
   }
 }
 
@@ -625,7 +738,13 @@ constexpr size_t kSmemCtaReserve = 1024;
 }  // namespace
 
 // Launch shape of any kernel built on GroupCtx: warps per CTA and dynamic shared memory bytes.
-size_t group_smem_bytes(int k, int warps_per_cta);
-int group_pick_warps(int k, const void* kernel);
+size_t group_smem_bytes(int k, int warps_per_cta, bool sorted);
+int group_pick_warps(int k, const void* kernel, bool sorted);
+// Which candidate structure a k-th-distance kernel uses for this k: the sorted list wherever it fits in
+// shared memory (k >= 2); the heap for k == 1 (it also tracks the winner's id) and, in global memory,
+// for k beyond the shared-memory limit. Every kernel that touches a travelling group must agree on it.
+static inline bool use_sorted_list(int k) {
+  return k >= 2 && (size_t)warp_smem_floats(k, true) * sizeof(float) + 1024 <= 232448;
+}
 
 }  // namespace b200knn
