@@ -219,24 +219,35 @@ __device__ __forceinline__ void fill_finish(GroupCtx& g) {
 //   * when some lane holds more than 32 buffered values (a further leaf might not fit), the whole warp
 //     flushes (sorted_flush): every lane sorts its first 32 buffered values in REGISTERS with a fixed
 //     191-comparator network (missing entries are +inf), writes them back, and merges them into its
-//     list in place — drop the 32 largest of (list, batch), then k output steps of "store the larger
-//     head, advance that side". Both loops are the same instruction stream for all lanes; only
-//     addresses and predicates differ. Values left in rows 32.. move to the front.
+//     list in place — skip the 32 largest of (list, batch), then k output steps of "store the larger
+//     head, advance that side". It is the same instruction stream for all lanes; only addresses and
+//     predicates differ. Values left in rows 32.. move to the front.
 // The set of the k smallest distances is the same as with any other insertion order, so the k-th
 // distance is bit-identical to the heap's.
 //
-// The two inner loops are written as predicated PTX: left to the compiler, "advance whichever side held the
-// larger head" became 14 instructions per merge step (address re-derivation and register moves on both
-// arms) and the predicated append 4 per candidate; by hand they are 6 and 3.
+// With 10 resident warps per SM (the lists pin 23 KB of shared memory per warp) the kernel lives on
+// instruction-level parallelism inside each warp, so the serial parts are written for latency:
+//   * a leaf's 32 distances are all computed before the first append (a store to a computed address
+//     would otherwise fence the next pair's loads);
+//   * the 32 largest of (list, batch) are found by a 6-step merge-path bisection, not 32 merge steps;
+//   * the merge keeps the next four entries of either side in registers, so the shared-memory load
+//     issued at step s is not needed before step s + 3: the loop-carried chain is compare -> move.
+// The two inner loops are predicated PTX: left to the compiler, "advance whichever side held the larger
+// head" became 14 instructions per step with address re-derivation on both arms.
+struct MergeHeads {
+  float a0, a1, a2, a3, b0, b1, b2, b3;    // a0/b0 = current heads, the others are prefetched successors
+};
 #if defined(B200KNN_SIMT_HOST)   // host emulation of the kernels (tests/simt): same steps in plain C++
 typedef float* smem_col_t;
 __device__ __forceinline__ smem_col_t smem_col(float* p) { return p; }
 __device__ __forceinline__ void append_if_less(smem_col_t& p, float v, float thr) {
   if (v < thr) { *p = v; p += 32; }
 }
-__device__ __forceinline__ float merge_step(smem_col_t& pa, smem_col_t& pb, float& ca, float& cb) {
-  const float o = fmaxf(ca, cb);
-  if (ca > cb) { pa += 32; ca = *pa; } else { pb += 32; cb = *pb; }
+// pa / pb: rows of a3 / b3. Returns the larger head and advances the side it came from (ties: b side).
+__device__ __forceinline__ float merge_step(smem_col_t& pa, smem_col_t& pb, MergeHeads& h) {
+  const float o = fmaxf(h.a0, h.b0);
+  if (h.a0 > h.b0) { h.a0 = h.a1; h.a1 = h.a2; h.a2 = h.a3; pa += 32; h.a3 = *pa; }
+  else             { h.b0 = h.b1; h.b1 = h.b2; h.b2 = h.b3; pb += 32; h.b3 = *pb; }
   return o;
 }
 __device__ __forceinline__ int rows_between(smem_col_t from, smem_col_t to) { return (int)((to - from) >> 5); }
@@ -248,13 +259,15 @@ __device__ __forceinline__ void append_if_less(smem_col_t& p, float v, float thr
   asm volatile("{\n\t.reg .pred q;\n\tsetp.lt.f32 q, %1, %2;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, 128;\n\t}"
                : "+r"(p) : "f"(v), "f"(thr));
 }
-// Returns the larger head and advances the side it came from (ties take the b side).
-__device__ __forceinline__ float merge_step(smem_col_t& pa, smem_col_t& pb, float& ca, float& cb) {
+__device__ __forceinline__ float merge_step(smem_col_t& pa, smem_col_t& pb, MergeHeads& h) {
   float o;
-  asm volatile("{\n\t.reg .pred q;\n\tsetp.gt.f32 q, %1, %2;\n\tmax.f32 %0, %1, %2;\n\t"
-               "@q add.u32 %3, %3, 128;\n\t@!q add.u32 %4, %4, 128;\n\t"
-               "@q ld.shared.f32 %1, [%3];\n\t@!q ld.shared.f32 %2, [%4];\n\t}"
-               : "=f"(o), "+f"(ca), "+f"(cb), "+r"(pa), "+r"(pb));
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.gt.f32 q, %1, %5;\n\tmax.f32 %0, %1, %5;\n\t"
+               "@q mov.f32 %1, %2;\n\t@q mov.f32 %2, %3;\n\t@q mov.f32 %3, %4;\n\t"
+               "@q ld.shared.f32 %4, [%9+128];\n\t@q add.u32 %9, %9, 128;\n\t"
+               "@!q mov.f32 %5, %6;\n\t@!q mov.f32 %6, %7;\n\t@!q mov.f32 %7, %8;\n\t"
+               "@!q ld.shared.f32 %8, [%10+128];\n\t@!q add.u32 %10, %10, 128;\n\t}"
+               : "=f"(o), "+f"(h.a0), "+f"(h.a1), "+f"(h.a2), "+f"(h.a3), "+f"(h.b0), "+f"(h.b1), "+f"(h.b2),
+                 "+f"(h.b3), "+r"(pa), "+r"(pb));
   return o;
 }
 __device__ __forceinline__ int rows_between(smem_col_t from, smem_col_t to) { return (int)((to - from) >> 7); }
@@ -273,17 +286,36 @@ __device__ __forceinline__ void sorted_flush(GroupCtx& g, int k) {
   // the batch needs a terminator too; row 32 may hold a live candidate, so borrow it
   const float saved = g.buf[kFlushRows * 32];
   g.buf[kFlushRows * 32] = -INFINITY;
-  float ca = g.heap[0], cb = r[0];
-  __syncwarp();                             // the stores above are in place before merge_step's loads
 
-  smem_col_t pa = smem_col(g.heap), pb = smem_col(g.buf);
-  // the union has k + 32 entries (+inf fillers included): the 32 largest go, fillers first
-#pragma unroll 8
-  for (int s = 0; s < kFlushRows; ++s) (void)merge_step(pa, pb, ca, cb);
-  // Output position t never passes the list head, and whenever a load and a store meet at the same
-  // row they carry the same value (the batch side is exhausted then), so the merge is in place.
+  // The union has k + 32 entries (+inf fillers included) and the 32 largest go: jb of them from the
+  // batch, 32 - jb from the list, jb = the largest j with batch[j-1] >= list[32-j] (merge path; ties drop
+  // the batch side first, so fillers go before sentinels). Rows past the list's terminator read as -inf.
+  int jb = 0;
+  {
+    int hi = kFlushRows;
+#pragma unroll
+    for (int it = 0; it < 6; ++it) {
+      const int mid = (jb + hi + 1) >> 1;          // jb < mid <= hi whenever jb < hi
+      const int ai = kFlushRows - mid < k ? kFlushRows - mid : k;
+      const bool ok = mid > jb && g.buf[(mid - 1) * 32] >= g.heap[ai * 32];
+      if (mid > jb) { if (ok) jb = mid; else hi = mid - 1; }
+    }
+  }
+  const int ja = kFlushRows - jb;
+  MergeHeads h;
+  {
+    const float* la = g.heap + ja * 32;
+    const float* lb = g.buf + jb * 32;
+    h.a0 = la[0]; h.a1 = la[32]; h.a2 = la[64]; h.a3 = la[96];
+    h.b0 = lb[0]; h.b1 = lb[32]; h.b2 = lb[64]; h.b3 = lb[96];
+  }
+  __syncwarp();                             // the C++ stores above are in place before merge_step's loads
+  smem_col_t pa = smem_col(g.heap + (ja + 3) * 32), pb = smem_col(g.buf + (jb + 3) * 32);
+  // Output position t never passes the list head (the heads start 32 entries ahead in total and only
+  // batch entries let t catch up), reads run ahead of writes, and where they meet the value is the same:
+  // the merge is in place.
 #pragma unroll 4
-  for (int t = 0; t < k; ++t) g.heap[t * 32] = merge_step(pa, pb, ca, cb);
+  for (int t = 0; t < k; ++t) g.heap[t * 32] = merge_step(pa, pb, h);
   __syncwarp();
   g.buf[kFlushRows * 32] = saved;
 
@@ -319,14 +351,18 @@ __device__ __forceinline__ void append_leaf(const TreeView& t, int leaf, int cnt
   const unsigned long long* sx = reinterpret_cast<const unsigned long long*>(g.soa);
   const unsigned long long* sy = reinterpret_cast<const unsigned long long*>(g.soa + 32);
   const unsigned long long* sz = reinterpret_cast<const unsigned long long*>(g.soa + 64);
+  unsigned long long d2[kGroup / 2];
+#pragma unroll
+  for (int jj = 0; jj < kGroup / 2; ++jj) {
+    const unsigned long long dx = sub2(qx2, sx[jj]), dy = sub2(qy2, sy[jj]), dz = sub2(qz2, sz[jj]);
+    d2[jj] = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
+  }
   const smem_col_t first = smem_col(g.buf + g.cnt * 32);
   smem_col_t pos = first;
 #pragma unroll
   for (int jj = 0; jj < kGroup / 2; ++jj) {
-    const unsigned long long dx = sub2(qx2, sx[jj]), dy = sub2(qy2, sy[jj]), dz = sub2(qz2, sz[jj]);
-    const unsigned long long d2 = fma2(dz, dz, fma2(dx, dx, mul2(dy, dy)));
-    append_if_less(pos, __uint_as_float((unsigned)(d2 & 0xffffffffull)), top0);
-    append_if_less(pos, __uint_as_float((unsigned)(d2 >> 32)), top0);
+    append_if_less(pos, __uint_as_float((unsigned)(d2[jj] & 0xffffffffull)), top0);
+    append_if_less(pos, __uint_as_float((unsigned)(d2[jj] >> 32)), top0);
   }
   const int added = rows_between(first, pos);
   g.n_inserts += (unsigned)added;
