@@ -29,13 +29,11 @@ struct CollectLeafOp {
   int32_t* ids;       // this lane's row
   float* dist;
 
-  __device__ __forceinline__ void operator()(const TreeView& t, int leaf, float lx, float ly, float lz, float hx,
-                                             float hy, float hz, int cnt, GroupCtx& g) {
+  __device__ __forceinline__ void operator()(const float4& p, float lx, float ly, float lz, float hx,
+                                             float hy, float hz, GroupCtx& g) {
     const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
     if (!__any_sync(kFullMask, g.valid && (lb < g.top))) return;
     const int lane = lane_id();
-    float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
-    if (lane < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane);
     g.stage[lane] = p;
     g.soa[lane] = p.x;
     g.soa[32 + lane] = p.y;

@@ -79,6 +79,7 @@ pv_main_kernel_t(const PvMainParams p) {
         for (int i = 0; i < k; ++i) g.heap[i * 32] = sent;
         g.top = sent;
         g.last_id = 0xffffffffu;
+        g.live = 0;
       }
     } else {
       const char* slot = p.inbox + (size_t)t * slot_bytes;
@@ -90,6 +91,7 @@ pv_main_kernel_t(const PvMainParams p) {
       const float* src = slot_heap(slot) + lane;
       for (int i = 0; i < k; ++i) g.heap[i * 32] = ldcg_f(src + (size_t)i * 32);
       g.top = g.heap[0];
+      g.live = k;       // an arriving list may be full
     }
     g.valid = lane < cnt;
 

@@ -85,6 +85,7 @@ knn_ring_kernel_t(const RingParams p) {
         for (int i = 0; i < k; ++i) g.heap[i * 32] = sent;
         g.top = sent;
         g.last_id = 0xffffffffu;
+        g.live = 0;
       }
     } else {
       if (p.use_flags) {
@@ -98,6 +99,7 @@ knn_ring_kernel_t(const RingParams p) {
         const float* src = p.inbox_heap[par] + (size_t)grp * k * 32 + lane;
         for (int i = 0; i < k; ++i) g.heap[i * 32] = ldcg_f(src + (size_t)i * 32);
         g.top = g.heap[0];
+        g.live = k;     // an arriving list may be full
       }
       if (p.use_flags) {
         __syncwarp();   // every lane's loads have returned (their values were stored to smem)

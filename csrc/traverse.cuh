@@ -20,7 +20,7 @@ constexpr int kBufRows = 2 * kFlushRows;   // a leaf (32 candidates) always fits
 __host__ __device__ constexpr int list_rows(int k) { return k + 1; }
 __host__ __device__ constexpr size_t warp_aux_floats() { return 128 + 2 * kQueueCap + 32 + 96 + 8; }   // stage | frontier | frames | soa | worklist
 __host__ __device__ constexpr size_t warp_smem_floats(int k, bool sorted) {
-  return (size_t)(sorted ? list_rows(k) + kBufRows : heap_padded(k)) * 32 + warp_aux_floats();
+  return (size_t)(sorted ? list_rows(k) + kBufRows + 1 : heap_padded(k)) * 32 + warp_aux_floats();
 }
 
 struct GroupCtx {
@@ -37,6 +37,7 @@ struct GroupCtx {
   unsigned* work;       // shared: lane-mask worklist of traverse_group (8 entries)
   float* buf;           // shared (sorted mode): buf[i*32] is buffered candidate i of this lane
   int cnt;              // sorted mode: candidates in this lane's buffer
+  int live;             // sorted mode: upper bound of the list entries that are not the sentinel any more
   bool flush_pending;   // sorted mode, warp-uniform: some lane's buffer cannot take another leaf
   int kp;               // rows of the candidate structure: padded heap size, or k + 1 in sorted mode
   bool valid;
@@ -114,10 +115,21 @@ __device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigne
 }
 #endif
 
-__device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g) {
+// This lane's point of a leaf (+inf padding beyond the leaf's count never beats any threshold). The
+// traversal issues this load as soon as it knows the leaf, next to the load of the leaf's box, so that
+// the two global-memory latencies overlap instead of following each other.
+__device__ __forceinline__ float4 load_leaf_point(const TreeView& t, int leaf, int cnt) {
+  float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
+  if (lane_id() < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane_id());
+  return p;
+}
+__device__ __forceinline__ int leaf_point_count(const TreeView& t, int leaf) {
+  const int rem = t.n - leaf * kGroup;
+  return rem < kGroup ? rem : kGroup;
+}
+
+__device__ __forceinline__ void process_leaf(const float4& p, GroupCtx& g) {
   const int lane = lane_id();
-  float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);   // padding never beats any top
-  if (lane < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane);
   g.stage[lane] = p;
   g.soa[lane] = p.x;          // x[32] | y[32] | z[32]: pairs of candidates load as one 64-bit word
   g.soa[32 + lane] = p.y;
@@ -166,10 +178,8 @@ __device__ __forceinline__ void process_leaf(const TreeView& t, int leaf, int cn
 // per lane, no test, no divergence — and one Floyd heapify turns the array into the heap. Values are
 // clamped to the sentinel, so a max-radius cut-off and +inf padding points behave as "no candidate".
 // The result is the same set of k smallest distances, hence bit-identical.
-__device__ __forceinline__ void fill_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g, int pos0) {
+__device__ __forceinline__ void fill_leaf(const float4& p, GroupCtx& g, int pos0) {
   const int lane = lane_id();
-  float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);
-  if (lane < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane);
   g.soa[lane] = p.x;
   g.soa[32 + lane] = p.y;
   g.soa[64 + lane] = p.z;
@@ -221,7 +231,7 @@ __device__ __forceinline__ void fill_finish(GroupCtx& g) {
 //     191-comparator network (missing entries are +inf), writes them back, and merges them into its
 //     list in place — skip the 32 largest of (list, batch), then k output steps of "store the larger
 //     head, advance that side". It is the same instruction stream for all lanes; only addresses and
-//     predicates differ. Values left in rows 32.. move to the front.
+//     predicates differ. A lane with more than 32 buffered values flushes its last 32.
 // The set of the k smallest distances is the same as with any other insertion order, so the k-th
 // distance is bit-identical to the heap's.
 //
@@ -235,7 +245,7 @@ __device__ __forceinline__ void fill_finish(GroupCtx& g) {
 // The two inner loops are predicated PTX: left to the compiler, "advance whichever side held the larger
 // head" became 14 instructions per step with address re-derivation on both arms.
 struct MergeHeads {
-  float a0, a1, a2, a3, b0, b1, b2, b3;    // a0/b0 = current heads, the others are prefetched successors
+  float a0, a1, a2, a3, b0, b1;    // a0/b0 = current heads, the others are prefetched successors
 };
 #if defined(B200KNN_SIMT_HOST)   // host emulation of the kernels (tests/simt): same steps in plain C++
 typedef float* smem_col_t;
@@ -243,11 +253,11 @@ __device__ __forceinline__ smem_col_t smem_col(float* p) { return p; }
 __device__ __forceinline__ void append_if_less(smem_col_t& p, float v, float thr) {
   if (v < thr) { *p = v; p += 32; }
 }
-// pa / pb: rows of a3 / b3. Returns the larger head and advances the side it came from (ties: b side).
+// pa / pb: rows of a3 / b1. Returns the larger head and advances the side it came from (ties: b side).
 __device__ __forceinline__ float merge_step(smem_col_t& pa, smem_col_t& pb, MergeHeads& h) {
   const float o = fmaxf(h.a0, h.b0);
   if (h.a0 > h.b0) { h.a0 = h.a1; h.a1 = h.a2; h.a2 = h.a3; pa += 32; h.a3 = *pa; }
-  else             { h.b0 = h.b1; h.b1 = h.b2; h.b2 = h.b3; pb += 32; h.b3 = *pb; }
+  else             { h.b0 = h.b1; pb += 32; h.b1 = *pb; }
   return o;
 }
 __device__ __forceinline__ int rows_between(smem_col_t from, smem_col_t to) { return (int)((to - from) >> 5); }
@@ -263,85 +273,82 @@ __device__ __forceinline__ float merge_step(smem_col_t& pa, smem_col_t& pb, Merg
   float o;
   asm volatile("{\n\t.reg .pred q;\n\tsetp.gt.f32 q, %1, %5;\n\tmax.f32 %0, %1, %5;\n\t"
                "@q mov.f32 %1, %2;\n\t@q mov.f32 %2, %3;\n\t@q mov.f32 %3, %4;\n\t"
-               "@q ld.shared.f32 %4, [%9+128];\n\t@q add.u32 %9, %9, 128;\n\t"
-               "@!q mov.f32 %5, %6;\n\t@!q mov.f32 %6, %7;\n\t@!q mov.f32 %7, %8;\n\t"
-               "@!q ld.shared.f32 %8, [%10+128];\n\t@!q add.u32 %10, %10, 128;\n\t}"
-               : "=f"(o), "+f"(h.a0), "+f"(h.a1), "+f"(h.a2), "+f"(h.a3), "+f"(h.b0), "+f"(h.b1), "+f"(h.b2),
-                 "+f"(h.b3), "+r"(pa), "+r"(pb));
+               "@q ld.shared.f32 %4, [%7+128];\n\t@q add.u32 %7, %7, 128;\n\t"
+               "@!q mov.f32 %5, %6;\n\t"
+               "@!q ld.shared.f32 %6, [%8+128];\n\t@!q add.u32 %8, %8, 128;\n\t}"
+               : "=f"(o), "+f"(h.a0), "+f"(h.a1), "+f"(h.a2), "+f"(h.a3), "+f"(h.b0), "+f"(h.b1), "+r"(pa), "+r"(pb));
   return o;
 }
 __device__ __forceinline__ int rows_between(smem_col_t from, smem_col_t to) { return (int)((to - from) >> 7); }
 #endif
 
 __device__ __forceinline__ void sorted_flush(GroupCtx& g, int k) {
-  float r[kFlushRows];
+  // This flush's batch = the lane's LAST (up to) 32 buffered rows [base, n); rows [0, base) simply stay
+  // where they are for the next flush. Row base + 32 (free: it is row n, or row 32 of a lane with
+  // n <= 32) takes the batch's -inf terminator.
   const int n = g.cnt;
+  const int base = n > kFlushRows ? n - kFlushRows : 0;
+  const int m = n - base;
+  float* bb = g.buf + base * 32;
+  float r[kFlushRows];
 #pragma unroll
-  for (int i = 0; i < kFlushRows; ++i) r[i] = i < n ? g.buf[i * 32] : INFINITY;
+  for (int i = 0; i < kFlushRows; ++i) r[i] = i < m ? bb[i * 32] : INFINITY;
 #define KNN_CE(a, b) { const float hi_ = fmaxf(r[a], r[b]); r[b] = fminf(r[a], r[b]); r[a] = hi_; }
 #include "sort32_network.inc"
 #undef KNN_CE
 #pragma unroll
-  for (int i = 0; i < kFlushRows; ++i) g.buf[i * 32] = r[i];
-  // the batch needs a terminator too; row 32 may hold a live candidate, so borrow it
-  const float saved = g.buf[kFlushRows * 32];
-  g.buf[kFlushRows * 32] = -INFINITY;
+  for (int i = 0; i < kFlushRows; ++i) bb[i * 32] = r[i];
+  bb[kFlushRows * 32] = -INFINITY;
 
-  // The union has k + 32 entries (+inf fillers included) and the 32 largest go: jb of them from the
-  // batch, 32 - jb from the list, jb = the largest j with batch[j-1] >= list[32-j] (merge path; ties drop
-  // the batch side first, so fillers go before sentinels). Rows past the list's terminator read as -inf.
+  // While the lists are still filling up, their first rows are sentinels and stay sentinels: with at
+  // most `live` real entries in any lane's list, output rows [0, t0) need not be touched.
+  const int live_max = (int)__reduce_max_sync(kFullMask, (unsigned)g.live);
+  const int t0 = k - kFlushRows - live_max > 0 ? k - kFlushRows - live_max : 0;
+  const int diag = kFlushRows + t0;
+  // The union has k + 32 entries (+inf fillers included); the `diag` largest are left alone: jb of them
+  // from the batch, diag - jb from the list, jb = the largest j with batch[j-1] >= list[diag-j] (merge
+  // path; ties take the batch side first, so fillers go before sentinels). Rows past the list's
+  // terminator read as the terminator.
   int jb = 0;
   {
     int hi = kFlushRows;
 #pragma unroll
     for (int it = 0; it < 6; ++it) {
       const int mid = (jb + hi + 1) >> 1;          // jb < mid <= hi whenever jb < hi
-      const int ai = kFlushRows - mid < k ? kFlushRows - mid : k;
-      const bool ok = mid > jb && g.buf[(mid - 1) * 32] >= g.heap[ai * 32];
+      const int ai = diag - mid < k ? diag - mid : k;
+      const bool ok = mid > jb && bb[(mid - 1) * 32] >= g.heap[ai * 32];
       if (mid > jb) { if (ok) jb = mid; else hi = mid - 1; }
     }
   }
-  const int ja = kFlushRows - jb;
+  const int ja = diag - jb;
   MergeHeads h;
   {
     const float* la = g.heap + ja * 32;
-    const float* lb = g.buf + jb * 32;
+    const float* lb = bb + jb * 32;
     h.a0 = la[0]; h.a1 = la[32]; h.a2 = la[64]; h.a3 = la[96];
-    h.b0 = lb[0]; h.b1 = lb[32]; h.b2 = lb[64]; h.b3 = lb[96];
+    h.b0 = lb[0]; h.b1 = lb[32];
   }
   __syncwarp();                             // the C++ stores above are in place before merge_step's loads
-  smem_col_t pa = smem_col(g.heap + (ja + 3) * 32), pb = smem_col(g.buf + (jb + 3) * 32);
+  smem_col_t pa = smem_col(g.heap + (ja + 3) * 32), pb = smem_col(bb + (jb + 1) * 32);
   // Output position t never passes the list head (the heads start 32 entries ahead in total and only
   // batch entries let t catch up), reads run ahead of writes, and where they meet the value is the same:
   // the merge is in place.
 #pragma unroll 4
-  for (int t = 0; t < k; ++t) g.heap[t * 32] = merge_step(pa, pb, h);
+  for (int t = t0; t < k; ++t) g.heap[t * 32] = merge_step(pa, pb, h);
   __syncwarp();
-  g.buf[kFlushRows * 32] = saved;
 
-  // what did not fit into this batch moves to the front, minus what the new k-th distance rules out
-  const float top = g.heap[0];
-  const int rest = n > kFlushRows ? n - kFlushRows : 0;
-  const int most = (int)__reduce_max_sync(kFullMask, (unsigned)rest);
-  int w = 0;
-  for (int i = 0; i < most; ++i) {
-    const float v = g.buf[(kFlushRows + i) * 32];
-    if (i < rest && v < top) { g.buf[w * 32] = v; ++w; }
-  }
-  g.cnt = w;
-  g.top = top;
-  __syncwarp();
+  g.live = g.live + m < k ? g.live + m : k;
+  g.cnt = base;
+  g.top = g.heap[0];
   g.maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, g.valid ? __float_as_uint(g.top) : 0u));
-  g.flush_pending = false;                  // w <= 32 on every lane
+  g.flush_pending = false;                  // base <= 32 on every lane
   ++g.n_flush;
 }
 
 // One leaf against the lanes' thresholds: survivors are appended to the lanes' buffers (see above).
 // Precondition: every lane has at most 32 buffered values (the traversal flushes before the next leaf).
-__device__ __forceinline__ void append_leaf(const TreeView& t, int leaf, int cnt, GroupCtx& g) {
+__device__ __forceinline__ void append_leaf(const float4& p, GroupCtx& g) {
   const int lane = lane_id();
-  float4 p = make_float4(INFINITY, INFINITY, INFINITY, 0.f);   // padding never beats any threshold
-  if (lane < cnt) p = __ldg(reinterpret_cast<const float4*>(t.pts) + (size_t)leaf * kGroup + lane);
   g.soa[lane] = p.x;
   g.soa[32 + lane] = p.y;
   g.soa[64 + lane] = p.z;
@@ -373,10 +380,10 @@ __device__ __forceinline__ void append_leaf(const TreeView& t, int leaf, int cnt
 }
 
 // Exact per-query test against the leaf box; skip the leaf if no lane can improve.
-__device__ __forceinline__ void maybe_leaf(const TreeView& t, int leaf, float lx, float ly, float lz,
-                                           float hx, float hy, float hz, int cnt, GroupCtx& g) {
+__device__ __forceinline__ void maybe_leaf(const float4& p, float lx, float ly, float lz,
+                                           float hx, float hy, float hz, GroupCtx& g) {
   const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
-  if (__any_sync(kFullMask, g.valid && (lb < g.top))) process_leaf(t, leaf, cnt, g);
+  if (__any_sync(kFullMask, g.valid && (lb < g.top))) process_leaf(p, g);
 }
 
 // What traverse() does with a leaf that survives the group-level test. The default keeps the k
@@ -384,9 +391,9 @@ __device__ __forceinline__ void maybe_leaf(const TreeView& t, int leaf, float lx
 struct HeapLeafOp {
   static constexpr bool kBuffered = false;
   __device__ __forceinline__ void flush(GroupCtx&) const {}
-  __device__ __forceinline__ void operator()(const TreeView& t, int leaf, float lx, float ly, float lz, float hx,
-                                             float hy, float hz, int cnt, GroupCtx& g) const {
-    maybe_leaf(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
+  __device__ __forceinline__ void operator()(const float4& p, float lx, float ly, float lz, float hx,
+                                             float hy, float hz, GroupCtx& g) const {
+    maybe_leaf(p, lx, ly, lz, hx, hy, hz, g);
   }
 };
 
@@ -396,10 +403,10 @@ struct SortedLeafOp {
   static constexpr bool kBuffered = true;
   int k;
   __device__ __forceinline__ void flush(GroupCtx& g) const { sorted_flush(g, k); }
-  __device__ __forceinline__ void operator()(const TreeView& t, int leaf, float lx, float ly, float lz, float hx,
-                                             float hy, float hz, int cnt, GroupCtx& g) const {
+  __device__ __forceinline__ void operator()(const float4& p, float lx, float ly, float lz, float hx,
+                                             float hy, float hz, GroupCtx& g) const {
     const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
-    if (__any_sync(kFullMask, g.valid && (lb < g.top))) append_leaf(t, leaf, cnt, g);
+    if (__any_sync(kFullMask, g.valid && (lb < g.top))) append_leaf(p, g);
   }
 };
 
@@ -524,7 +531,7 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
     if constexpr (LeafOp::kBuffered) {
       if (g.flush_pending) leaf_op.flush(g);
     }
-    int leaf, cnt;
+    float4 pt;
     float lx, ly, lz, hx, hy, hz;
     if (depth >= 0) {
       // ---- frame step
@@ -556,12 +563,11 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         __syncwarp();
         continue;
       }
+      pt = load_leaf_point(t, child, leaf_point_count(t, child));
       __syncwarp();
-      leaf = child;
       lx = __shfl_sync(kFullMask, a.x, who); ly = __shfl_sync(kFullMask, a.y, who);
       lz = __shfl_sync(kFullMask, a.z, who); hx = __shfl_sync(kFullMask, b.x, who);
       hy = __shfl_sync(kFullMask, b.y, who); hz = __shfl_sync(kFullMask, b.z, who);
-      cnt = __float_as_int(__shfl_sync(kFullMask, a.w, who));
     } else {
       // ---- frontier step
       if (!started) {
@@ -608,17 +614,16 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       }
       const float4* bp = reinterpret_cast<const float4*>(t.boxes[0]) + 2 * (size_t)idx;
       const float4 a = __ldg(bp), b = __ldg(bp + 1);
-      leaf = idx;
+      pt = load_leaf_point(t, idx, leaf_point_count(t, idx));
       lx = a.x; ly = a.y; lz = a.z; hx = b.x; hy = b.y; hz = b.z;
-      cnt = __float_as_int(a.w);
     }
     if (fill_leaves > 0) {
-      fill_leaf(t, leaf, cnt, g, fill_pos);
+      fill_leaf(pt, g, fill_pos);
       fill_pos += kGroup;
       if (--fill_leaves == 0) fill_finish(g);
       continue;
     }
-    leaf_op(t, leaf, lx, ly, lz, hx, hy, hz, cnt, g);
+    leaf_op(pt, lx, ly, lz, hx, hy, hz, g);
   }
   if (fill_pos > 0 && fill_leaves > 0) fill_finish(g);    // the tree ran out of leaves during the fill
 }
@@ -628,7 +633,7 @@ __host__ __device__ constexpr size_t warp_smem_floats_noheap() { return warp_aux
 
 // Carve one warp's slice of dynamic shared memory: candidate structure first, then the staging and
 // frontier areas.
-//   sorted               list (k + 1 rows) | append buffer (kBufRows rows) | aux
+//   sorted               list (k + 1 rows) | append buffer (kBufRows + 1 rows) | aux
 //   heap in shared       padded heap | aux
 //   heap in global       (global_heap != nullptr) this warp's [kp][32] block of `global_heap`; shared
 //                        memory only holds the aux areas.
@@ -646,7 +651,7 @@ __device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int war
     aux = warp_base + (size_t)kp * 32;
     if (sorted) {
       g.buf = aux + lane;
-      aux += (size_t)kBufRows * 32;
+      aux += (size_t)(kBufRows + 1) * 32;
     }
   }
   g.stage = reinterpret_cast<float4*>(aux);
@@ -657,6 +662,7 @@ __device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int war
   g.work = reinterpret_cast<unsigned*>(g.soa + 96);
   g.kp = kp;
   g.cnt = 0;
+  g.live = k;
   g.flush_pending = false;
   g.n_leaves = g.n_inner = g.n_inserts = g.n_fallback = g.n_purge = g.n_flush = 0;
 }
