@@ -18,9 +18,13 @@ __host__ __device__ constexpr int heap_padded(int k) { return 4 * ((k - 1 + 3) /
 constexpr int kFlushRows = 32;         // buffered candidates merged per flush (one register sort)
 constexpr int kBufRows = 2 * kFlushRows;   // a leaf (32 candidates) always fits behind a not-yet-flushed batch
 __host__ __device__ constexpr int list_rows(int k) { return k + 1; }
-__host__ __device__ constexpr size_t warp_aux_floats() { return 128 + 2 * kQueueCap + 32 + 96 + 8; }   // stage | frontier | frames | soa | worklist
+// frontier | frames | soa | worklist, preceded by the float4 stage of the heap kernels (the sorted path has no use for it)
+__host__ __device__ constexpr size_t warp_aux_floats(bool with_stage = true) {
+  return (with_stage ? 128 : 0) + 2 * kQueueCap + 32 + 96 + 8;
+}
 __host__ __device__ constexpr size_t warp_smem_floats(int k, bool sorted) {
-  return (size_t)(sorted ? list_rows(k) + kBufRows + 1 : heap_padded(k)) * 32 + warp_aux_floats();
+  return sorted ? (size_t)(list_rows(k) + kBufRows + 1) * 32 + warp_aux_floats(false)
+                : (size_t)heap_padded(k) * 32 + warp_aux_floats(true);
 }
 
 struct GroupCtx {
@@ -654,8 +658,8 @@ __device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int war
       aux += (size_t)(kBufRows + 1) * 32;
     }
   }
-  g.stage = reinterpret_cast<float4*>(aux);
-  g.qkey = reinterpret_cast<unsigned*>(aux + 128);
+  g.stage = sorted ? nullptr : reinterpret_cast<float4*>(aux);
+  g.qkey = reinterpret_cast<unsigned*>(aux + (sorted ? 0 : 128));
   g.qnode = g.qkey + kQueueCap;
   g.frames = g.qnode + kQueueCap;
   g.soa = reinterpret_cast<float*>(g.frames + 32);
