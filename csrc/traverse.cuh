@@ -457,16 +457,23 @@ __device__ __forceinline__ int find_seed_l1(const TreeView& t, const GroupCtx& g
 
 // Push the children [base, base+count) of `level` that lie inside the group radius. On overflow
 // (after purging stale entries) the children are handed to the frame stack instead.
-__device__ __forceinline__ void frontier_expand(const TreeView& t, int level, int base, int count, int seed_l1,
-                                                int& qcount, int& depth, GroupCtx& g) {
-  const int lane = lane_id();
-  const bool have = lane < count;
-  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-  if (have) {
-    const float4* bp = reinterpret_cast<const float4*>(t.boxes[level]) + 2 * (size_t)(base + lane);
+// This lane's child box of the node whose children are [base, base+count) on `level` (zeros beyond count).
+__device__ __forceinline__ void load_child_box(const TreeView& t, int level, int base, int count, float4& a, float4& b) {
+  a = make_float4(0.f, 0.f, 0.f, 0.f);
+  b = a;
+  if (lane_id() < count) {
+    const float4* bp = reinterpret_cast<const float4*>(t.boxes[level]) + 2 * (size_t)(base + lane_id());
     a = __ldg(bp);
     b = __ldg(bp + 1);
   }
+}
+
+// (a, b) = this lane's child box, loaded by the caller (load_child_box) — early, so that the latency is
+// behind other work by the time the keys are needed.
+__device__ __forceinline__ void frontier_expand(int level, int base, int count, const float4& a, const float4& b,
+                                                int seed_l1, int& qcount, int& depth, GroupCtx& g) {
+  const int lane = lane_id();
+  const bool have = lane < count;
   const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
   const bool pass = have && (key < g.maxR2) && !(level == 1 && base + lane == seed_l1);
   const unsigned mask = __ballot_sync(kFullMask, pass);
@@ -514,9 +521,23 @@ __device__ __forceinline__ void frontier_expand(const TreeView& t, int level, in
 
 // fill_leaves > 0: the valid lanes' heaps are fresh; the first fill_leaves leaves that come up are
 // appended without a test (see fill_leaf). fill_leaves * 32 <= k.
-// Buffered leaf ops (LeafOp::kBuffered) are flushed at ONE place, the top of the loop: when a buffer is
-// about to overflow, and when the traversal would otherwise stop — the flush tightens the radius, after
-// which the stop test is simply evaluated again.
+//
+// The loop is software-pipelined by one item. With ~10 resident warps per SM nothing else hides a
+// dependent global-memory access, and a best-first walk is a chain of them (pop -> load the node's
+// boxes -> decide -> load the leaf's points -> sweep). So every iteration first SELECTS the next item —
+// pops the nearest frontier entry and issues its loads (a leaf: its box and this lane's point; an inner
+// node: this lane's child box) — and only then PROCESSES the item selected one iteration earlier, whose
+// loads have had a whole leaf sweep or expansion to arrive. Popping one item early is harmless: between
+// two flushes the radius does not change anyway, an item is re-checked against the current radius when
+// its turn comes, and any visiting order is exact.
+// Order of business: the 32 leaves of the seed level-1 node go through the frontier first; the root is
+// expanded only when they are done (and flushed), so that the radius is tight before inner nodes are
+// queued. Buffered leaf ops (LeafOp::kBuffered) are flushed at ONE place, the top of the loop: when a
+// buffer is about to overflow, and when the traversal would otherwise stop — the flush tightens the
+// radius, after which the stop test is simply evaluated again. Frontier overflow falls back to the
+// depth-first frame stack (rare; not pipelined).
+constexpr unsigned kNoNode = 0xffffffffu;
+
 template <class LeafOp>
 __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int seed_l1, int fill_leaves, LeafOp& leaf_op) {
   const int lane = lane_id();
@@ -525,31 +546,29 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
   const int top_level = t.levels - 1;
   int depth = -1, qcount = 0;
   bool started = false;
+  // the item selected one iteration ago: node, its frontier key, its loads
+  unsigned cur_node = kNoNode, cur_key = 0u;
+  float4 cur_a = make_float4(0.f, 0.f, 0.f, 0.f), cur_b = cur_a, cur_p = cur_a;
+
   if (seed_l1 >= 0) {
-    const int rem = t.count[0] - seed_l1 * kFanout;
-    if (lane == 0) push_frame(fr, 0, 0, seed_l1 * kFanout, rem < kFanout ? rem : kFanout);
-    depth = 0;
-    __syncwarp();
+    const int base = seed_l1 * kFanout, rem = t.count[0] - base;
+    const int count = rem < kFanout ? rem : kFanout;
+    float4 a, b;
+    load_child_box(t, 0, base, count, a, b);
+    frontier_expand(0, base, count, a, b, seed_l1, qcount, depth, g);
   }
   for (;;) {
     if constexpr (LeafOp::kBuffered) {
       if (g.flush_pending) leaf_op.flush(g);
     }
-    float4 pt;
-    float lx, ly, lz, hx, hy, hz;
     if (depth >= 0) {
-      // ---- frame step
+      // ---- frame step (overflow fallback): depth-first, nearest child first, boxes re-loaded per visit
       const int L = (int)fr[depth * 4 + 0], B = (int)fr[depth * 4 + 1], Cn = (int)fr[depth * 4 + 2];
       const unsigned todo_in = fr[depth * 4 + 3];
-      const bool have = lane < Cn;
-      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-      if (have) {
-        const float4* bp = reinterpret_cast<const float4*>(t.boxes[L]) + 2 * (size_t)(B + lane);
-        a = __ldg(bp);
-        b = __ldg(bp + 1);
-      }
+      float4 a, b;
+      load_child_box(t, L, B, Cn, a, b);
       const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
-      const bool pass = have && ((todo_in >> lane) & 1u) && (key < g.maxR2) &&
+      const bool pass = lane < Cn && ((todo_in >> lane) & 1u) && (key < g.maxR2) &&
                         !(L == 1 && B + lane == seed_l1);
       const unsigned pm = __ballot_sync(kFullMask, pass);
       if (pm == 0u) { --depth; continue; }
@@ -567,24 +586,25 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         __syncwarp();
         continue;
       }
-      pt = load_leaf_point(t, child, leaf_point_count(t, child));
+      const float4 pt = load_leaf_point(t, child, leaf_point_count(t, child));
       __syncwarp();
-      lx = __shfl_sync(kFullMask, a.x, who); ly = __shfl_sync(kFullMask, a.y, who);
-      lz = __shfl_sync(kFullMask, a.z, who); hx = __shfl_sync(kFullMask, b.x, who);
-      hy = __shfl_sync(kFullMask, b.y, who); hz = __shfl_sync(kFullMask, b.z, who);
-    } else {
-      // ---- frontier step
-      if (!started) {
-        started = true;
-        frontier_expand(t, top_level, 0, t.count[top_level], seed_l1, qcount, depth, g);
-        continue;
+      const float lx = __shfl_sync(kFullMask, a.x, who), ly = __shfl_sync(kFullMask, a.y, who);
+      const float lz = __shfl_sync(kFullMask, a.z, who), hx = __shfl_sync(kFullMask, b.x, who);
+      const float hy = __shfl_sync(kFullMask, b.y, who), hz = __shfl_sync(kFullMask, b.z, who);
+      if (fill_leaves > 0) {
+        fill_leaf(pt, g, fill_pos);
+        fill_pos += kGroup;
+        if (--fill_leaves == 0) fill_finish(g);
+      } else {
+        leaf_op(pt, lx, ly, lz, hx, hy, hz, g);
       }
-      if (qcount == 0) {
-        if constexpr (LeafOp::kBuffered) {
-          if (__any_sync(kFullMask, g.cnt > 0)) { g.flush_pending = true; continue; }
-        }
-        break;
-      }
+      continue;
+    }
+
+    // ---- select: pop the nearest frontier entry inside the radius and issue its loads
+    unsigned nx_node = kNoNode, nx_key = 0u;
+    float4 nx_a = make_float4(0.f, 0.f, 0.f, 0.f), nx_b = nx_a, nx_p = nx_a;
+    if (qcount > 0) {
       unsigned best = 0xffffffffu;
       int bslot = 0;
       for (int s = lane; s < qcount; s += 32) {
@@ -592,44 +612,64 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         if (kx < best) { best = kx; bslot = s; }
       }
       const unsigned m = __reduce_min_sync(kFullMask, best);
-      if (m >= __float_as_uint(g.maxR2)) {               // nothing left inside the group radius
-        if constexpr (LeafOp::kBuffered) {
-          if (__any_sync(kFullMask, g.cnt > 0)) { g.flush_pending = true; continue; }
+      if (m < __float_as_uint(g.maxR2)) {
+        const int wl = __ffs(__ballot_sync(kFullMask, best == m)) - 1;
+        const int slot = __shfl_sync(kFullMask, bslot, wl);
+        nx_node = g.qnode[slot];
+        nx_key = m;
+        __syncwarp();
+        if (lane == 0) {
+          g.qkey[slot] = g.qkey[qcount - 1];
+          g.qnode[slot] = g.qnode[qcount - 1];
         }
-        break;
+        --qcount;
+        __syncwarp();
+        const int level = (int)(nx_node >> kNodeIdxBits);
+        const int idx = (int)(nx_node & ((1u << kNodeIdxBits) - 1u));
+        if (level == 0) {
+          const float4* bp = reinterpret_cast<const float4*>(t.boxes[0]) + 2 * (size_t)idx;
+          nx_a = __ldg(bp);
+          nx_b = __ldg(bp + 1);
+          nx_p = load_leaf_point(t, idx, leaf_point_count(t, idx));
+        } else {
+          const int rem = t.count[level - 1] - idx * kFanout;
+          load_child_box(t, level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, nx_a, nx_b);
+        }
       }
-      const int wl = __ffs(__ballot_sync(kFullMask, best == m)) - 1;
-      const int slot = __shfl_sync(kFullMask, bslot, wl);
-      const unsigned node = g.qnode[slot];
-      __syncwarp();
-      if (lane == 0) {
-        g.qkey[slot] = g.qkey[qcount - 1];
-        g.qnode[slot] = g.qnode[qcount - 1];
-      }
-      --qcount;
-      __syncwarp();
-      const int level = (int)(node >> kNodeIdxBits);
-      const int idx = (int)(node & ((1u << kNodeIdxBits) - 1u));
-      if (level != 0) {
-        ++g.n_inner;
-        const int rem = t.count[level - 1] - idx * kFanout;
-        frontier_expand(t, level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, seed_l1, qcount, depth, g);
-        continue;
-      }
-      const float4* bp = reinterpret_cast<const float4*>(t.boxes[0]) + 2 * (size_t)idx;
-      const float4 a = __ldg(bp), b = __ldg(bp + 1);
-      pt = load_leaf_point(t, idx, leaf_point_count(t, idx));
-      lx = a.x; ly = a.y; lz = a.z; hx = b.x; hy = b.y; hz = b.z;
     }
-    if (fill_leaves > 0) {
-      fill_leaf(pt, g, fill_pos);
-      fill_pos += kGroup;
-      if (--fill_leaves == 0) fill_finish(g);
+
+    // ---- process the item selected one iteration ago
+    if (cur_node != kNoNode) {
+      if (cur_key < __float_as_uint(g.maxR2)) {          // the radius may have shrunk since it was popped
+        const int level = (int)(cur_node >> kNodeIdxBits);
+        const int idx = (int)(cur_node & ((1u << kNodeIdxBits) - 1u));
+        if (level != 0) {
+          ++g.n_inner;
+          const int rem = t.count[level - 1] - idx * kFanout;
+          frontier_expand(level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, cur_a, cur_b, seed_l1, qcount, depth, g);
+        } else if (fill_leaves > 0) {
+          fill_leaf(cur_p, g, fill_pos);
+          fill_pos += kGroup;
+          if (--fill_leaves == 0) fill_finish(g);
+        } else {
+          leaf_op(cur_p, cur_a.x, cur_a.y, cur_a.z, cur_b.x, cur_b.y, cur_b.z, g);
+        }
+      }
+    } else if (nx_node == kNoNode) {
+      // nothing in flight and nothing left inside the radius
+      if constexpr (LeafOp::kBuffered) {
+        if (__any_sync(kFullMask, g.cnt > 0)) { g.flush_pending = true; continue; }
+      }
+      if (fill_pos > 0 && fill_leaves > 0) { fill_finish(g); fill_leaves = 0; continue; }   // ran out of leaves during the fill
+      if (started) break;
+      started = true;
+      float4 a, b;
+      load_child_box(t, top_level, 0, t.count[top_level], a, b);
+      frontier_expand(top_level, 0, t.count[top_level], a, b, seed_l1, qcount, depth, g);
       continue;
     }
-    leaf_op(pt, lx, ly, lz, hx, hy, hz, g);
+    cur_node = nx_node; cur_key = nx_key; cur_a = nx_a; cur_b = nx_b; cur_p = nx_p;
   }
-  if (fill_pos > 0 && fill_leaves > 0) fill_finish(g);    // the tree ran out of leaves during the fill
 }
 
 // Shared-memory floats per warp when the heap lives in GLOBAL memory (k too large for shared memory).
