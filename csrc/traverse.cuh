@@ -522,20 +522,25 @@ __device__ __forceinline__ void frontier_expand(int level, int base, int count, 
 // fill_leaves > 0: the valid lanes' heaps are fresh; the first fill_leaves leaves that come up are
 // appended without a test (see fill_leaf). fill_leaves * 32 <= k.
 //
-// The loop is software-pipelined by one item. With ~10 resident warps per SM nothing else hides a
-// dependent global-memory access, and a best-first walk is a chain of them (pop -> load the node's
-// boxes -> decide -> load the leaf's points -> sweep). So every iteration first SELECTS the next item —
-// pops the nearest frontier entry and issues its loads (a leaf: its box and this lane's point; an inner
-// node: this lane's child box) — and only then PROCESSES the item selected one iteration earlier, whose
-// loads have had a whole leaf sweep or expansion to arrive. Popping one item early is harmless: between
-// two flushes the radius does not change anyway, an item is re-checked against the current radius when
-// its turn comes, and any visiting order is exact.
-// Order of business: the 32 leaves of the seed level-1 node go through the frontier first; the root is
-// expanded only when they are done (and flushed), so that the radius is tight before inner nodes are
-// queued. Buffered leaf ops (LeafOp::kBuffered) are flushed at ONE place, the top of the loop: when a
-// buffer is about to overflow, and when the traversal would otherwise stop — the flush tightens the
-// radius, after which the stop test is simply evaluated again. Frontier overflow falls back to the
-// depth-first frame stack (rare; not pipelined).
+// Structure of the walk:
+//   * the FRONTIER (shared memory, best-first) holds inner nodes only;
+//   * when a level-1 node is opened, its 32 leaf boxes stay in the lanes' registers as a LEAF RUN: the
+//     leaves inside the radius are swept nearest first, one per loop iteration, "pop" = one redux.sync
+//     over the lanes' keys; a run ends when its nearest remaining leaf is outside the current radius.
+//     Leaves of different level-1 nodes are therefore not interleaved by distance; each leaf is still
+//     checked against the radius of the moment, and any visiting order is exact;
+//   * the walk starts with a run over the seed level-1 node (the group's own, or the nearest), and the
+//     root is expanded only when that run is done (and flushed), so the radius is tight before any
+//     inner node is queued.
+// With ~10 resident warps per SM nothing else hides a dependent global-memory access, so the loop is
+// software-pipelined by one item: the next leaf of a run is chosen, and this lane's point of it
+// requested, before the current leaf is swept; the next frontier entry is popped, and this lane's child
+// box of it requested, before the current inner node is expanded. Popping early is harmless: between
+// two flushes the radius does not change anyway and an item is re-checked when its turn comes.
+// Buffered leaf ops (LeafOp::kBuffered) are flushed at ONE place, the top of the loop: when a buffer is
+// about to overflow, and when the walk would otherwise stop — the flush tightens the radius, after
+// which the stop test is simply evaluated again. Frontier overflow falls back to the depth-first frame
+// stack (rare; not pipelined).
 constexpr unsigned kNoNode = 0xffffffffu;
 
 template <class LeafOp>
@@ -546,16 +551,33 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
   const int top_level = t.levels - 1;
   int depth = -1, qcount = 0;
   bool started = false;
-  // the item selected one iteration ago: node, its frontier key, its loads
+  // the inner node selected one iteration ago: node, its frontier key, this lane's child box
   unsigned cur_node = kNoNode, cur_key = 0u;
-  float4 cur_a = make_float4(0.f, 0.f, 0.f, 0.f), cur_b = cur_a, cur_p = cur_a;
+  float4 cur_a = make_float4(0.f, 0.f, 0.f, 0.f), cur_b = cur_a;
+  // the leaf run: this lane's leaf box and key (0xffffffff = not / no longer a candidate), the leaf
+  // whose turn is next and this lane's point of it
+  float4 run_a = cur_a, run_b = cur_a, run_pt = cur_a;
+  unsigned run_key = 0xffffffffu;
+  int run_base = 0, run_who = -1;              // run_who < 0: no run
+
+  auto run_select = [&]() {                    // nearest remaining leaf of the run; request its points
+    const unsigned m = __reduce_min_sync(kFullMask, run_key);
+    run_who = m == 0xffffffffu ? -1 : __ffs(__ballot_sync(kFullMask, run_key == m)) - 1;
+    if (run_who >= 0) run_pt = load_leaf_point(t, run_base + run_who, leaf_point_count(t, run_base + run_who));
+  };
+  auto run_start = [&](int base, int count, const float4& a, const float4& b) {
+    run_a = a; run_b = b; run_base = base;
+    const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
+    run_key = (lane < count && key < g.maxR2) ? __float_as_uint(key) : 0xffffffffu;
+    run_select();
+  };
 
   if (seed_l1 >= 0) {
     const int base = seed_l1 * kFanout, rem = t.count[0] - base;
     const int count = rem < kFanout ? rem : kFanout;
     float4 a, b;
     load_child_box(t, 0, base, count, a, b);
-    frontier_expand(0, base, count, a, b, seed_l1, qcount, depth, g);
+    run_start(base, count, a, b);
   }
   for (;;) {
     if constexpr (LeafOp::kBuffered) {
@@ -601,9 +623,30 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       continue;
     }
 
-    // ---- select: pop the nearest frontier entry inside the radius and issue its loads
+    if (run_who >= 0) {
+      // ---- leaf run step: take the selected leaf, select + request the next one, then sweep
+      const int who = run_who;
+      const float4 pt = run_pt;
+      const unsigned kw = __shfl_sync(kFullMask, run_key, who);
+      const float lx = __shfl_sync(kFullMask, run_a.x, who), ly = __shfl_sync(kFullMask, run_a.y, who);
+      const float lz = __shfl_sync(kFullMask, run_a.z, who), hx = __shfl_sync(kFullMask, run_b.x, who);
+      const float hy = __shfl_sync(kFullMask, run_b.y, who), hz = __shfl_sync(kFullMask, run_b.z, who);
+      if (!(kw < __float_as_uint(g.maxR2))) { run_who = -1; continue; }   // nearest first: the rest is farther still
+      if (lane == who) run_key = 0xffffffffu;
+      run_select();
+      if (fill_leaves > 0) {
+        fill_leaf(pt, g, fill_pos);
+        fill_pos += kGroup;
+        if (--fill_leaves == 0) fill_finish(g);
+      } else {
+        leaf_op(pt, lx, ly, lz, hx, hy, hz, g);
+      }
+      continue;
+    }
+
+    // ---- select: pop the nearest frontier entry inside the radius and request this lane's child box
     unsigned nx_node = kNoNode, nx_key = 0u;
-    float4 nx_a = make_float4(0.f, 0.f, 0.f, 0.f), nx_b = nx_a, nx_p = nx_a;
+    float4 nx_a = make_float4(0.f, 0.f, 0.f, 0.f), nx_b = nx_a;
     if (qcount > 0) {
       unsigned best = 0xffffffffu;
       int bslot = 0;
@@ -626,49 +669,41 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         __syncwarp();
         const int level = (int)(nx_node >> kNodeIdxBits);
         const int idx = (int)(nx_node & ((1u << kNodeIdxBits) - 1u));
-        if (level == 0) {
-          const float4* bp = reinterpret_cast<const float4*>(t.boxes[0]) + 2 * (size_t)idx;
-          nx_a = __ldg(bp);
-          nx_b = __ldg(bp + 1);
-          nx_p = load_leaf_point(t, idx, leaf_point_count(t, idx));
-        } else {
-          const int rem = t.count[level - 1] - idx * kFanout;
-          load_child_box(t, level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, nx_a, nx_b);
-        }
+        const int rem = t.count[level - 1] - idx * kFanout;
+        load_child_box(t, level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, nx_a, nx_b);
       }
     }
 
-    // ---- process the item selected one iteration ago
+    // ---- process the inner node selected one iteration ago
     if (cur_node != kNoNode) {
       if (cur_key < __float_as_uint(g.maxR2)) {          // the radius may have shrunk since it was popped
         const int level = (int)(cur_node >> kNodeIdxBits);
         const int idx = (int)(cur_node & ((1u << kNodeIdxBits) - 1u));
-        if (level != 0) {
-          ++g.n_inner;
-          const int rem = t.count[level - 1] - idx * kFanout;
-          frontier_expand(level - 1, idx * kFanout, rem < kFanout ? rem : kFanout, cur_a, cur_b, seed_l1, qcount, depth, g);
-        } else if (fill_leaves > 0) {
-          fill_leaf(cur_p, g, fill_pos);
-          fill_pos += kGroup;
-          if (--fill_leaves == 0) fill_finish(g);
-        } else {
-          leaf_op(cur_p, cur_a.x, cur_a.y, cur_a.z, cur_b.x, cur_b.y, cur_b.z, g);
-        }
+        ++g.n_inner;
+        const int rem = t.count[level - 1] - idx * kFanout;
+        const int count = rem < kFanout ? rem : kFanout;
+        if (level == 1) run_start(idx * kFanout, count, cur_a, cur_b);
+        else frontier_expand(level - 1, idx * kFanout, count, cur_a, cur_b, seed_l1, qcount, depth, g);
       }
     } else if (nx_node == kNoNode) {
       // nothing in flight and nothing left inside the radius
+      if (fill_pos > 0 && fill_leaves > 0) { fill_finish(g); fill_leaves = 0; continue; }   // ran out of leaves during the fill
+      if (!started) {
+        // the seed run is over: open the root (with the radius as of the last flush; whatever that
+        // lets in too generously is dropped again when its turn comes)
+        started = true;
+        float4 a, b;
+        load_child_box(t, top_level, 0, t.count[top_level], a, b);
+        if (top_level == 0) { if (seed_l1 < 0) run_start(0, t.count[0], a, b); }
+        else frontier_expand(top_level, 0, t.count[top_level], a, b, seed_l1, qcount, depth, g);
+        continue;
+      }
       if constexpr (LeafOp::kBuffered) {
         if (__any_sync(kFullMask, g.cnt > 0)) { g.flush_pending = true; continue; }
       }
-      if (fill_pos > 0 && fill_leaves > 0) { fill_finish(g); fill_leaves = 0; continue; }   // ran out of leaves during the fill
-      if (started) break;
-      started = true;
-      float4 a, b;
-      load_child_box(t, top_level, 0, t.count[top_level], a, b);
-      frontier_expand(top_level, 0, t.count[top_level], a, b, seed_l1, qcount, depth, g);
-      continue;
+      break;
     }
-    cur_node = nx_node; cur_key = nx_key; cur_a = nx_a; cur_b = nx_b; cur_p = nx_p;
+    cur_node = nx_node; cur_key = nx_key; cur_a = nx_a; cur_b = nx_b;
   }
 }
 
