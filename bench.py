@@ -102,8 +102,7 @@ def main() -> int:
                     help="multi-GPU strategy (auto = redistribute: scatter to spatial owners + bbox-culled exchange)")
     ap.add_argument("--chunk-groups", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--verify", action="store_true",
-                    help="several GPUs: also run the (collective) counting check of sampled results; always on for 1 GPU")
+    ap.add_argument("--verify", action="store_true", help="kept for old command lines: the check always runs")
     args = ap.parse_args()
 
     if args.impl == "reference":
@@ -230,16 +229,14 @@ def main() -> int:
         except Exception as e:  # noqa: BLE001
             e2e["prefetch_error"] = repr(e)[:200]
 
-    # Outside every timed region: check 64 sampled results of the last step against ALL points with one
-    # counting pass (independent of index, heaps and traversal). On several GPUs it is collective and only
-    # runs on request; it must never cost the bench its number.
-    verified = None
-    if world == 1 or args.verify:
-        try:
-            from mpi_cuda_largescaleknn_b200.ops.knn import verify_sample
-            verified = verify_sample(x_dev, out_dev, k, samples=64, seed=7)
-        except Exception as e:  # noqa: BLE001
-            verified = {"error": repr(e)[:200]}
+    # Outside every timed region, at every GPU count: check 64 sampled results of the last step against ALL
+    # points of all ranks with one counting pass (independent of index, lists and traversal). Collective:
+    # every rank calls it.
+    try:
+        from mpi_cuda_largescaleknn_b200.ops.knn import verify_sample
+        verified = verify_sample(x_dev, out_dev, k, samples=64, seed=7)
+    except Exception as e:  # noqa: BLE001
+        verified = {"error": repr(e)[:200]}
 
     if rank == 0:
         line = {

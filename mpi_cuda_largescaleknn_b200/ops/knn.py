@@ -156,42 +156,66 @@ def neighbors(index: "KnnIndex", queries: Optional[torch.Tensor], k: int, max_ra
 
 
 def verify_sample(points: torch.Tensor, result: torch.Tensor, k: int, samples: int = 64, seed: int = 0,
-                  group=None) -> dict:
+                  group=None, max_radius: float = math.inf) -> dict:
     """Check ``samples`` (<= 64) randomly chosen entries of a self-kNN ``result`` against ALL points with one
     counting pass on the GPU: ``result[i]`` is right iff fewer than k points are strictly closer than it and at
-    least k are no farther. With ``group`` (a torch.distributed process group whose ranks each pass their own
-    ``points`` / ``result`` slice) rank 0's sample is checked against the union of all ranks' points.
-    Returns ``{"queries": n, "violations": v}``. Independent of the index, the heaps and the traversal."""
+    least k are no farther. A result equal to ``sqrt(max_radius^2)`` (the cut-off) is right iff fewer than k
+    points lie strictly inside the cut-off; ``+inf`` iff fewer than k points exist at all.
+    On several ranks (``group``, or the default process group when one is initialised) every rank passes its own
+    ``points`` / ``result`` slice and ALL ranks must call; the sample is drawn on the first rank that holds any
+    points and checked against the union of all ranks' points.
+    Returns ``{"queries": n, "violations": v}``. Independent of the index, the lists and the traversal."""
     import torch.distributed as dist
     xyz = _as_xyz(points)
     dev = xyz.device
+    n_local = int(xyz.shape[0])
     multi = group is not None or (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1)
-    rank = dist.get_rank(group) if multi else 0
-    nq = max(1, min(int(samples), 64, int(xyz.shape[0]) if not multi else 64))
+    rank, src = 0, 0
+    if multi:
+        rank = dist.get_rank(group)
+        counts = torch.zeros(dist.get_world_size(group), dtype=torch.int64, device=dev)
+        counts[rank] = n_local
+        dist.all_reduce(counts, group=group)
+        holders = torch.nonzero(counts > 0).flatten()
+        if holders.numel() == 0:
+            return {"queries": 0, "violations": 0}
+        src = int(holders[0].item())
+        n_src = int(counts[src].item())
+    else:
+        if n_local == 0:
+            return {"queries": 0, "violations": 0}
+        n_src = n_local
+    nq = max(1, min(int(samples), 64, n_src))
     q = torch.zeros((nq, 3), dtype=torch.float32, device=dev)
     r = torch.zeros(nq, dtype=torch.float32, device=dev)
-    if rank == 0:
+    if rank == src:
         g = torch.Generator(device="cpu").manual_seed(seed)
-        pick = torch.randint(0, int(xyz.shape[0]), (nq,), generator=g).to(dev)
+        pick = torch.randint(0, n_local, (nq,), generator=g).to(dev)
         q.copy_(xyz[pick])
         r.copy_(result.to(torch.float32)[pick])
     if multi:
-        dist.broadcast(q, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-        dist.broadcast(r, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        gsrc = dist.get_global_rank(group, src) if group is not None else src
+        dist.broadcast(q, src=gsrc, group=group)
+        dist.broadcast(r, src=gsrc, group=group)
     less = torch.zeros(nq, dtype=torch.int64, device=dev)
     less_equal = torch.zeros(nq, dtype=torch.int64, device=dev)
     fn = lib().b200knn_count_within
     fn.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     fn.restype = C.c_int
     with torch.cuda.device(dev):
-        check(fn(xyz.data_ptr() if xyz.shape[0] else None, int(xyz.shape[0]), q.data_ptr(), nq, r.data_ptr(),
+        check(fn(xyz.data_ptr() if n_local else None, n_local, q.data_ptr(), nq, r.data_ptr(),
                  less.data_ptr(), less_equal.data_ptr(), _stream_ptr()), "count_within")
     if multi:
         dist.all_reduce(less, group=group)
         dist.all_reduce(less_equal, group=group)
-    bad = ((less >= k) | (less_equal < k)) & torch.isfinite(r)
+    exact = ((less >= k) | (less_equal < k)) & torch.isfinite(r)
+    if math.isfinite(max_radius):
+        # a result AT the cut-off says "fewer than k points strictly inside it" and nothing about ties
+        cut = torch.sqrt(torch.tensor(float(max_radius), dtype=torch.float32) ** 2).to(dev)
+        at_cut = r == cut
+        exact = torch.where(at_cut, less >= k, exact)
     # +inf results claim "fewer than k points exist": then every point is counted as strictly closer
-    bad |= torch.isinf(r) & (less >= k)
+    bad = exact | (torch.isinf(r) & (less >= k))
     return {"queries": nq, "violations": int(bad.sum().item())}
 
 
