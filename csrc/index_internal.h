@@ -5,6 +5,8 @@
 
 using namespace b200knn;
 
+namespace b200knn { int frontier_capacity(); }   // api.cu: 128, or B200KNN_QUEUE_CAP (a test knob)
+
 struct b200knn_index {
   int device = 0;
   int num_sms = 148;
@@ -29,6 +31,7 @@ struct b200knn_index {
     for (int l = 0; l < kMaxLevels; ++l) { t.boxes[l] = boxes[l]; t.count[l] = count[l]; }
     t.levels = levels;
     t.n = (int)n;
+    t.queue_cap = frontier_capacity();
     return t;
   }
   int64_t groups() const { return div_up(n, kGroup); }

@@ -27,6 +27,7 @@ struct TreeView {
   int count[kMaxLevels];        // number of boxes on level l
   int levels;                   // number of levels in use (top level has <= 32 boxes)
   int n;                        // number of points
+  int queue_cap;                // frontier entries a warp may use (<= 128; smaller only to test the overflow paths)
 };
 
 struct Bounds { float lo[3]; float hi[3]; };

@@ -142,6 +142,7 @@ int b200knn_knn_self_noalloc(const float* d_xyz, int64_t n, int k, float max_rad
     cnt = (int)div_up(cnt, kFanout);
   }
   tree.levels = levels;
+  tree.queue_cap = 128;
   if ((rc = build_leaf_boxes(pts, n, box_level[0], stream))) return rc;
   for (int l = 1; l < levels; ++l)
     if ((rc = build_upper_boxes(box_level[l - 1], tree.count[l - 1], box_level[l], stream))) return rc;

@@ -471,7 +471,7 @@ __device__ __forceinline__ void load_child_box(const TreeView& t, int level, int
 // (a, b) = this lane's child box, loaded by the caller (load_child_box) — early, so that the latency is
 // behind other work by the time the keys are needed.
 __device__ __forceinline__ void frontier_expand(int level, int base, int count, const float4& a, const float4& b,
-                                                int seed_l1, int& qcount, int& depth, GroupCtx& g) {
+                                                int seed_l1, int qcap, int& qcount, int& depth, GroupCtx& g) {
   const int lane = lane_id();
   const bool have = lane < count;
   const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
@@ -480,7 +480,7 @@ __device__ __forceinline__ void frontier_expand(int level, int base, int count, 
   const int np = __popc(mask);
   if (np == 0) return;
   const unsigned lt = (1u << lane) - 1u;
-  if (qcount + np > kQueueCap) {
+  if (qcount + np > qcap) {
     // purge entries that the shrinking radius has made irrelevant (in-place, order-preserving)
     const unsigned maxbits = __float_as_uint(g.maxR2);
     int kept = 0;
@@ -503,7 +503,7 @@ __device__ __forceinline__ void frontier_expand(int level, int base, int count, 
     qcount = kept;
     ++g.n_purge;
   }
-  if (qcount + np > kQueueCap) {
+  if (qcount + np > qcap) {
     ++g.n_fallback;
     depth = 0;
     if (lane == 0) push_frame(g.frames, 0, level, base, count);
@@ -683,7 +683,7 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         const int rem = t.count[level - 1] - idx * kFanout;
         const int count = rem < kFanout ? rem : kFanout;
         if (level == 1) run_start(idx * kFanout, count, cur_a, cur_b);
-        else frontier_expand(level - 1, idx * kFanout, count, cur_a, cur_b, seed_l1, qcount, depth, g);
+        else frontier_expand(level - 1, idx * kFanout, count, cur_a, cur_b, seed_l1, t.queue_cap, qcount, depth, g);
       }
     } else if (nx_node == kNoNode) {
       // nothing in flight and nothing left inside the radius
@@ -695,7 +695,7 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         float4 a, b;
         load_child_box(t, top_level, 0, t.count[top_level], a, b);
         if (top_level == 0) { if (seed_l1 < 0) run_start(0, t.count[0], a, b); }
-        else frontier_expand(top_level, 0, t.count[top_level], a, b, seed_l1, qcount, depth, g);
+        else frontier_expand(top_level, 0, t.count[top_level], a, b, seed_l1, t.queue_cap, qcount, depth, g);
         continue;
       }
       if constexpr (LeafOp::kBuffered) {
