@@ -10,7 +10,7 @@ NVFLAGS   := $(ARCH) -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-ffp-contract=off
 CXXFLAGS  := -O2 -std=c++17 -fPIC -ffp-contract=off -mfma -pthread -Iinclude -Icsrc
 BUILD     := build
 
-CU_SRCS   := csrc/radix_sort.cu csrc/build.cu csrc/query.cu csrc/pv.cu csrc/api.cu csrc/dist.cu csrc/noalloc.cu csrc/neighbors.cu csrc/verify.cu
+CU_SRCS   := csrc/radix_sort.cu csrc/build.cu csrc/query.cu csrc/pv.cu csrc/redist.cu csrc/api.cu csrc/dist.cu csrc/noalloc.cu csrc/neighbors.cu csrc/verify.cu
 CU_OBJS   := $(patsubst csrc/%.cu,$(BUILD)/%.o,$(CU_SRCS))
 CPP_OBJS  := $(BUILD)/cpu_engine.o
 

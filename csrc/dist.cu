@@ -462,246 +462,178 @@ int knn_prepartitioned(b200knn_dist* d, const float* d_xyz, int64_t n_local, int
   return rc;
 }
 
+// Elapsed GPU time between phases of a pipeline that the host no longer synchronises with: events recorded
+// on the stream, read after the final synchronisation.
+struct PhaseEvents {
+  static constexpr int kMax = 6;
+  cudaEvent_t ev[kMax] = {};
+  int n = 0;
+  bool on;
+  explicit PhaseEvents(bool enabled) : on(enabled) {}
+  ~PhaseEvents() { for (int i = 0; i < n; ++i) cudaEventDestroy(ev[i]); }
+  void mark(cudaStream_t s) {
+    if (!on || n >= kMax) return;
+    if (cudaEventCreate(&ev[n]) != cudaSuccess) { on = false; return; }
+    cudaEventRecord(ev[n++], s);
+  }
+  double ms(int from, int to) const {
+    float t = 0.f;
+    if (!on || to >= n || cudaEventElapsedTime(&t, ev[from], ev[to]) != cudaSuccess) return 0.0;
+    return t;
+  }
+};
+
 int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64_t global_begin, int k,
                      float max_radius, int groups_per_chunk, float* d_out, cudaStream_t stream,
                      b200knn_dist_report* rep) {
   NvtxRange range("b200knn:redistribute_pipeline");
   const int R = d->world, me = d->rank;
   int rc;
-  const double t0 = now_ms();
   PhaseTrace trace(me, stream);
-  // ---- who has what
-  struct Info { int64_t n, begin; float box[6]; };
-  Info mine{};
-  mine.n = n_local;
-  mine.begin = global_begin;
-  StreamBuf<unsigned> d_bord(stream);
-  StreamBuf<float> d_box6(stream);
+  PhaseEvents pe(rep != nullptr);
+  KNN_REQUIRE(n_local < (int64_t)0x7fffffff - 64, "redistribute: more than 2^31 points on one rank");
+
+  // ---- the histograms live in the symmetric heap (peers read them): make sure it exists
+  const size_t hist_bytes = align256(rd_hist_bytes());
+  if ((rc = ensure_heap(d, kHeapReserved + hist_bytes + 4 * 256))) return rc;
+  d->bump = kHeapReserved;
+  const size_t off_hist = d->alloc(hist_bytes);
+  pe.mark(stream);
+
+  // ---- who has what: bounds, count and first global index of every rank, gathered on the device
+  StreamBuf<unsigned> d_bord(stream), d_info(stream), d_info_all(stream);
+  StreamBuf<uint64_t> d_split(stream);
+  StreamBuf<long long> d_row(stream), d_M(stream), d_begins(stream);
+  StreamBuf<RdPlan> d_plan(stream);
   KNN_CUDA_TRY(d_bord.alloc_bytes(6 * sizeof(unsigned)));
-  KNN_CUDA_TRY(d_box6.alloc_bytes(6 * sizeof(float)));
+  KNN_CUDA_TRY(d_info.alloc_bytes(kCollWords * sizeof(unsigned)));
+  KNN_CUDA_TRY(d_info_all.alloc_bytes((size_t)kMaxRanks * kCollWords * sizeof(unsigned)));
+  KNN_CUDA_TRY(d_split.alloc_bytes(kMaxRanks * sizeof(uint64_t)));
+  KNN_CUDA_TRY(d_row.alloc_bytes(kMaxRanks * sizeof(long long)));
+  KNN_CUDA_TRY(d_M.alloc_bytes((size_t)kMaxRanks * kMaxRanks * sizeof(long long)));
+  KNN_CUDA_TRY(d_begins.alloc_bytes((kMaxRanks + 1) * sizeof(long long)));
+  KNN_CUDA_TRY(d_plan.alloc_bytes(sizeof(RdPlan)));
   if ((rc = bounds_init(d_bord, stream))) return rc;
   if ((rc = bounds_accumulate(d_xyz, 3, n_local, d_bord, stream))) return rc;
-  if ((rc = bounds_decode(d_bord, d_box6, stream))) return rc;
-  KNN_CUDA_TRY(cudaMemcpyAsync(mine.box, d_box6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  if ((rc = rd_pack_info_launch(d_bord, n_local, global_begin, d_info, stream))) return rc;
+  if (R > 1) {
+    if ((rc = device_collective(d, d_info, kRdInfoWords, kCollGather, d_info_all, stream))) return rc;
+  } else {
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_info_all, d_info, kRdInfoWords * sizeof(unsigned), cudaMemcpyDeviceToDevice, stream));
+  }
+
+  // ---- histograms of the leading Morton bits -> splitters and this rank's row of the count matrix
+  unsigned* histA = reinterpret_cast<unsigned*>(d->base + off_hist);
+  unsigned* histB = reinterpret_cast<unsigned*>(d->base + off_hist + rd_histB_offset());
+  if ((rc = rd_hist_launch(d_xyz, n_local, d_info_all, R, histA, histB, d->num_sms, stream))) return rc;
+  if ((rc = device_barrier(d, stream))) return rc;
+  RdSplitParams sp;
+  memset(&sp, 0, sizeof(sp));
+  for (int r = 0; r < R; ++r) {
+    sp.histA[r] = reinterpret_cast<const unsigned*>(d->peer[r] + off_hist);
+    sp.histB[r] = reinterpret_cast<const unsigned*>(d->peer[r] + off_hist + rd_histB_offset());
+  }
+  sp.R = R;
+  sp.rank = me;
+  sp.n_local = n_local;
+  sp.split_keys = d_split;
+  sp.row = d_row;
+  if ((rc = rd_split_launch(sp, stream))) return rc;
+  if (R > 1) {
+    if ((rc = device_collective(d, d_row, 2 * R, kCollGather, d_M, stream))) return rc;
+  } else {
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_M, d_row, sizeof(long long), cudaMemcpyDeviceToDevice, stream));
+  }
+  if ((rc = rd_plan_launch(d_M, R, me, d_plan, stream))) return rc;
+
+  // ---- the one host synchronisation: sizes
+  RdPlan plan;
+  std::vector<unsigned> info((size_t)R * kRdInfoWords);
+  KNN_CUDA_TRY(cudaMemcpyAsync(&plan, d_plan, sizeof(RdPlan), cudaMemcpyDeviceToHost, stream));
+  KNN_CUDA_TRY(cudaMemcpyAsync(info.data(), d_info_all, info.size() * sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-  trace.mark("bounds kernel + copy");
-  std::vector<Info> info(R);
-  if (d->allgather(&mine, info.data(), sizeof(Info))) { set_last_error("bootstrap allgather failed"); return -3; }
-  trace.mark("allgather info");
-  float gbox[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  trace.mark("redistribute: bounds, histograms, splitters, plan");
+  std::vector<long long> begins(R + 1);
   int64_t max_local = 0, total = 0;
   for (int r = 0; r < R; ++r) {
-    for (int a = 0; a < 3; ++a) { gbox[a] = fminf(gbox[a], info[r].box[a]); gbox[3 + a] = fmaxf(gbox[3 + a], info[r].box[3 + a]); }
-    max_local = std::max(max_local, info[r].n);
-    total += info[r].n;
-    KNN_REQUIRE(r == 0 || info[r].begin == info[r - 1].begin + info[r - 1].n,
+    const unsigned* w = info.data() + (size_t)r * kRdInfoWords;
+    const int64_t n_r = (int64_t)(((uint64_t)w[7] << 32) | w[6]), b_r = (int64_t)(((uint64_t)w[9] << 32) | w[8]);
+    KNN_REQUIRE(r == 0 || b_r == begins[0] + total,
                 "redistribute: ranks must hold consecutive slices of the global point order");
+    begins[r] = b_r;
+    max_local = std::max(max_local, n_r);
+    total += n_r;
   }
-  KNN_REQUIRE(info[0].begin + total <= (int64_t)0xffffffffll, "redistribute: global point ids must fit 32 bits");
-  KNN_CUDA_TRY(cudaMemcpyAsync(d_box6, gbox, sizeof(gbox), cudaMemcpyHostToDevice, stream));
-
-  // ---- local sort by GLOBAL Morton key
-  StreamBuf<uint64_t> keys(stream), keys_tmp(stream), d_samples(stream), d_split(stream);
-  StreamBuf<uint32_t> vals(stream), vals_tmp(stream), scratch(stream);
-  StreamBuf<int64_t> d_cut(stream);
-  const int S = 2048;
-  const int64_t na = n_local > 0 ? n_local : 1;
-  KNN_CUDA_TRY(keys.alloc_bytes(na * sizeof(uint64_t)));
-  KNN_CUDA_TRY(keys_tmp.alloc_bytes(na * sizeof(uint64_t)));
-  KNN_CUDA_TRY(vals.alloc_bytes(na * sizeof(uint32_t)));
-  KNN_CUDA_TRY(vals_tmp.alloc_bytes(na * sizeof(uint32_t)));
-  KNN_CUDA_TRY(scratch.alloc_bytes(radix_sort_scratch_bytes(na)));
-  KNN_CUDA_TRY(d_samples.alloc_bytes(S * sizeof(uint64_t)));
-  KNN_CUDA_TRY(d_split.alloc_bytes(B200KNN_MAX_RANKS * sizeof(uint64_t)));
-  KNN_CUDA_TRY(d_cut.alloc_bytes(B200KNN_MAX_RANKS * sizeof(int64_t)));
-  if ((rc = morton_keys(d_xyz, 3, n_local, d_box6, keys, vals, stream))) return rc;
-  int in_tmp = 0;
-  // Only the upper 32 bits of the key are sorted (4 radix passes instead of 8): the owners sort what they
-  // receive by their own keys anyway, and the splitters below are multiples of 2^32, so "key < splitter" only
-  // depends on the sorted prefix. 32 bits = 10.7 bits per axis = 4.3e9 cells, far finer than any rank boundary.
-  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n_local, kSplitShift, 64, stream, &in_tmp))) return rc;
-  const uint64_t* skeys = in_tmp ? keys_tmp.get() : keys.get();
-  const uint32_t* order = in_tmp ? vals_tmp.get() : vals.get();
-  trace.mark("alloc + keys + 64-bit sort");
-
-  // ---- splitters from evenly spaced local order statistics
-  std::vector<uint64_t> my_samples(S), all_samples((size_t)S * R);
-  if ((rc = sample_keys_launch(skeys, n_local, S, d_samples, stream))) return rc;
-  KNN_CUDA_TRY(cudaMemcpyAsync(my_samples.data(), d_samples, S * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream));
-  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-  trace.mark("sample kernel + copy");
-  if (d->allgather(my_samples.data(), all_samples.data(), S * sizeof(uint64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
-  trace.mark("allgather samples");
-  std::sort(all_samples.begin(), all_samples.end());
-  uint64_t split[B200KNN_MAX_RANKS] = {};
-  // Splitter j = the j/R quantile of the pooled samples, snapped to the coarsest Morton-cell
-  // boundary (of at least 2^kSplitShift keys) inside a +-0.5 % window around it. A boundary that is a whole-cell boundary keeps every
-  // rank's region a union of whole cells, so a few stray points at the end of a range cannot inflate
-  // a rank's bounding box across a neighbouring rank's region (which would defeat the culling).
-  {
-    const size_t total_s = (size_t)S * R;
-    const size_t w = std::max<size_t>(1, total_s / 200);
-    for (int j = 1; j < R; ++j) {
-      const size_t q = (size_t)j * S;
-      const uint64_t lo = all_samples[q > w ? q - w : 0];
-      const uint64_t hi = all_samples[std::min(total_s - 1, q + w)];
-      uint64_t best = (all_samples[q] >> kSplitShift) << kSplitShift;   // if the window holds no cell boundary
-      for (int b = 63; b >= kSplitShift; --b) {
-        const uint64_t cand = (hi >> b) << b;
-        if (cand >= lo && cand > 0) { best = cand; break; }
-      }
-      split[j - 1] = best;
-    }
-  }
-  std::vector<int64_t> cut(R + 1, 0);
-  if (R > 1) {
-    KNN_CUDA_TRY(cudaMemcpyAsync(d_split, split, (R - 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
-    if ((rc = lower_bounds_launch(skeys, n_local, d_split, R - 1, d_cut, stream))) return rc;
-    KNN_CUDA_TRY(cudaMemcpyAsync(cut.data() + 1, d_cut, (R - 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
-    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-  }
-  cut[R] = n_local;
-  trace.mark("host sort + splitters + cuts");
-
-  // ---- count matrix
-  std::vector<int64_t> send(R), M((size_t)R * R);
-  for (int r = 0; r < R; ++r) send[r] = cut[r + 1] - cut[r];
-  if (d->allgather(send.data(), M.data(), R * sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
-  trace.mark("allgather count matrix");
-  int64_t max_recv = 0, my_recv = 0;
-  std::vector<int64_t> recv_n(R, 0);
-  for (int dst = 0; dst < R; ++dst) {
-    for (int s = 0; s < R; ++s) recv_n[dst] += M[(size_t)s * R + dst];
-    max_recv = std::max(max_recv, recv_n[dst]);
-  }
-  my_recv = recv_n[me];
+  begins[R] = begins[0] + total;
+  KNN_REQUIRE(begins[R] <= (int64_t)0xffffffffll, "redistribute: global point ids must fit 32 bits");
+  const int64_t max_recv = plan.max_recv, my_recv = plan.my_recv;
   KNN_REQUIRE(max_recv < (int64_t)0x7fffffff - 64, "redistribute: a rank would receive more than 2^31 points");
 
-  // ---- symmetric heap: receive buffer + result landing zone + exchange slots
+  // ---- symmetric heap: histograms | receive buffer | result landing zone | exchange slots
   const PvPlan pl = pv_plan(max_recv, k, groups_per_chunk);
-  const size_t need = align256((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4)) +
+  const size_t need = hist_bytes + align256((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4)) +
                       align256((size_t)std::max<int64_t>(max_local, 1) * 8) + pv_heap_need(k, pl.Gc);
   if ((rc = ensure_heap(d, need))) return rc;
-  trace.mark("ensure heap");
   d->bump = kHeapReserved;
+  (void)d->alloc(hist_bytes);
   const size_t off_recv = d->alloc((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4));
   const size_t off_out = d->alloc((size_t)std::max<int64_t>(max_local, 1) * 8);   // (id, value) pairs land here
 
-  RedistributeParams rp;
+  RdScatterParams rp;
   memset(&rp, 0, sizeof(rp));
   rp.xyz = d_xyz;
-  rp.order = order;
   rp.n = n_local;
   rp.global_begin = global_begin;
   rp.R = R;
-  for (int r = 0; r <= R; ++r) rp.cut[r] = cut[r];
-  for (int dst = 0; dst < R; ++dst) {
-    rp.recv[dst] = reinterpret_cast<Float4*>(d->peer[dst] + off_recv);
-    int64_t off = 0;
-    for (int s = 0; s < me; ++s) off += M[(size_t)s * R + dst];
-    rp.recv_offset[dst] = off;
-  }
-  if ((rc = redistribute_launch(rp, stream))) return rc;
-  keys.release();
-  keys_tmp.release();
-  vals.release();
-  vals_tmp.release();
-  scratch.release();
-  d_samples.release();
-  d_split.release();
-  d_cut.release();
-  d_bord.release();
-  d_box6.release();
-  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-  trace.mark("scatter kernel + frees");
-  if (d->barrier()) { set_last_error("bootstrap barrier failed"); return -3; }
-  trace.mark("barrier after scatter");
-  const double t1 = now_ms();
+  rp.info_all = d_info_all;
+  rp.split_keys = d_split;
+  rp.plan = d_plan;
+  for (int dst = 0; dst < R; ++dst) rp.recv[dst] = reinterpret_cast<Float4*>(d->peer[dst] + off_recv);
+  if ((rc = rd_scatter_launch(rp, d->num_sms, stream))) return rc;
+  // everybody's points have landed (and are visible) before anybody builds on them
+  if ((rc = device_barrier(d, stream))) return rc;
+  pe.mark(stream);
+  trace.mark("redistribute: scatter + barrier");
 
   // ---- local index over the received (spatially compact) points, then the culled exchange
   IndexGuard index_guard;
   b200knn_index*& idx = index_guard.p;
   rc = b200knn_index_create_xyzw(reinterpret_cast<const float*>(d->base + off_recv), my_recv, 0, stream, &idx);
+  pe.mark(stream);
   trace.mark("index build");
-  const double t2 = now_ms();
   if (!rc) rc = run_pv(d, idx, k, max_radius, pl, stream, rep);
-  const double t3 = now_ms();
+  pe.mark(stream);
 
-  // ---- results go back to the rank that read the point: sort (id, value) by id, push each owner's
-  // run as contiguous pairs into its staging area, owner scatters locally into d_out
+  // ---- results go back to the rank that read the point: (id, value) pairs partitioned by reader, each
+  // reader's run pushed as contiguous pairs into its landing zone, the reader scatters locally into d_out
   if (!rc) {
-    const int64_t m = idx->n, ma = m > 0 ? m : 1;
-    StreamBuf<uint32_t> ids(stream), ids_tmp(stream), vals2(stream), vals2_tmp(stream), scratch2(stream);
-    StreamBuf<int64_t> d_begins(stream), d_cut2(stream);
-    KNN_CUDA_TRY(ids.alloc_bytes(ma * sizeof(uint32_t)));
-    KNN_CUDA_TRY(ids_tmp.alloc_bytes(ma * sizeof(uint32_t)));
-    KNN_CUDA_TRY(vals2.alloc_bytes(ma * sizeof(uint32_t)));
-    KNN_CUDA_TRY(vals2_tmp.alloc_bytes(ma * sizeof(uint32_t)));
-    KNN_CUDA_TRY(scratch2.alloc_bytes(radix_sort_scratch_bytes(ma)));
-    KNN_CUDA_TRY(d_begins.alloc_bytes((B200KNN_MAX_RANKS + 1) * sizeof(int64_t)));
-    KNN_CUDA_TRY(d_cut2.alloc_bytes((B200KNN_MAX_RANKS + 1) * sizeof(int64_t)));
-    if ((rc = extract_pairs_launch(idx->pts, idx->result_sorted, m, ids, vals2, stream))) return rc;
-    int in_tmp2 = 0;
-    if ((rc = radix_sort_u32(ids, vals2, ids_tmp, vals2_tmp, scratch2, m, 0, 32, stream, &in_tmp2))) return rc;
-    const uint32_t* sids = in_tmp2 ? ids_tmp.get() : ids.get();
-    const uint32_t* svals = in_tmp2 ? vals2_tmp.get() : vals2.get();
-    std::vector<int64_t> begins(R + 1), cut2(R + 1, 0);
-    for (int r = 0; r < R; ++r) begins[r] = info[r].begin;
-    begins[R] = info[R - 1].begin + info[R - 1].n;
-    KNN_CUDA_TRY(cudaMemcpyAsync(d_begins, begins.data(), (R + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
-    if ((rc = lower_bounds32_launch(sids, m, d_begins, R + 1, d_cut2, stream))) return rc;
-    KNN_CUDA_TRY(cudaMemcpyAsync(cut2.data(), d_cut2, (R + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
-    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-    trace.mark("return: pairs + 32-bit sort");
-    std::vector<int64_t> send2(R), M2((size_t)R * R);
-    for (int r = 0; r < R; ++r) send2[r] = cut2[r + 1] - cut2[r];
-    if (d->allgather(send2.data(), M2.data(), R * sizeof(int64_t))) { set_last_error("bootstrap allgather failed"); return -3; }
-    trace.mark("return: allgather matrix");
-    PushPairsParams pp;
-    memset(&pp, 0, sizeof(pp));
-    pp.ids = sids;
-    pp.vals = svals;
-    pp.n = m;
-    pp.R = R;
-    for (int r = 0; r <= R; ++r) pp.cut[r] = cut2[r];
-    for (int o = 0; o < R; ++o) {
-      pp.dst[o] = reinterpret_cast<uint2*>(d->peer[o] + off_out);
-      int64_t off = 0;
-      for (int s2 = 0; s2 < me; ++s2) off += M2[(size_t)s2 * R + o];
-      pp.dst_offset[o] = off;
-    }
-    if ((rc = push_pairs_launch(pp, stream))) return rc;
-    ids.release();
-    ids_tmp.release();
-    vals2.release();
-    vals2_tmp.release();
-    scratch2.release();
-    d_begins.release();
-    d_cut2.release();
+    KNN_CUDA_TRY(cudaMemcpyAsync(d_begins, begins.data(), (size_t)(R + 1) * sizeof(long long), cudaMemcpyHostToDevice, stream));
+    RdReturnParams qp;
+    memset(&qp, 0, sizeof(qp));
+    qp.pts = idx->pts;
+    qp.res = idx->result_sorted;
+    qp.n = idx->n;
+    qp.R = R;
+    qp.begins = d_begins;
+    qp.plan = d_plan;
+    for (int o = 0; o < R; ++o) qp.dst[o] = d->peer[o] + off_out;
+    rc = rd_return_launch(qp, d->num_sms, stream);
   }
+  if (!rc) rc = device_barrier(d, stream);
+  if (!rc && n_local > 0) rc = scatter_pairs_launch(d->base + off_out, n_local, global_begin, d_out, stream);
+  pe.mark(stream);
+  // No fence is needed before the next call: a peer writes into this rank's buffers only behind a device
+  // barrier or collective of that next call, which this rank joins after everything above (stream order).
   if (!rc) {
     cudaError_t e = cudaStreamSynchronize(stream);
     if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
   }
-  trace.mark("return: push pairs");
-  if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
-  trace.mark("return: barrier");
-  if (!rc && n_local > 0) {
-    rc = scatter_pairs_launch(d->base + off_out, n_local, global_begin, d_out, stream);
-    if (!rc) {
-      cudaError_t e = cudaStreamSynchronize(stream);
-      if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
-    }
-  }
-  trace.mark("return: local scatter");
-  // nobody may start overwriting the landing zone (next call) before everyone has copied out
-  if (!rc && d->barrier()) { set_last_error("bootstrap barrier failed"); rc = -3; }
-  trace.mark("return: final barrier");
+  trace.mark("return: push pairs + barrier + local scatter");
   if (rep) {
-    rep->ms_redistribute += t1 - t0;
-    rep->ms_build += t2 - t1;
-    rep->ms_query += t3 - t2;
-    rep->ms_return += now_ms() - t3;
+    rep->ms_redistribute += pe.ms(0, 1);
+    rep->ms_build += pe.ms(1, 2);
+    rep->ms_query += pe.ms(2, 3);
+    rep->ms_return += pe.ms(3, 4);
     rep->points_after_redistribute = my_recv;
   }
   return rc;

@@ -216,6 +216,51 @@ int sample_keys_launch(const uint64_t* sorted_keys, int64_t n, int samples, uint
 int lower_bounds_launch(const uint64_t* sorted_keys, int64_t n, const uint64_t* splitters, int count,
                         int64_t* out, cudaStream_t stream);
 
+// ---------------- sort-free redistribution (redist.cu) ----------------
+constexpr int kRdInfoWords = 10;   // per rank: bounds (6 order-preserving uints), n (2 words), global begin (2 words)
+struct RdPlan {                    // device-resident; the host reads my_recv / max_recv once
+  long long recv_offset[kMaxRanks];      // where this rank's run starts inside owner d's receive buffer (points)
+  long long ret_offset[kMaxRanks];       // where this rank's run starts inside reader o's landing zone (pairs)
+  long long my_recv, max_recv;
+  unsigned long long cursor[kMaxRanks];      // running positions inside those runs
+  unsigned long long ret_cursor[kMaxRanks];
+};
+struct RdSplitParams {
+  const unsigned* histA[kMaxRanks];      // every rank's histograms (peer pointers)
+  const unsigned* histB[kMaxRanks];
+  int R, rank;
+  long long n_local;
+  uint64_t* split_keys;                  // out [R-1]: owner d takes keys in [split[d-1], split[d])
+  long long* row;                        // out [R]: points this rank sends to each owner
+};
+struct RdScatterParams {
+  const float* xyz;
+  int64_t n, global_begin;
+  int R;
+  const unsigned* info_all;              // [R][kRdInfoWords]
+  const uint64_t* split_keys;
+  RdPlan* plan;
+  Float4* recv[kMaxRanks];               // owners' receive buffers (peer pointers)
+};
+struct RdReturnParams {
+  const Float4* pts;                     // local sorted points, .w = global id
+  const float* res;                      // their k-th distances
+  int64_t n;
+  int R;
+  const long long* begins;               // [R+1] global id ranges of the readers
+  RdPlan* plan;
+  void* dst[kMaxRanks];                  // readers' landing zones of (id, value) pairs (peer pointers)
+};
+size_t rd_hist_bytes();                  // histogram A followed by histogram B
+size_t rd_histB_offset();
+int rd_pack_info_launch(const unsigned* d_bounds_ord, int64_t n, int64_t begin, unsigned* d_out, cudaStream_t stream);
+int rd_hist_launch(const float* d_xyz, int64_t n, const unsigned* d_info_all, int R, unsigned* histA, unsigned* histB,
+                   int num_sms, cudaStream_t stream);
+int rd_split_launch(const RdSplitParams& p, cudaStream_t stream);
+int rd_plan_launch(const long long* d_M, int R, int rank, RdPlan* d_plan, cudaStream_t stream);
+int rd_scatter_launch(const RdScatterParams& p, int num_sms, cudaStream_t stream);
+int rd_return_launch(const RdReturnParams& p, int num_sms, cudaStream_t stream);
+
 // out[id(i)] = sorted_result[i]  (id taken from pts[i].w, minus id_offset)
 int scatter_results(const Float4* sorted_pts, const float* sorted_result, int64_t n,
                     uint32_t id_offset, float* out, cudaStream_t stream);

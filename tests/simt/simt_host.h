@@ -16,6 +16,7 @@
 // code, launch geometry, and the flag protocols between ranks as far as a sequentially consistent
 // x86 host exercises them. What it cannot check: the GPU memory model, performance.
 #pragma once
+#include <time.h>
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -210,6 +211,14 @@ inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyK
 inline cudaError_t cudaMemset(void* d, int v, size_t n) { if (n) memset(d, v, n); return cudaSuccess; }
 inline cudaError_t cudaMemsetAsync(void* d, int v, size_t n, cudaStream_t = nullptr) { if (n) memset(d, v, n); return cudaSuccess; }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
+// events: everything runs synchronously here, so an event is a host timestamp
+struct simt_event { double ms; };
+inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = new simt_event{0.0}; return cudaSuccess; }
+inline cudaError_t cudaEventDestroy(cudaEvent_t e) { delete e; return cudaSuccess; }
+inline cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t = nullptr) {
+  timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); e->ms = ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; return cudaSuccess;
+}
+inline cudaError_t cudaEventElapsedTime(float* out, cudaEvent_t a, cudaEvent_t b) { *out = (float)(b->ms - a->ms); return cudaSuccess; }
 inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
 inline cudaError_t cudaGetDevice(int* d) { *d = 0; return cudaSuccess; }
 inline cudaError_t cudaSetDevice(int) { return cudaSuccess; }
