@@ -140,7 +140,8 @@ static_assert(2 * kMaxRanks * sizeof(unsigned) <= kCollDataOff - kCollFlagsOff, 
 static_assert(kHeapReserved % 256 == 0, "reserved area keeps the 256-byte alignment of what follows");
 
 size_t pv_heap_need(int k, int Gc) {
-  return kHeapReserved + 2 * align256((size_t)Gc * pv_slot_bytes(k)) + 4 * 256;
+  return kHeapReserved + 2 * align256((size_t)Gc * pv_slot_bytes(k)) + 6 * 256 +
+         align256((size_t)kMaxRanks * kRegionBoxes * sizeof(Box)) + align256((size_t)kMaxRanks * sizeof(RegionHead));
 }
 
 // Device-side barrier over all ranks, enqueued on `stream` (replaces MPI_Barrier,
@@ -210,132 +211,36 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   NvtxRange range("b200knn:culled_exchange");
   const int R = d->world, me = d->rank;
   PhaseTrace trace(me, stream);
-  // everyone's region: the boxes of the deepest tree level with at most kRegionBoxes nodes, plus the
-  // overall box for a quick reject. One box per rank is far too coarse: a few stray points at the end
-  // of a Morton range, or the tails of a Gaussian blob, stretch it across the neighbours' regions.
-  struct RegionHead { int32_t count; int32_t pad; float box[6]; };
-  const size_t region_bytes = sizeof(RegionHead) + (size_t)kRegionBoxes * sizeof(Box);
-  std::vector<char> my_region(region_bytes, 0), all_regions(region_bytes * R);
-  {
-    RegionHead* head = reinterpret_cast<RegionHead*>(my_region.data());
-    memcpy(head->box, idx->h_bounds, sizeof(head->box));
-    if (idx->levels > 0 && R > 1) {
-      // Adaptive description: start from the top level and keep splitting the box with the largest
-      // surface into its parts until kRegionBoxes boxes are in use: inner node -> its <= 32 children,
-      // leaf -> its points cut in two at the largest gap along the widest axis, and such point sets
-      // again. A fixed tree level is not enough: a node (even a single leaf) that straddles a jump of
-      // the Z-curve or the gap between two clusters has one huge box that swallows other ranks' dense
-      // regions and would send all of their groups here for nothing. Levels >= 1 are copied to the host
-      // up front (<= 2 MB); leaf boxes and points are fetched on demand for the few nodes that need it.
-      const int lfetch = idx->levels > 1 ? 1 : 0;
-      std::vector<std::vector<Box>> lv(idx->levels);
-      for (int l = lfetch; l < idx->levels; ++l) {
-        lv[l].resize(idx->count[l]);
-        KNN_CUDA_TRY(cudaMemcpyAsync(lv[l].data(), idx->boxes[l], (size_t)idx->count[l] * sizeof(Box),
-                                     cudaMemcpyDeviceToHost, stream));
-      }
-      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-      struct Item { double area; int level; int index; Box box; };     // level -1: explicit point set `index`
-      std::vector<std::vector<Float4>> point_sets;
-      auto area_of = [](const Box& b) {
-        const double ex = (double)b.hix - b.lox, ey = (double)b.hiy - b.loy, ez = (double)b.hiz - b.loz;
-        return ex * ey + ey * ez + ez * ex + 1e-30 * (ex + ey + ez);    // half surface area; flat boxes still rank
-      };
-      auto box_of_points = [](const std::vector<Float4>& ps) {
-        Box b;
-        b.lox = b.loy = b.loz = INFINITY; b.hix = b.hiy = b.hiz = -INFINITY; b.cnt_bits = 0.f; b.pad = 0.f;
-        for (const Float4& q : ps) {
-          b.lox = fminf(b.lox, q.x); b.loy = fminf(b.loy, q.y); b.loz = fminf(b.loz, q.z);
-          b.hix = fmaxf(b.hix, q.x); b.hiy = fmaxf(b.hiy, q.y); b.hiz = fmaxf(b.hiz, q.z);
-        }
-        return b;
-      };
-      auto smaller = [](const Item& x, const Item& y) { return x.area < y.area; };
-      std::vector<Item> heap, done;
-      const int top = idx->levels - 1;
-      if (top >= lfetch) {
-        for (int i = 0; i < idx->count[top]; ++i) heap.push_back({area_of(lv[top][i]), top, i, lv[top][i]});
-      } else {   // single-level tree whose leaves were not fetched: cannot happen (lfetch == 0 then)
-        KNN_REQUIRE(false, "internal: region levels");
-      }
-      std::make_heap(heap.begin(), heap.end(), smaller);
-      std::vector<Box> kids(kFanout);
-      while (!heap.empty()) {
-        std::pop_heap(heap.begin(), heap.end(), smaller);
-        const Item it = heap.back();
-        heap.pop_back();
-        const int used = (int)(heap.size() + done.size());
-        if (it.level >= 1) {
-          const int c0 = it.index * kFanout;
-          const int nc = std::min(kFanout, idx->count[it.level - 1] - c0);
-          if (used + nc > kRegionBoxes) { done.push_back(it); continue; }
-          const Box* src = nullptr;
-          if (it.level - 1 >= lfetch) src = lv[it.level - 1].data() + c0;
-          else {
-            KNN_CUDA_TRY(cudaMemcpy(kids.data(), idx->boxes[0] + c0, (size_t)nc * sizeof(Box), cudaMemcpyDeviceToHost));
-            src = kids.data();
-          }
-          for (int c = 0; c < nc; ++c) {
-            heap.push_back({area_of(src[c]), it.level - 1, c0 + c, src[c]});
-            std::push_heap(heap.begin(), heap.end(), smaller);
-          }
-          continue;
-        }
-        // a leaf or an explicit point set: cut at the largest gap along the widest axis
-        if (used + 2 > kRegionBoxes) { done.push_back(it); continue; }
-        std::vector<Float4> ps;
-        if (it.level == 0) {
-          const int64_t first = (int64_t)it.index * kGroup;
-          const int cnt = (int)std::min<int64_t>(kGroup, idx->n - first);
-          ps.resize(cnt);
-          KNN_CUDA_TRY(cudaMemcpy(ps.data(), idx->pts + first, (size_t)cnt * sizeof(Float4), cudaMemcpyDeviceToHost));
-        } else {
-          ps = point_sets[it.index];
-        }
-        if (ps.size() < 2) { done.push_back(it); continue; }
-        const float ex = it.box.hix - it.box.lox, ey = it.box.hiy - it.box.loy, ez = it.box.hiz - it.box.loz;
-        const int axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
-        auto coord = [axis](const Float4& q) { return axis == 0 ? q.x : (axis == 1 ? q.y : q.z); };
-        std::sort(ps.begin(), ps.end(), [&](const Float4& x, const Float4& y) { return coord(x) < coord(y); });
-        size_t cut = 1;
-        float best_gap = -1.f;
-        for (size_t i = 1; i < ps.size(); ++i) {
-          const float gap = coord(ps[i]) - coord(ps[i - 1]);
-          if (gap > best_gap) { best_gap = gap; cut = i; }
-        }
-        if (!(best_gap > 0.f)) { done.push_back(it); continue; }      // all points identical along every axis
-        for (int half = 0; half < 2; ++half) {
-          std::vector<Float4> part(half == 0 ? ps.begin() : ps.begin() + cut, half == 0 ? ps.begin() + cut : ps.end());
-          const Box pb = box_of_points(part);
-          point_sets.push_back(std::move(part));
-          heap.push_back({area_of(pb), -1, (int)point_sets.size() - 1, pb});
-          std::push_heap(heap.begin(), heap.end(), smaller);
-        }
-      }
-      head->count = (int32_t)done.size();
-      Box* out_boxes = reinterpret_cast<Box*>(my_region.data() + sizeof(RegionHead));
-      for (size_t i = 0; i < done.size(); ++i) out_boxes[i] = done[i].box;
-    }
-    trace.mark("exchange: region boxes (host)");
-    if (d->allgather(my_region.data(), all_regions.data(), (int64_t)region_bytes)) { set_last_error("bootstrap allgather failed"); return -3; }
-    trace.mark("exchange: allgather regions");
-  }
-  StreamBuf<Box> d_regions(stream);
-  KNN_CUDA_TRY(d_regions.alloc_bytes((size_t)R * kRegionBoxes * sizeof(Box)));
-  std::vector<RegionHead> heads(R);
-  for (int r = 0; r < R; ++r) {
-    memcpy(&heads[r], all_regions.data() + (size_t)r * region_bytes, sizeof(RegionHead));
-    KNN_CUDA_TRY(cudaMemcpyAsync(d_regions + (size_t)r * kRegionBoxes, all_regions.data() + (size_t)r * region_bytes + sizeof(RegionHead),
-                                 (size_t)kRegionBoxes * sizeof(Box), cudaMemcpyHostToDevice, stream));
-  }
-  if (me == 0 && getenv("B200KNN_DEBUG_REGIONS")) {
+  // everyone's region (pv.cu, region_build_kernel): built on the device next to the tree and stored into
+  // every rank's table by peer stores; a device barrier makes the tables complete. No host collective.
+  const size_t off_regions = d->alloc((size_t)kMaxRanks * kRegionBoxes * sizeof(Box));
+  const size_t off_heads = d->alloc((size_t)kMaxRanks * sizeof(RegionHead));
+  KNN_REQUIRE(d->bump <= d->bytes, "symmetric heap too small (internal sizing error)");
+  const Box* d_regions = reinterpret_cast<const Box*>(d->base + off_regions);
+  const RegionHead* d_heads = reinterpret_cast<const RegionHead*>(d->base + off_heads);
+  if (R > 1) {
+    RegionBuildParams rb;
+    memset(&rb, 0, sizeof(rb));
+    rb.tree = idx->view();
+    memcpy(rb.overall, idx->h_bounds, sizeof(rb.overall));
+    rb.R = R;
+    rb.rank = me;
     for (int r = 0; r < R; ++r) {
-      const Box* bx = reinterpret_cast<const Box*>(all_regions.data() + (size_t)r * region_bytes + sizeof(RegionHead));
-      fprintf(stderr, "[regions] rank %d: %d boxes, overall (%g %g %g)-(%g %g %g)\n", r, heads[r].count, heads[r].box[0],
-              heads[r].box[1], heads[r].box[2], heads[r].box[3], heads[r].box[4], heads[r].box[5]);
-      for (int i = 0; i < heads[r].count && i < 6; ++i)
-        fprintf(stderr, "   box %d: (%g %g %g)-(%g %g %g)\n", i, bx[i].lox, bx[i].loy, bx[i].loz, bx[i].hix, bx[i].hiy, bx[i].hiz);
+      rb.tables[r] = reinterpret_cast<Box*>(d->peer[r] + off_regions);
+      rb.heads[r] = reinterpret_cast<RegionHead*>(d->peer[r] + off_heads);
     }
+    int rcb;
+    if ((rcb = region_build_launch(rb, stream))) return rcb;
+    if ((rcb = device_barrier(d, stream))) return rcb;
+    if (me == 0 && getenv("B200KNN_DEBUG_REGIONS")) {
+      std::vector<RegionHead> heads(R);
+      KNN_CUDA_TRY(cudaMemcpyAsync(heads.data(), d_heads, (size_t)R * sizeof(RegionHead), cudaMemcpyDeviceToHost, stream));
+      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      for (int r = 0; r < R; ++r)
+        fprintf(stderr, "[regions] rank %d: %d boxes, overall (%g %g %g)-(%g %g %g)\n", r, heads[r].count, heads[r].box[0],
+                heads[r].box[1], heads[r].box[2], heads[r].box[3], heads[r].box[4], heads[r].box[5]);
+    }
+    trace.mark("exchange: region boxes (device) + barrier");
   }
 
   const size_t slot = pv_slot_bytes(k);
@@ -354,10 +259,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.R = R;
   p.rank = me;
   p.region_boxes = d_regions;
-  for (int r = 0; r < R; ++r) {
-    p.region_count[r] = heads[r].count;
-    for (int a = 0; a < 6; ++a) p.rank_box[r][a] = heads[r].box[a];
-  }
+  p.region_heads = d_heads;
   p.home_queries = idx->pts;
   p.home_n = idx->n;
   p.home_is_tree = 1;
@@ -416,9 +318,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     const double tr0 = now_ms();
     for (int j = 1; j < R; ++j) {
       const int dst = (me + j) % R, src = (me - j + R) % R;
-      if ((rc = pv_push_launch(p.pending, p.pending_count, k, d_regions + (size_t)dst * kRegionBoxes, heads[dst].count,
-                               heads[dst].box, d->peer[dst] + off_inbox,
-                               out_count, idx->num_sms, stream))) return rc;
+      if ((rc = pv_push_launch(p.pending, p.pending_count, k, d_regions + (size_t)dst * kRegionBoxes, d_heads + dst,
+                               d->peer[dst] + off_inbox, out_count, idx->num_sms, stream))) return rc;
       if ((rc = pv_publish_launch(out_count, reinterpret_cast<int*>(d->peer[dst] + off_icount), stream))) return rc;
       // round fences are device-side sequence-flag barriers, enqueued on the stream: the host does
       // not synchronise between push, serve and the next round
@@ -433,7 +334,6 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     if (rep) { KNN_CUDA_TRY(cudaStreamSynchronize(stream)); rep->ms_rounds += now_ms() - tr0; }
     trace.mark("exchange: rounds + final");
   }
-  d_regions.release();
   if (d_votes) d_votes.release();
   return 0;
 }
@@ -603,6 +503,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   trace.mark("index build");
   if (!rc) rc = run_pv(d, idx, k, max_radius, pl, stream, rep);
   pe.mark(stream);
+  trace.mark("culled exchange (total)");
 
   // ---- results go back to the rank that read the point: (id, value) pairs partitioned by reader, each
   // reader's run pushed as contiguous pairs into its landing zone, the reader scatters locally into d_out
@@ -619,7 +520,9 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     for (int o = 0; o < R; ++o) qp.dst[o] = d->peer[o] + off_out;
     rc = rd_return_launch(qp, d->num_sms, stream);
   }
+  trace.mark("return: push pairs");
   if (!rc) rc = device_barrier(d, stream);
+  trace.mark("return: barrier");
   if (!rc && n_local > 0) rc = scatter_pairs_launch(d->base + off_out, n_local, global_begin, d_out, stream);
   pe.mark(stream);
   // No fence is needed before the next call: a peer writes into this rank's buffers only behind a device
@@ -628,7 +531,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     cudaError_t e = cudaStreamSynchronize(stream);
     if (e != cudaSuccess) { set_last_error(cudaGetErrorString(e)); rc = (int)e; }
   }
-  trace.mark("return: push pairs + barrier + local scatter");
+  trace.mark("return: local scatter");
   if (rep) {
     rep->ms_redistribute += pe.ms(0, 1);
     rep->ms_build += pe.ms(1, 2);

@@ -122,6 +122,8 @@ constexpr int kRegionBoxes = 2048;
 // A slot carries one group: heap [k][32] floats, positions [32] float4, meta [4] int32.
 KNN_HD size_t pv_slot_bytes(int k) { return (size_t)k * 128 + 512 + 16; }
 
+struct RegionHead { int count; int pad; float box[6]; };   // 32 bytes
+
 struct PvMainParams {
   TreeView tree;
   int k;
@@ -130,10 +132,9 @@ struct PvMainParams {
   int fill;                    // as RingParams::fill, LOCAL phase only
   float* global_heaps;         // set by pv_main_launch when k exceeds the shared-memory heap
   int R, rank;
-  const Box* region_boxes;     // [R][kRegionBoxes]: every rank's region = the boxes of the deepest tree
-                               // level that has at most kRegionBoxes nodes
-  int region_count[kMaxRanks]; // boxes in use per rank (0 for an empty rank)
-  float rank_box[kMaxRanks][6];// every rank's overall bounding box (quick reject)
+  const Box* region_boxes;     // [R][kRegionBoxes]: every rank's region, a cover of its points by up to
+                               // kRegionBoxes boxes (region_build_kernel), written here by that rank
+  const RegionHead* region_heads;   // [R]: boxes in use (0 for an empty rank) + overall bounding box (quick reject)
   // LOCAL
   const Float4* home_queries;
   int64_t home_n;
@@ -151,8 +152,21 @@ struct PvMainParams {
   unsigned long long* stats;
 };
 int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream);
-int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, int dst_box_count,
-                   const float* dst_rank_box6, char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
+int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, const RegionHead* dst_head,
+                   char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
+
+// One CTA describes this rank's points by up to kRegionBoxes boxes and stores the description into every
+// rank's region table (peer stores): start from the tree's top level and keep splitting the box with the
+// largest surface — an inner node into its children, a leaf (or a subset of a leaf's points) in two at the
+// largest gap along its widest axis.
+struct RegionBuildParams {
+  TreeView tree;
+  float overall[6];             // this rank's bounding box
+  int R, rank;
+  Box* tables[kMaxRanks];       // every rank's [R][kRegionBoxes] table (peer pointers)
+  RegionHead* heads[kMaxRanks]; // every rank's [R] heads
+};
+int region_build_launch(const RegionBuildParams& p, cudaStream_t stream);
 int pv_publish_launch(const int* out_count, int* peer_inbox_count, cudaStream_t stream);
 int pv_final_launch(const char* pending, const int* pending_count, int k, float* result_sorted, int num_sms,
                     cudaStream_t stream);

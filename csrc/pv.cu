@@ -111,14 +111,17 @@ pv_main_kernel_t(const PvMainParams p) {
         for (int s = 0; s < p.R && !need; ++s) {
           if (s == p.rank) continue;
           // quick reject against the rank's overall box (warp-uniform)
-          if (!(box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, p.rank_box[s][0], p.rank_box[s][1],
-                           p.rank_box[s][2], p.rank_box[s][3], p.rank_box[s][4], p.rank_box[s][5]) < g.maxR2))
+          const int region_count = __ldg(&p.region_heads[s].count);
+          const float* ob = p.region_heads[s].box;
+          if (region_count == 0 ||
+              !(box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, __ldg(ob), __ldg(ob + 1), __ldg(ob + 2), __ldg(ob + 3),
+                           __ldg(ob + 4), __ldg(ob + 5)) < g.maxR2))
             continue;
           const Box* rb = p.region_boxes + (size_t)s * kRegionBoxes;
-          for (int base = 0; base < p.region_count[s] && !need; base += 32) {
+          for (int base = 0; base < region_count && !need; base += 32) {
             bool hit = false;
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-            if (base + lane < p.region_count[s]) {
+            if (base + lane < region_count) {
               const float4* bp = reinterpret_cast<const float4*>(rb + base + lane);
               a = __ldg(bp);
               b = __ldg(bp + 1);
@@ -167,10 +170,12 @@ pv_main_kernel_t(const PvMainParams p) {
 // the whole slot into the next free slot of the destination GPU's inbox.
 __global__ void __launch_bounds__(256)
 pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending_count, int k,
-               const Box* __restrict__ dst_boxes, int dst_box_count,
-               float rlx, float rly, float rlz, float rhx, float rhy, float rhz,
+               const Box* __restrict__ dst_boxes, const RegionHead* __restrict__ dst_head,
                char* __restrict__ peer_inbox, int* __restrict__ out_count) {
   const int lane = lane_id();
+  const int dst_box_count = dst_head->count;
+  const float rlx = dst_head->box[0], rly = dst_head->box[1], rlz = dst_head->box[2];
+  const float rhx = dst_head->box[3], rhy = dst_head->box[4], rhz = dst_head->box[5];
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const size_t slot_bytes = pv_slot_bytes(k);
   const int total = *pending_count;
@@ -391,6 +396,177 @@ __global__ void lower_bounds_kernel(const uint64_t* __restrict__ sorted_keys, in
   out[j] = lo;
 }
 
+// ---- region description -------------------------------------------------------------------------------
+// A rank's REGION is what the others test a group's ball against to decide whether the group must visit.
+// One box per rank, or any fixed tree level, is defeated by a single node that straddles a jump of the
+// Z-curve or the gap between two clusters: its box covers everything in between and attracts every group
+// of the ranks in between. So the cover is adaptive: up to kRegionBoxes boxes, grown from the tree's top
+// level by always splitting the box with the largest surface. Round 1 did this on the host with a blocking
+// copy per opened node and shipped the result through a bootstrap all-gather; here one CTA does it next to
+// the data and stores the result straight into every rank's table.
+constexpr int kRegionThreads = 1024;
+
+struct RegionItem {
+  float key;          // half surface area; < 0: cannot be split any further
+  int level;          // >= 1 inner node, 0 leaf, -1 subset of a leaf's points (mask)
+  int index;          // node index (for a subset: the leaf)
+  unsigned mask;      // subset: which of the leaf's points
+};
+
+__device__ __forceinline__ float region_area(float lx, float ly, float lz, float hx, float hy, float hz) {
+  const float ex = hx - lx, ey = hy - ly, ez = hz - lz;
+  return ex * ey + ey * ez + ez * ex + 1e-30f * (ex + ey + ez);     // flat boxes still rank
+}
+
+__global__ void __launch_bounds__(kRegionThreads)
+region_build_kernel(const RegionBuildParams p) {
+  extern __shared__ __align__(16) unsigned char region_smem[];
+  RegionItem* items = reinterpret_cast<RegionItem*>(region_smem);                       // [kRegionBoxes]
+  float4* lo = reinterpret_cast<float4*>(items + kRegionBoxes);                          // [kRegionBoxes]
+  float4* hi = lo + kRegionBoxes;
+  __shared__ float s_key[32];
+  __shared__ int s_idx[32];
+  __shared__ int s_count, s_best;
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  const TreeView& tr = p.tree;
+
+  if (t == 0) s_count = 0;
+  __syncthreads();
+  if (tr.levels > 0 && tr.n > 0) {
+    const int top = tr.levels - 1;
+    if (t < tr.count[top]) {
+      const float4* bp = reinterpret_cast<const float4*>(tr.boxes[top]) + 2 * (size_t)t;
+      const float4 a = bp[0], b = bp[1];
+      lo[t] = a; hi[t] = b;
+      items[t].key = region_area(a.x, a.y, a.z, b.x, b.y, b.z);
+      items[t].level = top; items[t].index = t; items[t].mask = 0xffffffffu;
+    }
+    if (t == 0) s_count = tr.count[top];
+  }
+  __syncthreads();
+
+  for (;;) {
+    const int count = s_count;
+    // ---- the splittable item with the largest surface
+    float bk = -1.f;
+    int bi = -1;
+    for (int i = t; i < count; i += kRegionThreads) {
+      const float kx = items[i].key;
+      if (kx > bk) { bk = kx; bi = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ok = __shfl_xor_sync(kFullMask, bk, o);
+      const int oi = __shfl_xor_sync(kFullMask, bi, o);
+      if (ok > bk || (ok == bk && oi >= 0 && (bi < 0 || oi < bi))) { bk = ok; bi = oi; }
+    }
+    if (lane == 0) { s_key[w] = bk; s_idx[w] = bi; }
+    __syncthreads();
+    if (w == 0) {
+      bk = s_key[lane]; bi = s_idx[lane];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ok = __shfl_xor_sync(kFullMask, bk, o);
+        const int oi = __shfl_xor_sync(kFullMask, bi, o);
+        if (ok > bk || (ok == bk && oi >= 0 && (bi < 0 || oi < bi))) { bk = ok; bi = oi; }
+      }
+      if (lane == 0) s_best = bk >= 0.f ? bi : -1;
+    }
+    __syncthreads();
+    const int best = s_best;
+    if (best < 0) break;                                   // nothing left that can be split
+    const RegionItem it = items[best];
+    if (it.level >= 1) {
+      const int c0 = it.index * kFanout;
+      const int rem = tr.count[it.level - 1] - c0;
+      const int nc = rem < kFanout ? rem : kFanout;
+      if (count - 1 + nc > kRegionBoxes) break;            // no room for its children: the cover is done
+      __syncthreads();
+      if (t < nc) {
+        const float4* bp = reinterpret_cast<const float4*>(tr.boxes[it.level - 1]) + 2 * (size_t)(c0 + t);
+        const float4 a = bp[0], b = bp[1];
+        const int slot = t == 0 ? best : count + t - 1;
+        lo[slot] = a; hi[slot] = b;
+        items[slot].key = region_area(a.x, a.y, a.z, b.x, b.y, b.z);
+        items[slot].level = it.level - 1; items[slot].index = c0 + t; items[slot].mask = 0xffffffffu;
+      }
+      if (t == 0) s_count = count + nc - 1;
+      __syncthreads();
+      continue;
+    }
+    // ---- a leaf or a subset of one: cut at the largest gap along the widest axis (warp 0)
+    if (count + 1 > kRegionBoxes) break;
+    __syncthreads();
+    if (w == 0) {
+      const int64_t first = (int64_t)it.index * kGroup;
+      const int64_t remn = (int64_t)tr.n - first;
+      const int cnt = remn < kGroup ? (int)remn : kGroup;
+      const bool valid = lane < cnt && ((it.mask >> lane) & 1u);
+      float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (valid) q = reinterpret_cast<const float4*>(tr.pts)[first + lane];
+      const float4 a = lo[best], b = hi[best];
+      const float ex = b.x - a.x, ey = b.y - a.y, ez = b.z - a.z;
+      const int axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
+      const float c = valid ? (axis == 0 ? q.x : (axis == 1 ? q.y : q.z)) : INFINITY;
+      float succ = INFINITY;
+      for (int j = 0; j < 32; ++j) {
+        const float cj = __shfl_sync(kFullMask, c, j);
+        if (cj > c) succ = fminf(succ, cj);
+      }
+      const float gap = (valid && succ < INFINITY) ? succ - c : 0.f;
+      const unsigned gbits = __float_as_uint(gap);
+      const unsigned gmax = __reduce_max_sync(kFullMask, gbits);
+      const unsigned vm = __ballot_sync(kFullMask, valid);
+      if (__popc(vm) < 2 || !(__uint_as_float(gmax) > 0.f)) {
+        if (lane == 0) items[best].key = -1.f;             // a single point, or all points identical
+      } else {
+        const int wl = __ffs(__ballot_sync(kFullMask, valid && gbits == gmax)) - 1;
+        const float cut = __shfl_sync(kFullMask, c, wl);
+        const unsigned left = __ballot_sync(kFullMask, valid && c <= cut);
+        const unsigned right = vm & ~left;
+        for (int half = 0; half < 2; ++half) {
+          const unsigned m = half == 0 ? left : right;
+          const bool in = (m >> lane) & 1u;
+          float lx = in ? q.x : INFINITY, ly = in ? q.y : INFINITY, lz = in ? q.z : INFINITY;
+          float hx = in ? q.x : -INFINITY, hy = in ? q.y : -INFINITY, hz = in ? q.z : -INFINITY;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            lx = fminf(lx, __shfl_xor_sync(kFullMask, lx, o)); ly = fminf(ly, __shfl_xor_sync(kFullMask, ly, o));
+            lz = fminf(lz, __shfl_xor_sync(kFullMask, lz, o)); hx = fmaxf(hx, __shfl_xor_sync(kFullMask, hx, o));
+            hy = fmaxf(hy, __shfl_xor_sync(kFullMask, hy, o)); hz = fmaxf(hz, __shfl_xor_sync(kFullMask, hz, o));
+          }
+          if (lane == 0) {
+            const int slot = half == 0 ? best : count;
+            lo[slot] = make_float4(lx, ly, lz, 0.f);
+            hi[slot] = make_float4(hx, hy, hz, 0.f);
+            items[slot].key = __popc(m) >= 2 ? region_area(lx, ly, lz, hx, hy, hz) : -1.f;
+            items[slot].level = -1; items[slot].index = it.index; items[slot].mask = m;
+          }
+        }
+        if (lane == 0) s_count = count + 1;
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---- publish: this rank's row of every rank's table
+  const int count = s_count;
+  for (int r = 0; r < p.R; ++r) {
+    float4* dst = reinterpret_cast<float4*>(p.tables[r] + (size_t)p.rank * kRegionBoxes);
+    for (int i = t; i < count; i += kRegionThreads) {
+      const float4 a = lo[i], b = hi[i];
+      dst[2 * i] = make_float4(a.x, a.y, a.z, 0.f);
+      dst[2 * i + 1] = make_float4(b.x, b.y, b.z, 0.f);
+    }
+    if (t == 0) {
+      RegionHead h;
+      h.count = count; h.pad = 0;
+      for (int a = 0; a < 6; ++a) h.box[a] = p.overall[a];
+      p.heads[r][p.rank] = h;
+    }
+  }
+}
+
 inline int blocks_for(int64_t n, int block) { return (int)div_up(n, block); }
 
 }  // namespace
@@ -444,11 +620,19 @@ int pv_main_launch(const PvMainParams& p_in, int max_tasks, int num_sms, cudaStr
   return 0;
 }
 
-int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, int dst_box_count,
-                   const float* r6, char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream) {
+int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, const RegionHead* dst_head,
+                   char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream) {
   KNN_CUDA_TRY(cudaMemsetAsync(out_count, 0, sizeof(int), stream));
-  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, dst_boxes, dst_box_count,
-                                                 r6[0], r6[1], r6[2], r6[3], r6[4], r6[5], peer_inbox, out_count);
+  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, dst_boxes, dst_head, peer_inbox, out_count);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int region_build_launch(const RegionBuildParams& p, cudaStream_t stream) {
+  const size_t smem = (size_t)kRegionBoxes * (sizeof(RegionItem) + 2 * sizeof(float4));
+  KNN_CUDA_TRY(cudaFuncSetAttribute(region_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  region_build_kernel<<<1, kRegionThreads, smem, stream>>>(p);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;

@@ -260,11 +260,20 @@ __device__ __forceinline__ void tile_scatter(const Item* items, const int* dest,
   const int t = threadIdx.x;
   if (t < kMaxRanks) s_count[t] = 0;
   __syncthreads();
+  // warp-aggregated: lanes with the same destination share one shared-memory atomic (a tile has <= 16
+  // destinations, so per-item atomics would pile up on a handful of addresses)
   int slot[kScatterPer];
+  const unsigned lt = (1u << (t & 31)) - 1u;
 #pragma unroll
   for (int j = 0; j < kScatterPer; ++j) {
     const int i = t + j * kScatterThreads;
-    slot[j] = i < count_in_tile ? atomicAdd(&s_count[dest[j]], 1) : 0;
+    const int dj = i < count_in_tile ? dest[j] : -1;
+    const unsigned peers = __match_any_sync(kFullMask, dj);
+    int base = 0;
+    const int leader = __ffs(peers) - 1;
+    if ((t & 31) == leader && dj >= 0) base = atomicAdd(&s_count[dj], __popc(peers));
+    base = __shfl_sync(kFullMask, base, leader);
+    slot[j] = base + __popc(peers & lt);
   }
   __syncthreads();
   if (t == 0) {
