@@ -367,12 +367,19 @@ push_pairs_kernel(const PushPairsParams p) {
   p.dst[o][p.dst_offset[o] + (i - p.cut[o])] = make_uint2(p.ids[i], p.vals[i]);
 }
 
+// The pairs arrive in no particular order, so this is a random permutation of 4-byte values: written in
+// one go, every store would be a read-modify-write of a 32-byte DRAM sector (measured 5.2 ms for 134 M
+// pairs). Instead the output is covered in windows small enough to stay in L2; every window re-reads the
+// pairs (sequential, cheap) and writes only its own ids, which merge in L2 before they go to DRAM.
 __global__ void __launch_bounds__(256)
-scatter_pairs_kernel(const uint2* __restrict__ pairs, int64_t n, int64_t begin, float* __restrict__ out) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const uint2 pr = pairs[i];
-  out[(int64_t)pr.x - begin] = __uint_as_float(pr.y);
+scatter_pairs_kernel(const uint2* __restrict__ pairs, int64_t n, int64_t begin, float* __restrict__ out,
+                     int64_t window_lo, int64_t window_hi) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint2 pr = __ldcs(pairs + i);
+    const int64_t o = (int64_t)pr.x - begin;
+    if (o >= window_lo && o < window_hi) out[o] = __uint_as_float(pr.y);
+  }
 }
 
 __global__ void __launch_bounds__(256)
@@ -707,8 +714,14 @@ int push_pairs_launch(const PushPairsParams& p, cudaStream_t stream) {
 
 int scatter_pairs_launch(const void* pairs, int64_t n, int64_t begin, float* out, cudaStream_t stream) {
   if (n <= 0) return 0;
-  scatter_pairs_kernel<<<blocks_for(n, 256), 256, 0, stream>>>(static_cast<const uint2*>(pairs), n, begin, out);
-  note_launch();
+  const int64_t window = (int64_t)20 << 20;             // 20 Mi results = 80 MB of output per window (L2: 126 MB)
+  int64_t blocks = blocks_for(n, 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  for (int64_t lo = 0; lo < n; lo += window) {
+    scatter_pairs_kernel<<<(int)blocks, 256, 0, stream>>>(static_cast<const uint2*>(pairs), n, begin, out, lo,
+                                                        lo + window < n ? lo + window : n);
+    note_launch();
+  }
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;
 }
