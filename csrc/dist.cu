@@ -139,9 +139,9 @@ constexpr size_t kHeapReserved = kCollDataOff + 2 * (size_t)kMaxRanks * kCollWor
 static_assert(2 * kMaxRanks * sizeof(unsigned) <= kCollDataOff - kCollFlagsOff, "collective flags overflow their area");
 static_assert(kHeapReserved % 256 == 0, "reserved area keeps the 256-byte alignment of what follows");
 
-size_t pv_heap_need(int k, int Gc) {
+size_t pv_heap_need(int k, int Gc, int64_t max_groups, int R) {
   return kHeapReserved + 2 * align256((size_t)Gc * pv_slot_bytes(k)) + 6 * 256 +
-         align256((size_t)kMaxRanks * kRegionBoxes * sizeof(Box)) + align256((size_t)kMaxRanks * sizeof(RegionHead));
+         align256((size_t)R * tops_capacity(max_groups) * sizeof(Box)) + align256((size_t)kMaxRanks * sizeof(TopHead));
 }
 
 // Device-side barrier over all ranks, enqueued on `stream` (replaces MPI_Barrier,
@@ -211,36 +211,32 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   NvtxRange range("b200knn:culled_exchange");
   const int R = d->world, me = d->rank;
   PhaseTrace trace(me, stream);
-  // everyone's region (pv.cu, region_build_kernel): built on the device next to the tree and stored into
-  // every rank's table by peer stores; a device barrier makes the tables complete. No host collective.
-  const size_t off_regions = d->alloc((size_t)kMaxRanks * kRegionBoxes * sizeof(Box));
-  const size_t off_heads = d->alloc((size_t)kMaxRanks * sizeof(RegionHead));
+  // everyone's upper tree levels, replicated on every rank by peer stores (pv.cu, tops_publish_kernel); a
+  // device barrier makes the tables complete. No host collective.
+  const int64_t tops_cap = tops_capacity(pl.max_groups);
+  const size_t off_tops = d->alloc((size_t)R * tops_cap * sizeof(Box));
+  const size_t off_heads = d->alloc((size_t)kMaxRanks * sizeof(TopHead));
   KNN_REQUIRE(d->bump <= d->bytes, "symmetric heap too small (internal sizing error)");
-  const Box* d_regions = reinterpret_cast<const Box*>(d->base + off_regions);
-  const RegionHead* d_heads = reinterpret_cast<const RegionHead*>(d->base + off_heads);
+  TopsView tops;
+  tops.boxes = reinterpret_cast<const Box*>(d->base + off_tops);
+  tops.heads = reinterpret_cast<const TopHead*>(d->base + off_heads);
+  tops.cap = tops_cap;
   if (R > 1) {
-    RegionBuildParams rb;
-    memset(&rb, 0, sizeof(rb));
-    rb.tree = idx->view();
-    memcpy(rb.overall, idx->h_bounds, sizeof(rb.overall));
-    rb.R = R;
-    rb.rank = me;
+    TopsPublishParams tp;
+    memset(&tp, 0, sizeof(tp));
+    tp.tree = idx->view();
+    memcpy(tp.overall, idx->h_bounds, sizeof(tp.overall));
+    tp.R = R;
+    tp.rank = me;
+    tp.cap = tops_cap;
     for (int r = 0; r < R; ++r) {
-      rb.tables[r] = reinterpret_cast<Box*>(d->peer[r] + off_regions);
-      rb.heads[r] = reinterpret_cast<RegionHead*>(d->peer[r] + off_heads);
+      tp.tables[r] = reinterpret_cast<Box*>(d->peer[r] + off_tops);
+      tp.heads[r] = reinterpret_cast<TopHead*>(d->peer[r] + off_heads);
     }
     int rcb;
-    if ((rcb = region_build_launch(rb, stream))) return rcb;
+    if ((rcb = tops_publish_launch(tp, idx->num_sms, stream))) return rcb;
     if ((rcb = device_barrier(d, stream))) return rcb;
-    if (me == 0 && getenv("B200KNN_DEBUG_REGIONS")) {
-      std::vector<RegionHead> heads(R);
-      KNN_CUDA_TRY(cudaMemcpyAsync(heads.data(), d_heads, (size_t)R * sizeof(RegionHead), cudaMemcpyDeviceToHost, stream));
-      KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-      for (int r = 0; r < R; ++r)
-        fprintf(stderr, "[regions] rank %d: %d boxes, overall (%g %g %g)-(%g %g %g)\n", r, heads[r].count, heads[r].box[0],
-                heads[r].box[1], heads[r].box[2], heads[r].box[3], heads[r].box[4], heads[r].box[5]);
-    }
-    trace.mark("exchange: region boxes (device) + barrier");
+    trace.mark("exchange: publish tree tops + barrier");
   }
 
   const size_t slot = pv_slot_bytes(k);
@@ -258,8 +254,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.sentinel = sentinel_d2(max_radius);
   p.R = R;
   p.rank = me;
-  p.region_boxes = d_regions;
-  p.region_heads = d_heads;
+  p.tops = tops;
   p.home_queries = idx->pts;
   p.home_n = idx->n;
   p.home_is_tree = 1;
@@ -318,8 +313,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     const double tr0 = now_ms();
     for (int j = 1; j < R; ++j) {
       const int dst = (me + j) % R, src = (me - j + R) % R;
-      if ((rc = pv_push_launch(p.pending, p.pending_count, k, d_regions + (size_t)dst * kRegionBoxes, d_heads + dst,
-                               d->peer[dst] + off_inbox, out_count, idx->num_sms, stream))) return rc;
+      if ((rc = pv_push_launch(p.pending, p.pending_count, k, tops, dst, d->peer[dst] + off_inbox, out_count,
+                               idx->num_sms, stream))) return rc;
       if ((rc = pv_publish_launch(out_count, reinterpret_cast<int*>(d->peer[dst] + off_icount), stream))) return rc;
       // round fences are device-side sequence-flag barriers, enqueued on the stream: the host does
       // not synchronise between push, serve and the next round
@@ -348,7 +343,7 @@ int knn_prepartitioned(b200knn_dist* d, const float* d_xyz, int64_t n_local, int
     for (int64_t v : all) max_n = std::max(max_n, v);
   }
   const PvPlan pl = pv_plan(max_n, k, groups_per_chunk);
-  if ((rc = ensure_heap(d, pv_heap_need(k, pl.Gc)))) return rc;
+  if ((rc = ensure_heap(d, pv_heap_need(k, pl.Gc, pl.max_groups, d->world)))) return rc;
   d->bump = kHeapReserved;
   const double t0 = now_ms();
   b200knn_index* idx = nullptr;
@@ -472,7 +467,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   // ---- symmetric heap: histograms | receive buffer | result landing zone | exchange slots
   const PvPlan pl = pv_plan(max_recv, k, groups_per_chunk);
   const size_t need = hist_bytes + align256((size_t)std::max<int64_t>(max_recv, 1) * sizeof(Float4)) +
-                      align256((size_t)std::max<int64_t>(max_local, 1) * 8) + pv_heap_need(k, pl.Gc);
+                      align256((size_t)std::max<int64_t>(max_local, 1) * 8) + pv_heap_need(k, pl.Gc, pl.max_groups, R);
   if ((rc = ensure_heap(d, need))) return rc;
   d->bump = kHeapReserved;
   (void)d->alloc(hist_bytes);

@@ -118,12 +118,27 @@ struct CollectParams {
 int collect_launch(const CollectParams& p, int num_sms, cudaStream_t stream);
 
 // ---------------- culled exchange / redistribution (pv.cu) ----------------
-constexpr int kRegionBoxes = 2048;
 // A slot carries one group: heap [k][32] floats, positions [32] float4, meta [4] int32.
 KNN_HD size_t pv_slot_bytes(int k) { return (size_t)k * 128 + 512 + 16; }
 
-struct RegionHead { int count; int pad; float box[6]; };   // 32 bytes
-
+// Every rank's upper tree levels (level 1 and above: one box per 1024 points and coarser), replicated on every
+// rank by peer stores (pv.cu, tops_publish_kernel). "Does this group's ball reach rank s?" is answered by
+// walking rank s's published levels: the walk only descends where the ball goes, so it is as fine as the
+// data is dense — a fixed number of cover boxes per rank is not (a rank that owns a piece of a dense
+// cluster AND far-flung sparse points spends its boxes on the latter, and one coarse box over its piece
+// of the cluster then attracts every group of the neighbour that owns the rest of it).
+struct TopHead {
+  int levels;                   // levels of that rank's tree (0: the rank is empty)
+  int base_level;               // published levels: base_level .. levels-1 (base_level = 1, or 0 for a single-level tree)
+  int count[kMaxLevels];        // boxes per level
+  int offset[kMaxLevels];       // where a published level starts inside the rank's table
+  float box[6];                 // overall bounding box (quick reject)
+};
+struct TopsView {
+  const Box* boxes;             // [R][cap]
+  const TopHead* heads;         // [R]
+  int64_t cap;
+};
 struct PvMainParams {
   TreeView tree;
   int k;
@@ -132,9 +147,7 @@ struct PvMainParams {
   int fill;                    // as RingParams::fill, LOCAL phase only
   float* global_heaps;         // set by pv_main_launch when k exceeds the shared-memory heap
   int R, rank;
-  const Box* region_boxes;     // [R][kRegionBoxes]: every rank's region, a cover of its points by up to
-                               // kRegionBoxes boxes (region_build_kernel), written here by that rank
-  const RegionHead* region_heads;   // [R]: boxes in use (0 for an empty rank) + overall bounding box (quick reject)
+  TopsView tops;               // every rank's published tree levels
   // LOCAL
   const Float4* home_queries;
   int64_t home_n;
@@ -152,21 +165,18 @@ struct PvMainParams {
   unsigned long long* stats;
 };
 int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream);
-int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, const RegionHead* dst_head,
+int pv_push_launch(const char* pending, const int* pending_count, int k, const TopsView& tops, int dst,
                    char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
-
-// One CTA describes this rank's points by up to kRegionBoxes boxes and stores the description into every
-// rank's region table (peer stores): start from the tree's top level and keep splitting the box with the
-// largest surface — an inner node into its children, a leaf (or a subset of a leaf's points) in two at the
-// largest gap along its widest axis.
-struct RegionBuildParams {
+struct TopsPublishParams {
   TreeView tree;
   float overall[6];             // this rank's bounding box
   int R, rank;
-  Box* tables[kMaxRanks];       // every rank's [R][kRegionBoxes] table (peer pointers)
-  RegionHead* heads[kMaxRanks]; // every rank's [R] heads
+  int64_t cap;
+  Box* tables[kMaxRanks];       // every rank's [R][cap] table (peer pointers)
+  TopHead* heads[kMaxRanks];    // every rank's [R] heads
 };
-int region_build_launch(const RegionBuildParams& p, cudaStream_t stream);
+int64_t tops_capacity(int64_t max_groups);      // boxes a rank with at most max_groups leaves publishes (upper bound)
+int tops_publish_launch(const TopsPublishParams& p, int num_sms, cudaStream_t stream);
 int pv_publish_launch(const int* out_count, int* peer_inbox_count, cudaStream_t stream);
 int pv_final_launch(const char* pending, const int* pending_count, int k, float* result_sorted, int num_sms,
                     cudaStream_t stream);

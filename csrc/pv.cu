@@ -40,6 +40,62 @@ __device__ __forceinline__ const int* slot_meta(const char* slot, int k) {
   return reinterpret_cast<const int*>(slot + (size_t)k * 128 + 512);
 }
 
+// Does the group's ball reach rank s's points, as far as s's published tree levels can tell? The warp walks
+// them depth-first (lane = child box, group-level test with the group's box and largest radius) and settles
+// the matter at the lowest published level with the per-query test. `stack` holds kTopsStack node ids; if it
+// overflows the answer is a conservative yes.
+constexpr int kTopsStack = 128;
+__device__ __forceinline__ bool reaches_rank(const TopsView& tv, int s, float qx, float qy, float qz, float top,
+                                             bool valid, float glx, float gly, float glz, float ghx, float ghy,
+                                             float ghz, float maxR2, unsigned* stack) {
+  const TopHead* h = tv.heads + s;
+  const int levels = __ldg(&h->levels);
+  if (levels == 0) return false;
+  if (!(box_box_lb(glx, gly, glz, ghx, ghy, ghz, __ldg(&h->box[0]), __ldg(&h->box[1]), __ldg(&h->box[2]),
+                   __ldg(&h->box[3]), __ldg(&h->box[4]), __ldg(&h->box[5])) < maxR2))
+    return false;
+  const int base_level = __ldg(&h->base_level);
+  const Box* boxes = tv.boxes + (size_t)s * tv.cap;
+  const int lane = lane_id();
+  const unsigned lt = (1u << lane) - 1u;
+  int sp = 0;
+  unsigned node = (unsigned)levels << kNodeIdxBits;      // virtual root: its children are the top level
+  for (;;) {
+    const int L = (int)(node >> kNodeIdxBits), idx = (int)(node & ((1u << kNodeIdxBits) - 1u));
+    const int cl = L - 1;
+    const int cbase = L == levels ? 0 : idx * kFanout;
+    const int rem = __ldg(&h->count[cl]) - cbase;
+    const int ccount = rem < kFanout ? rem : kFanout;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    if (lane < ccount) {
+      const float4* bp = reinterpret_cast<const float4*>(boxes + __ldg(&h->offset[cl]) + cbase + lane);
+      a = __ldg(bp);
+      b = __ldg(bp + 1);
+    }
+    const bool pass = lane < ccount && box_box_lb(glx, gly, glz, ghx, ghy, ghz, a.x, a.y, a.z, b.x, b.y, b.z) < maxR2;
+    unsigned pm = __ballot_sync(kFullMask, pass);
+    if (cl == base_level) {
+      while (pm != 0u) {
+        const int bi = __ffs(pm) - 1;
+        pm &= pm - 1;
+        const float lb = point_box_lb(qx, qy, qz, __shfl_sync(kFullMask, a.x, bi), __shfl_sync(kFullMask, a.y, bi),
+                                      __shfl_sync(kFullMask, a.z, bi), __shfl_sync(kFullMask, b.x, bi),
+                                      __shfl_sync(kFullMask, b.y, bi), __shfl_sync(kFullMask, b.z, bi));
+        if (__any_sync(kFullMask, valid && (lb < top))) return true;
+      }
+    } else if (pm != 0u) {
+      const int np = __popc(pm);
+      if (sp + np > kTopsStack) return true;
+      if (pass) stack[sp + __popc(pm & lt)] = ((unsigned)cl << kNodeIdxBits) | (unsigned)(cbase + lane);
+      sp += np;
+      __syncwarp();
+    }
+    if (sp == 0) return false;
+    node = stack[--sp];
+    __syncwarp();
+  }
+}
+
 // SORTED / GLOBAL_HEAP: as in query.cu — sorted lists + append buffers in shared memory for 2 <= k <= ~1700,
 // the heap for k == 1 and (in a global scratch block per resident warp) for k beyond the shared-memory limit.
 template <bool GLOBAL_HEAP, bool SORTED>
@@ -110,34 +166,8 @@ pv_main_kernel_t(const PvMainParams p) {
         bool need = false;
         for (int s = 0; s < p.R && !need; ++s) {
           if (s == p.rank) continue;
-          // quick reject against the rank's overall box (warp-uniform)
-          const int region_count = __ldg(&p.region_heads[s].count);
-          const float* ob = p.region_heads[s].box;
-          if (region_count == 0 ||
-              !(box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, __ldg(ob), __ldg(ob + 1), __ldg(ob + 2), __ldg(ob + 3),
-                           __ldg(ob + 4), __ldg(ob + 5)) < g.maxR2))
-            continue;
-          const Box* rb = p.region_boxes + (size_t)s * kRegionBoxes;
-          for (int base = 0; base < region_count && !need; base += 32) {
-            bool hit = false;
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-            if (base + lane < region_count) {
-              const float4* bp = reinterpret_cast<const float4*>(rb + base + lane);
-              a = __ldg(bp);
-              b = __ldg(bp + 1);
-              hit = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z) < g.maxR2;
-            }
-            // group-level hits are refined per query: lane = query, one candidate box at a time
-            unsigned hm = __ballot_sync(kFullMask, hit);
-            while (hm != 0u && !need) {
-              const int bi = __ffs(hm) - 1;
-              hm &= hm - 1;
-              const float lb = point_box_lb(g.qx, g.qy, g.qz, __shfl_sync(kFullMask, a.x, bi), __shfl_sync(kFullMask, a.y, bi),
-                                            __shfl_sync(kFullMask, a.z, bi), __shfl_sync(kFullMask, b.x, bi),
-                                            __shfl_sync(kFullMask, b.y, bi), __shfl_sync(kFullMask, b.z, bi));
-              need = __any_sync(kFullMask, g.valid && (lb < g.top));
-            }
-          }
+          need = reaches_rank(p.tops, s, g.qx, g.qy, g.qz, g.top, g.valid, g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz,
+                              g.maxR2, g.qnode);
         }
         if (need) {
           int slot_idx = 0;
@@ -166,16 +196,13 @@ pv_main_kernel_t(const PvMainParams p) {
   flush_stats(g, p.stats);
 }
 
-// One warp per pending slot: if the group's ball reaches any box of the destination's region, copy
-// the whole slot into the next free slot of the destination GPU's inbox.
+// One warp per pending slot: if the group's ball (with the radius it has by now) still reaches the
+// destination rank, copy the whole slot into the next free slot of the destination GPU's inbox.
 __global__ void __launch_bounds__(256)
-pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending_count, int k,
-               const Box* __restrict__ dst_boxes, const RegionHead* __restrict__ dst_head,
-               char* __restrict__ peer_inbox, int* __restrict__ out_count) {
+pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending_count, int k, const TopsView tops,
+               int dst_rank, char* __restrict__ peer_inbox, int* __restrict__ out_count) {
+  __shared__ unsigned stacks[8][kTopsStack];
   const int lane = lane_id();
-  const int dst_box_count = dst_head->count;
-  const float rlx = dst_head->box[0], rly = dst_head->box[1], rlz = dst_head->box[2];
-  const float rhx = dst_head->box[3], rhy = dst_head->box[4], rhz = dst_head->box[5];
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const size_t slot_bytes = pv_slot_bytes(k);
   const int total = *pending_count;
@@ -197,28 +224,8 @@ pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending
     }
     const float top = slot_heap(slot)[lane];
     const float maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, valid ? __float_as_uint(top) : 0u));
-    if (!(box_box_lb(lx, ly, lz, hx, hy, hz, rlx, rly, rlz, rhx, rhy, rhz) < maxR2)) continue;   // overall box
-    bool need = false;
-    for (int base = 0; base < dst_box_count && !need; base += 32) {
-      bool hit = false;
-      float4 ba = make_float4(0.f, 0.f, 0.f, 0.f), bb = ba;
-      if (base + lane < dst_box_count) {
-        const float4* bp = reinterpret_cast<const float4*>(dst_boxes + base + lane);
-        ba = __ldg(bp);
-        bb = __ldg(bp + 1);
-        hit = box_box_lb(lx, ly, lz, hx, hy, hz, ba.x, ba.y, ba.z, bb.x, bb.y, bb.z) < maxR2;
-      }
-      unsigned hm = __ballot_sync(kFullMask, hit);
-      while (hm != 0u && !need) {
-        const int bi = __ffs(hm) - 1;
-        hm &= hm - 1;
-        const float lb = point_box_lb(q.x, q.y, q.z, __shfl_sync(kFullMask, ba.x, bi), __shfl_sync(kFullMask, ba.y, bi),
-                                      __shfl_sync(kFullMask, ba.z, bi), __shfl_sync(kFullMask, bb.x, bi),
-                                      __shfl_sync(kFullMask, bb.y, bi), __shfl_sync(kFullMask, bb.z, bi));
-        need = __any_sync(kFullMask, valid && (lb < top));
-      }
-    }
-    if (!need) continue;
+    if (!reaches_rank(tops, dst_rank, q.x, q.y, q.z, top, valid, lx, ly, lz, hx, hy, hz, maxR2, stacks[threadIdx.x >> 5]))
+      continue;
     int o = 0;
     if (lane == 0) o = atomicAdd(out_count, 1);
     o = __shfl_sync(kFullMask, o, 0);
@@ -403,174 +410,34 @@ __global__ void lower_bounds_kernel(const uint64_t* __restrict__ sorted_keys, in
   out[j] = lo;
 }
 
-// ---- region description -------------------------------------------------------------------------------
-// A rank's REGION is what the others test a group's ball against to decide whether the group must visit.
-// One box per rank, or any fixed tree level, is defeated by a single node that straddles a jump of the
-// Z-curve or the gap between two clusters: its box covers everything in between and attracts every group
-// of the ranks in between. So the cover is adaptive: up to kRegionBoxes boxes, grown from the tree's top
-// level by always splitting the box with the largest surface. Round 1 did this on the host with a blocking
-// copy per opened node and shipped the result through a bootstrap all-gather; here one CTA does it next to
-// the data and stores the result straight into every rank's table.
-constexpr int kRegionThreads = 1024;
-
-struct RegionItem {
-  float key;          // half surface area; < 0: cannot be split any further
-  int level;          // >= 1 inner node, 0 leaf, -1 subset of a leaf's points (mask)
-  int index;          // node index (for a subset: the leaf)
-  unsigned mask;      // subset: which of the leaf's points
-};
-
-__device__ __forceinline__ float region_area(float lx, float ly, float lz, float hx, float hy, float hz) {
-  const float ex = hx - lx, ey = hy - ly, ez = hz - lz;
-  return ex * ey + ey * ez + ez * ex + 1e-30f * (ex + ey + ez);     // flat boxes still rank
-}
-
-__global__ void __launch_bounds__(kRegionThreads)
-region_build_kernel(const RegionBuildParams p) {
-  extern __shared__ __align__(16) unsigned char region_smem[];
-  RegionItem* items = reinterpret_cast<RegionItem*>(region_smem);                       // [kRegionBoxes]
-  float4* lo = reinterpret_cast<float4*>(items + kRegionBoxes);                          // [kRegionBoxes]
-  float4* hi = lo + kRegionBoxes;
-  __shared__ float s_key[32];
-  __shared__ int s_idx[32];
-  __shared__ int s_count, s_best;
-  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+// ---- publishing the upper tree levels ---------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+tops_publish_kernel(const TopsPublishParams p) {
   const TreeView& tr = p.tree;
-
-  if (t == 0) s_count = 0;
-  __syncthreads();
-  if (tr.levels > 0 && tr.n > 0) {
-    const int top = tr.levels - 1;
-    if (t < tr.count[top]) {
-      const float4* bp = reinterpret_cast<const float4*>(tr.boxes[top]) + 2 * (size_t)t;
-      const float4 a = bp[0], b = bp[1];
-      lo[t] = a; hi[t] = b;
-      items[t].key = region_area(a.x, a.y, a.z, b.x, b.y, b.z);
-      items[t].level = top; items[t].index = t; items[t].mask = 0xffffffffu;
+  const int base_level = tr.levels > 1 ? 1 : 0;
+  int64_t off = 0;
+  for (int l = base_level; l < tr.levels; ++l) {
+    const float4* src = reinterpret_cast<const float4*>(tr.boxes[l]);
+    const int64_t n4 = 2 * (int64_t)tr.count[l];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+      const float4 v = src[i];
+      for (int r = 0; r < p.R; ++r)
+        reinterpret_cast<float4*>(p.tables[r] + (size_t)p.rank * p.cap + off)[i] = v;
     }
-    if (t == 0) s_count = tr.count[top];
+    off += tr.count[l];
   }
-  __syncthreads();
-
-  for (;;) {
-    const int count = s_count;
-    // ---- the splittable item with the largest surface
-    float bk = -1.f;
-    int bi = -1;
-    for (int i = t; i < count; i += kRegionThreads) {
-      const float kx = items[i].key;
-      if (kx > bk) { bk = kx; bi = i; }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    TopHead h;
+    h.levels = tr.n > 0 ? tr.levels : 0;
+    h.base_level = base_level;
+    int64_t o = 0;
+    for (int l = 0; l < kMaxLevels; ++l) {
+      h.count[l] = l < tr.levels ? tr.count[l] : 0;
+      h.offset[l] = (l >= base_level && l < tr.levels) ? (int)o : 0;
+      if (l >= base_level && l < tr.levels) o += tr.count[l];
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ok = __shfl_xor_sync(kFullMask, bk, o);
-      const int oi = __shfl_xor_sync(kFullMask, bi, o);
-      if (ok > bk || (ok == bk && oi >= 0 && (bi < 0 || oi < bi))) { bk = ok; bi = oi; }
-    }
-    if (lane == 0) { s_key[w] = bk; s_idx[w] = bi; }
-    __syncthreads();
-    if (w == 0) {
-      bk = s_key[lane]; bi = s_idx[lane];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float ok = __shfl_xor_sync(kFullMask, bk, o);
-        const int oi = __shfl_xor_sync(kFullMask, bi, o);
-        if (ok > bk || (ok == bk && oi >= 0 && (bi < 0 || oi < bi))) { bk = ok; bi = oi; }
-      }
-      if (lane == 0) s_best = bk >= 0.f ? bi : -1;
-    }
-    __syncthreads();
-    const int best = s_best;
-    if (best < 0) break;                                   // nothing left that can be split
-    const RegionItem it = items[best];
-    if (it.level >= 1) {
-      const int c0 = it.index * kFanout;
-      const int rem = tr.count[it.level - 1] - c0;
-      const int nc = rem < kFanout ? rem : kFanout;
-      if (count - 1 + nc > kRegionBoxes) break;            // no room for its children: the cover is done
-      __syncthreads();
-      if (t < nc) {
-        const float4* bp = reinterpret_cast<const float4*>(tr.boxes[it.level - 1]) + 2 * (size_t)(c0 + t);
-        const float4 a = bp[0], b = bp[1];
-        const int slot = t == 0 ? best : count + t - 1;
-        lo[slot] = a; hi[slot] = b;
-        items[slot].key = region_area(a.x, a.y, a.z, b.x, b.y, b.z);
-        items[slot].level = it.level - 1; items[slot].index = c0 + t; items[slot].mask = 0xffffffffu;
-      }
-      if (t == 0) s_count = count + nc - 1;
-      __syncthreads();
-      continue;
-    }
-    // ---- a leaf or a subset of one: cut at the largest gap along the widest axis (warp 0)
-    if (count + 1 > kRegionBoxes) break;
-    __syncthreads();
-    if (w == 0) {
-      const int64_t first = (int64_t)it.index * kGroup;
-      const int64_t remn = (int64_t)tr.n - first;
-      const int cnt = remn < kGroup ? (int)remn : kGroup;
-      const bool valid = lane < cnt && ((it.mask >> lane) & 1u);
-      float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (valid) q = reinterpret_cast<const float4*>(tr.pts)[first + lane];
-      const float4 a = lo[best], b = hi[best];
-      const float ex = b.x - a.x, ey = b.y - a.y, ez = b.z - a.z;
-      const int axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
-      const float c = valid ? (axis == 0 ? q.x : (axis == 1 ? q.y : q.z)) : INFINITY;
-      float succ = INFINITY;
-      for (int j = 0; j < 32; ++j) {
-        const float cj = __shfl_sync(kFullMask, c, j);
-        if (cj > c) succ = fminf(succ, cj);
-      }
-      const float gap = (valid && succ < INFINITY) ? succ - c : 0.f;
-      const unsigned gbits = __float_as_uint(gap);
-      const unsigned gmax = __reduce_max_sync(kFullMask, gbits);
-      const unsigned vm = __ballot_sync(kFullMask, valid);
-      if (__popc(vm) < 2 || !(__uint_as_float(gmax) > 0.f)) {
-        if (lane == 0) items[best].key = -1.f;             // a single point, or all points identical
-      } else {
-        const int wl = __ffs(__ballot_sync(kFullMask, valid && gbits == gmax)) - 1;
-        const float cut = __shfl_sync(kFullMask, c, wl);
-        const unsigned left = __ballot_sync(kFullMask, valid && c <= cut);
-        const unsigned right = vm & ~left;
-        for (int half = 0; half < 2; ++half) {
-          const unsigned m = half == 0 ? left : right;
-          const bool in = (m >> lane) & 1u;
-          float lx = in ? q.x : INFINITY, ly = in ? q.y : INFINITY, lz = in ? q.z : INFINITY;
-          float hx = in ? q.x : -INFINITY, hy = in ? q.y : -INFINITY, hz = in ? q.z : -INFINITY;
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-            lx = fminf(lx, __shfl_xor_sync(kFullMask, lx, o)); ly = fminf(ly, __shfl_xor_sync(kFullMask, ly, o));
-            lz = fminf(lz, __shfl_xor_sync(kFullMask, lz, o)); hx = fmaxf(hx, __shfl_xor_sync(kFullMask, hx, o));
-            hy = fmaxf(hy, __shfl_xor_sync(kFullMask, hy, o)); hz = fmaxf(hz, __shfl_xor_sync(kFullMask, hz, o));
-          }
-          if (lane == 0) {
-            const int slot = half == 0 ? best : count;
-            lo[slot] = make_float4(lx, ly, lz, 0.f);
-            hi[slot] = make_float4(hx, hy, hz, 0.f);
-            items[slot].key = __popc(m) >= 2 ? region_area(lx, ly, lz, hx, hy, hz) : -1.f;
-            items[slot].level = -1; items[slot].index = it.index; items[slot].mask = m;
-          }
-        }
-        if (lane == 0) s_count = count + 1;
-      }
-    }
-    __syncthreads();
-  }
-
-  // ---- publish: this rank's row of every rank's table
-  const int count = s_count;
-  for (int r = 0; r < p.R; ++r) {
-    float4* dst = reinterpret_cast<float4*>(p.tables[r] + (size_t)p.rank * kRegionBoxes);
-    for (int i = t; i < count; i += kRegionThreads) {
-      const float4 a = lo[i], b = hi[i];
-      dst[2 * i] = make_float4(a.x, a.y, a.z, 0.f);
-      dst[2 * i + 1] = make_float4(b.x, b.y, b.z, 0.f);
-    }
-    if (t == 0) {
-      RegionHead h;
-      h.count = count; h.pad = 0;
-      for (int a = 0; a < 6; ++a) h.box[a] = p.overall[a];
-      p.heads[r][p.rank] = h;
-    }
+    for (int a = 0; a < 6; ++a) h.box[a] = p.overall[a];
+    for (int r = 0; r < p.R; ++r) p.heads[r][p.rank] = h;
   }
 }
 
@@ -627,19 +494,24 @@ int pv_main_launch(const PvMainParams& p_in, int max_tasks, int num_sms, cudaStr
   return 0;
 }
 
-int pv_push_launch(const char* pending, const int* pending_count, int k, const Box* dst_boxes, const RegionHead* dst_head,
+int pv_push_launch(const char* pending, const int* pending_count, int k, const TopsView& tops, int dst,
                    char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream) {
   KNN_CUDA_TRY(cudaMemsetAsync(out_count, 0, sizeof(int), stream));
-  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, dst_boxes, dst_head, peer_inbox, out_count);
+  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, tops, dst, peer_inbox, out_count);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
-int region_build_launch(const RegionBuildParams& p, cudaStream_t stream) {
-  const size_t smem = (size_t)kRegionBoxes * (sizeof(RegionItem) + 2 * sizeof(float4));
-  KNN_CUDA_TRY(cudaFuncSetAttribute(region_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  region_build_kernel<<<1, kRegionThreads, smem, stream>>>(p);
+int64_t tops_capacity(int64_t max_groups) {
+  int64_t c = max_groups > 1 ? max_groups : 1, total = 0;
+  if (c <= kFanout) return c + 64;                       // single-level tree: the leaf level is what gets published
+  while (c > kFanout) { c = div_up(c, kFanout); total += c; }
+  return total + 64;
+}
+
+int tops_publish_launch(const TopsPublishParams& p, int num_sms, cudaStream_t stream) {
+  tops_publish_kernel<<<num_sms * 2, 256, 0, stream>>>(p);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;

@@ -78,9 +78,12 @@ def main():
         n_total = int(sum(float(x[3]) for x in allp))
         ms = sum(times) / len(times)
         finite = bool(torch.isfinite(out).all().item()) if pts.shape[0] else True
+        # 64 sampled results proven against ALL points of all ranks by counting (collective; ops.knn.verify_sample)
+        from mpi_cuda_largescaleknn_b200.ops.knn import verify_sample
+        verified = verify_sample(pts, out, k, samples=64, seed=11)
         if rank == 0:
             print(json.dumps({"config": name, "n_total": n_total, "k": k, "mode": mode, "gpus": world, "ms_per_step": ms,
-                              "queries_per_s": n_total / ms * 1e3, "all_finite": finite,
+                              "queries_per_s": n_total / ms * 1e3, "all_finite": finite, "verified": verified,
                               "local_phase_ms_per_rank": [round(float(x[0]), 1) for x in allp],
                               "pending_groups_per_rank": [int(x[2]) for x in allp],
                               "heap_bytes": eng.heap_bytes, "report_rank0": rep}), flush=True)
