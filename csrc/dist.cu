@@ -207,7 +207,7 @@ PvPlan pv_plan(int64_t max_n, int k, int groups_per_chunk) {
 // The culled exchange over an existing local index. Heap must already be large enough; sub-allocations
 // are taken from d->bump (symmetric: same sequence on every rank). Results land in idx->result_sorted.
 int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const PvPlan& pl, cudaStream_t stream,
-           b200knn_dist_report* rep) {
+           b200knn_dist_report* rep, const Box* territory = nullptr, const int* territory_count = nullptr) {
   NvtxRange range("b200knn:culled_exchange");
   const int R = d->world, me = d->rank;
   PhaseTrace trace(me, stream);
@@ -255,6 +255,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.R = R;
   p.rank = me;
   p.tops = tops;
+  p.territory = territory;
+  p.territory_count = territory_count;
   p.home_queries = idx->pts;
   p.home_n = idx->n;
   p.home_is_tree = 1;
@@ -313,8 +315,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     const double tr0 = now_ms();
     for (int j = 1; j < R; ++j) {
       const int dst = (me + j) % R, src = (me - j + R) % R;
-      if ((rc = pv_push_launch(p.pending, p.pending_count, k, tops, dst, d->peer[dst] + off_inbox, out_count,
-                               idx->num_sms, stream))) return rc;
+      if ((rc = pv_push_launch(p.pending, p.pending_count, k, tops, territory, territory_count, dst,
+                               d->peer[dst] + off_inbox, out_count, idx->num_sms, stream))) return rc;
       if ((rc = pv_publish_launch(out_count, reinterpret_cast<int*>(d->peer[dst] + off_icount), stream))) return rc;
       // round fences are device-side sequence-flag barriers, enqueued on the stream: the host does
       // not synchronise between push, serve and the next round
@@ -400,6 +402,10 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   StreamBuf<uint64_t> d_split(stream);
   StreamBuf<long long> d_row(stream), d_M(stream), d_begins(stream);
   StreamBuf<RdPlan> d_plan(stream);
+  StreamBuf<Box> d_cells(stream);
+  StreamBuf<int> d_cell_counts(stream);
+  KNN_CUDA_TRY(d_cells.alloc_bytes((size_t)kMaxRanks * kTerritoryCells * sizeof(Box)));
+  KNN_CUDA_TRY(d_cell_counts.alloc_bytes(kMaxRanks * sizeof(int)));
   KNN_CUDA_TRY(d_bord.alloc_bytes(6 * sizeof(unsigned)));
   KNN_CUDA_TRY(d_info.alloc_bytes(kCollWords * sizeof(unsigned)));
   KNN_CUDA_TRY(d_info_all.alloc_bytes((size_t)kMaxRanks * kCollWords * sizeof(unsigned)));
@@ -440,6 +446,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
     KNN_CUDA_TRY(cudaMemcpyAsync(d_M, d_row, sizeof(long long), cudaMemcpyDeviceToDevice, stream));
   }
   if ((rc = rd_plan_launch(d_M, R, me, d_plan, stream))) return rc;
+  if ((rc = rd_territory_launch(d_split, d_info_all, R, d_cells, d_cell_counts, stream))) return rc;
 
   // ---- the one host synchronisation: sizes
   RdPlan plan;
@@ -496,7 +503,7 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   rc = b200knn_index_create_xyzw(reinterpret_cast<const float*>(d->base + off_recv), my_recv, 0, stream, &idx);
   pe.mark(stream);
   trace.mark("index build");
-  if (!rc) rc = run_pv(d, idx, k, max_radius, pl, stream, rep);
+  if (!rc) rc = run_pv(d, idx, k, max_radius, pl, stream, rep, d_cells, d_cell_counts);
   pe.mark(stream);
   trace.mark("culled exchange (total)");
 

@@ -148,6 +148,8 @@ struct PvMainParams {
   float* global_heaps;         // set by pv_main_launch when k exceeds the shared-memory heap
   int R, rank;
   TopsView tops;               // every rank's published tree levels
+  const Box* territory;        // optional [R][kTerritoryCells]: the octree cells that make up each rank's share of
+  const int* territory_count;  // key space after a redistribution (redist.cu); NULL: ranks own arbitrary point sets
   // LOCAL
   const Float4* home_queries;
   int64_t home_n;
@@ -165,8 +167,8 @@ struct PvMainParams {
   unsigned long long* stats;
 };
 int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream);
-int pv_push_launch(const char* pending, const int* pending_count, int k, const TopsView& tops, int dst,
-                   char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
+int pv_push_launch(const char* pending, const int* pending_count, int k, const TopsView& tops, const Box* territory,
+                   const int* territory_count, int dst, char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
 struct TopsPublishParams {
   TreeView tree;
   float overall[6];             // this rank's bounding box
@@ -275,6 +277,14 @@ struct RdReturnParams {
   RdPlan* plan;
   void* dst[kMaxRanks];                  // readers' landing zones of (id, value) pairs (peer pointers)
 };
+// After a redistribution rank s owns exactly the points whose Morton key lies in [split[s-1], split[s]): a union
+// of at most kTerritoryCells octree cells. rd_territory writes them as (slightly enlarged) boxes, identically on
+// every rank and without communication. A group whose ball misses all of rank s's cells cannot have a neighbour
+// there, whatever s's bounding boxes say — and the boxes of a Morton-ordered tree do say silly things: a node
+// that straddles a jump of the Z-curve has a box that covers other ranks' whole territory.
+constexpr int kTerritoryCells = 128;
+int rd_territory_launch(const uint64_t* d_split_keys, const unsigned* d_info_all, int R, Box* d_cells, int* d_counts,
+                        cudaStream_t stream);
 size_t rd_hist_bytes();                  // histogram A followed by histogram B
 size_t rd_histB_offset();
 int rd_pack_info_launch(const unsigned* d_bounds_ord, int64_t n, int64_t begin, unsigned* d_out, cudaStream_t stream);

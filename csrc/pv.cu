@@ -96,6 +96,35 @@ __device__ __forceinline__ bool reaches_rank(const TopsView& tv, int s, float qx
   }
 }
 
+// Does the group's ball touch rank s's share of key space (redist.cu, rd_territory)? lane = cell.
+__device__ __forceinline__ bool reaches_territory(const Box* __restrict__ territory, const int* __restrict__ territory_count,
+                                                  int s, float qx, float qy, float qz, float top, bool valid, float glx,
+                                                  float gly, float glz, float ghx, float ghy, float ghz, float maxR2) {
+  const int n = __ldg(territory_count + s);
+  const Box* cells = territory + (size_t)s * kTerritoryCells;
+  const int lane = lane_id();
+  for (int base = 0; base < n; base += 32) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    bool hit = false;
+    if (base + lane < n) {
+      const float4* bp = reinterpret_cast<const float4*>(cells + base + lane);
+      a = __ldg(bp);
+      b = __ldg(bp + 1);
+      hit = box_box_lb(glx, gly, glz, ghx, ghy, ghz, a.x, a.y, a.z, b.x, b.y, b.z) < maxR2;
+    }
+    unsigned hm = __ballot_sync(kFullMask, hit);
+    while (hm != 0u) {
+      const int bi = __ffs(hm) - 1;
+      hm &= hm - 1;
+      const float lb = point_box_lb(qx, qy, qz, __shfl_sync(kFullMask, a.x, bi), __shfl_sync(kFullMask, a.y, bi),
+                                    __shfl_sync(kFullMask, a.z, bi), __shfl_sync(kFullMask, b.x, bi),
+                                    __shfl_sync(kFullMask, b.y, bi), __shfl_sync(kFullMask, b.z, bi));
+      if (__any_sync(kFullMask, valid && (lb < top))) return true;
+    }
+  }
+  return false;
+}
+
 // SORTED / GLOBAL_HEAP: as in query.cu — sorted lists + append buffers in shared memory for 2 <= k <= ~1700,
 // the heap for k == 1 and (in a global scratch block per resident warp) for k beyond the shared-memory limit.
 template <bool GLOBAL_HEAP, bool SORTED>
@@ -166,6 +195,10 @@ pv_main_kernel_t(const PvMainParams p) {
         bool need = false;
         for (int s = 0; s < p.R && !need; ++s) {
           if (s == p.rank) continue;
+          if (p.territory != nullptr &&
+              !reaches_territory(p.territory, p.territory_count, s, g.qx, g.qy, g.qz, g.top, g.valid, g.glx, g.gly, g.glz,
+                                 g.ghx, g.ghy, g.ghz, g.maxR2))
+            continue;
           need = reaches_rank(p.tops, s, g.qx, g.qy, g.qz, g.top, g.valid, g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz,
                               g.maxR2, g.qnode);
         }
@@ -200,7 +233,8 @@ pv_main_kernel_t(const PvMainParams p) {
 // destination rank, copy the whole slot into the next free slot of the destination GPU's inbox.
 __global__ void __launch_bounds__(256)
 pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending_count, int k, const TopsView tops,
-               int dst_rank, char* __restrict__ peer_inbox, int* __restrict__ out_count) {
+               const Box* __restrict__ territory, const int* __restrict__ territory_count, int dst_rank,
+               char* __restrict__ peer_inbox, int* __restrict__ out_count) {
   __shared__ unsigned stacks[8][kTopsStack];
   const int lane = lane_id();
   const int warps = (gridDim.x * blockDim.x) >> 5;
@@ -224,6 +258,9 @@ pv_push_kernel(const char* __restrict__ pending, const int* __restrict__ pending
     }
     const float top = slot_heap(slot)[lane];
     const float maxR2 = __uint_as_float(__reduce_max_sync(kFullMask, valid ? __float_as_uint(top) : 0u));
+    if (territory != nullptr &&
+        !reaches_territory(territory, territory_count, dst_rank, q.x, q.y, q.z, top, valid, lx, ly, lz, hx, hy, hz, maxR2))
+      continue;
     if (!reaches_rank(tops, dst_rank, q.x, q.y, q.z, top, valid, lx, ly, lz, hx, hy, hz, maxR2, stacks[threadIdx.x >> 5]))
       continue;
     int o = 0;
@@ -494,10 +531,11 @@ int pv_main_launch(const PvMainParams& p_in, int max_tasks, int num_sms, cudaStr
   return 0;
 }
 
-int pv_push_launch(const char* pending, const int* pending_count, int k, const TopsView& tops, int dst,
-                   char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream) {
+int pv_push_launch(const char* pending, const int* pending_count, int k, const TopsView& tops, const Box* territory,
+                   const int* territory_count, int dst, char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream) {
   KNN_CUDA_TRY(cudaMemsetAsync(out_count, 0, sizeof(int), stream));
-  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, tops, dst, peer_inbox, out_count);
+  pv_push_kernel<<<num_sms * 8, 256, 0, stream>>>(pending, pending_count, k, tops, territory, territory_count, dst,
+                                                 peer_inbox, out_count);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;

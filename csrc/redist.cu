@@ -366,6 +366,60 @@ rd_return_kernel(const RdReturnParams p) {
   }
 }
 
+// Thread s decomposes rank s's key interval, in units of B bins (21 bits = 7 octree levels), into maximal
+// aligned cells and turns each into a box in world coordinates.
+__global__ void rd_territory_kernel(const uint64_t* __restrict__ split_keys, const unsigned* __restrict__ info_all, int R,
+                                    Box* __restrict__ cells, int* __restrict__ counts) {
+  const int s = threadIdx.x;
+  if (s >= R) return;
+  const KeyFrame f = key_frame(info_all, R);
+  const float ex = f.ivx > 0.f ? 1.f / f.ivx : 0.f, ey = f.ivy > 0.f ? 1.f / f.ivy : 0.f, ez = f.ivz > 0.f ? 1.f / f.ivz : 0.f;
+  const unsigned end_all = 1u << kBBits;
+  unsigned a = s == 0 ? 0u : (unsigned)(split_keys[s - 1] >> (kKeyBits - kBBits));
+  const unsigned b = s == R - 1 ? end_all : (unsigned)(split_keys[s] >> (kKeyBits - kBBits));
+  Box* out = cells + (size_t)s * kTerritoryCells;
+  int n = 0;
+  const int depth_max = kBBits / 3;                       // 7
+  while (a < b && n < kTerritoryCells) {
+    int j = 0;                                            // largest j: a is a multiple of 8^j and a + 8^j <= b
+    while (j < depth_max && (a & ((1u << (3 * (j + 1))) - 1u)) == 0u && a + (1u << (3 * (j + 1))) <= b) ++j;
+    const int d = depth_max - j;                          // octree depth of the cell
+    const unsigned prefix = a >> (3 * j);                 // 3 d bits: x y z interleaved, x highest
+    unsigned ix = 0, iy = 0, iz = 0;
+    for (int l = 0; l < d; ++l) {
+      const unsigned tri = (prefix >> (3 * (d - 1 - l))) & 7u;
+      ix = (ix << 1) | ((tri >> 2) & 1u);
+      iy = (iy << 1) | ((tri >> 1) & 1u);
+      iz = (iz << 1) | (tri & 1u);
+    }
+    // quantised coordinate q (21 bits) belongs to the cell iff q >> (21 - d) == i; q = floor(t * (2^21 - 1)),
+    // t = (x - lo) / extent. Two fine cells of slack on either side cover the rounding of that arithmetic.
+    const float scale = (float)(1u << (21 - d)) / 2097151.f;
+    const float slack = 2.f / 2097151.f;
+    Box c;
+    c.lox = f.lox + ((float)ix * scale - slack) * ex;  c.hix = f.lox + ((float)(ix + 1) * scale + slack) * ex;
+    c.loy = f.loy + ((float)iy * scale - slack) * ey;  c.hiy = f.loy + ((float)(iy + 1) * scale + slack) * ey;
+    c.loz = f.loz + ((float)iz * scale - slack) * ez;  c.hiz = f.loz + ((float)(iz + 1) * scale + slack) * ez;
+    // the outermost cells also own everything the clamping of t maps onto them
+    if (ix == 0) c.lox = -INFINITY;
+    if (iy == 0) c.loy = -INFINITY;
+    if (iz == 0) c.loz = -INFINITY;
+    if (ix + 1 == (1u << d)) c.hix = INFINITY;
+    if (iy + 1 == (1u << d)) c.hiy = INFINITY;
+    if (iz + 1 == (1u << d)) c.hiz = INFINITY;
+    c.cnt_bits = 0.f; c.pad = 0.f;
+    out[n++] = c;
+    a += 1u << (3 * j);
+  }
+  if (a < b) {                                            // cannot happen (<= 98 cells); stay conservative if it does
+    Box c;
+    c.lox = c.loy = c.loz = -INFINITY; c.hix = c.hiy = c.hiz = INFINITY; c.cnt_bits = 0.f; c.pad = 0.f;
+    out[0] = c;
+    n = 1;
+  }
+  counts[s] = n;
+}
+
 __global__ void rd_pack_info_kernel(const unsigned* __restrict__ bounds_ord, long long n, long long begin,
                                     unsigned* __restrict__ out) {
   const int t = threadIdx.x;
@@ -383,6 +437,14 @@ size_t rd_histB_offset() { return (size_t)kABins * sizeof(unsigned); }
 
 int rd_pack_info_launch(const unsigned* d_bounds_ord, int64_t n, int64_t begin, unsigned* d_out, cudaStream_t stream) {
   rd_pack_info_kernel<<<1, 32, 0, stream>>>(d_bounds_ord, (long long)n, (long long)begin, d_out);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+int rd_territory_launch(const uint64_t* d_split_keys, const unsigned* d_info_all, int R, Box* d_cells, int* d_counts,
+                        cudaStream_t stream) {
+  rd_territory_kernel<<<1, 32, 0, stream>>>(d_split_keys, d_info_all, R, d_cells, d_counts);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;
