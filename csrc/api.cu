@@ -136,8 +136,8 @@ static int index_create_impl(const float* d_xyz, int stride, int64_t n, const ui
   KNN_CUDA_TRY(cudaMallocAsync(&idx->d_bounds_ord, 6 * sizeof(unsigned), stream));
   KNN_CUDA_TRY(cudaMallocAsync(&idx->d_bounds6, 6 * sizeof(float), stream));
   KNN_CUDA_TRY(cudaMallocAsync(&idx->task_counter, sizeof(unsigned long long), stream));
-  KNN_CUDA_TRY(cudaMallocAsync(&idx->stats, 8 * sizeof(unsigned long long), stream));
-  KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
+  KNN_CUDA_TRY(cudaMallocAsync(&idx->stats, 16 * sizeof(unsigned long long), stream));
+  KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 16 * sizeof(unsigned long long), stream));
   int rc;
   if ((rc = bounds_init(idx->d_bounds_ord, stream))) return rc;
   if ((rc = bounds_accumulate(d_xyz, stride, n, idx->d_bounds_ord, stream))) return rc;
@@ -260,7 +260,7 @@ int b200knn_knn_self(b200knn_index* idx, int k, float max_radius, float* d_out, 
   p.home_n = idx->n;
   p.home_is_tree = 1;
   p.result_sorted = idx->result_sorted;
-  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 16 * sizeof(unsigned long long), stream));
   int rc;
   if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
   return scatter_results(idx->pts, idx->result_sorted, idx->n, idx->id_offset, d_out, stream);
@@ -298,7 +298,7 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   p.home_queries = qsorted;
   p.home_n = nq;
   p.result_sorted = rsorted;
-  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 16 * sizeof(unsigned long long), stream));
   if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
   if ((rc = scatter_results(qsorted, rsorted, nq, 0, d_out, stream))) return rc;
   keys.release();
@@ -442,6 +442,14 @@ int b200knn_index_stats(b200knn_index* idx, uint64_t out8[8]) {
   KNN_REQUIRE(idx && out8, "index_stats: NULL argument");
   unsigned long long h[8];
   KNN_CUDA_TRY(cudaMemcpy(h, idx->stats, sizeof(h), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < 8; ++i) out8[i] = h[i];
+  return 0;
+}
+
+int b200knn_index_stats_slowest(b200knn_index* idx, uint64_t out8[8]) {
+  KNN_REQUIRE(idx && out8, "index_stats_slowest: NULL argument");
+  unsigned long long h[8];
+  KNN_CUDA_TRY(cudaMemcpy(h, idx->stats + 8, sizeof(h), cudaMemcpyDeviceToHost));
   for (int i = 0; i < 8; ++i) out8[i] = h[i];
   return 0;
 }
@@ -614,7 +622,7 @@ int b200knn_ring_run(b200knn_ring* r, float max_radius, void* stream_) {
   // last hop of a group runs on the rank before its home: results go to the NEXT rank's array
   p.result_sorted = reinterpret_cast<float*>(nb + NL.result);
   r->seq_base += (unsigned)(r->C * r->world + 8);
-  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 16 * sizeof(unsigned long long), stream));
   return ring_launch(p, idx->num_sms, stream);
 }
 

@@ -270,7 +270,7 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.stats = idx->stats_on ? idx->stats : nullptr;
   int* out_count = reinterpret_cast<int*>(d->base + off_ocount);
   const int64_t my_groups = idx->groups();
-  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 8 * sizeof(unsigned long long), stream));
+  if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 16 * sizeof(unsigned long long), stream));
 
   // the per-chunk vote "does anybody have groups that must travel?" is a device-side all-gather of
   // the pending counters (B200KNN_HOST_VOTE=1: through the bootstrap, as a cross-check)

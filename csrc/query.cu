@@ -109,6 +109,7 @@ knn_ring_kernel_t(const RingParams p) {
     g.valid = lane < cnt;
 
     // ------------------------------------------------------------------ traverse the local tree
+    const long long clock_before = p.stats != nullptr ? clock64() : 0ll;
     if (cnt > 0 && p.tree.n > 0) {
       for (int i = k; i < kp; ++i) g.heap[i * 32] = -INFINITY;   // heap padding
       // seed = the level-1 node holding the group's own leaf (self queries at home), else the nearest (-2)
@@ -116,6 +117,18 @@ knn_ring_kernel_t(const RingParams p) {
       traverse_group_knn<SORTED>(p.tree, g, cnt, own_seed, k, (hop == 0 && p.fill) ? k / kGroup : 0);
     }
 
+    if (p.stats != nullptr) {
+      // diagnostics (b200knn_index_enable_stats): counters are flushed per group, and counter 7 keeps the slowest
+      // group as (kilo-cycles << 32) | group index, counters 8..13 what that group did
+      const unsigned long long kc = (unsigned long long)((clock64() - clock_before) >> 10);
+      const unsigned long long packed = (kc << 32) | (unsigned long long)(home_group & 0xffffffffll);
+      if (lane == 0 && atomicMax(p.stats + 7, packed) < packed) {
+        p.stats[8] = g.n_leaves; p.stats[9] = g.n_inner; p.stats[10] = g.n_flush;
+        p.stats[11] = g.n_fallback; p.stats[12] = g.n_purge; p.stats[13] = g.n_inserts;
+      }
+      flush_stats(g, p.stats);
+      g.n_leaves = g.n_inner = g.n_inserts = g.n_fallback = g.n_purge = g.n_flush = 0;
+    }
     // ------------------------------------------------------------------ output
     if (hop == R - 1) {
       if (g.valid) {

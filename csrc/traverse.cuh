@@ -457,6 +457,33 @@ __device__ __forceinline__ int find_seed_l1(const TreeView& t, const GroupCtx& g
 
 // Push the children [base, base+count) of `level` that lie inside the group radius. On overflow
 // (after purging stale entries) the children are handed to the frame stack instead.
+// The group-level test (group box against node box, largest radius of any lane) is what makes one warp's
+// walk serve 32 queries; it is also loose exactly when the group is not one compact thing: a group of two
+// clumps (a leaf at a joint of the Morton curve, or between two clusters) has a box that spans the space in
+// between, and everything in that space passes. Splitting such groups up front (traverse_group) only
+// catches the blatant cases — measured on clustered data: one group with a gap of 0.63 of its extent, just
+// under the splitting rule, kept a warp busy for 460 ms while the rest of the GPU idled. So whenever the
+// group's box is wide compared with its radius, children that pass the group-level test are confirmed by
+// the exact one: is the node's box inside the ball of at least one lane? (lane = query, one child at a
+// time). A compact group never pays for this; a loose one then costs what its lanes need, not what its
+// bounding box covers.
+__device__ __forceinline__ bool group_is_loose(const GroupCtx& g) {
+  const float e = fmaxf(g.ghx - g.glx, fmaxf(g.ghy - g.gly, g.ghz - g.glz));
+  return e * e > 4.f * g.maxR2;          // wider than two radii; never while the radius is still +inf
+}
+__device__ __forceinline__ unsigned confirm_children(const GroupCtx& g, unsigned pm, const float4& a, const float4& b) {
+  unsigned keep = 0u;
+  while (pm != 0u) {
+    const int bi = __ffs(pm) - 1;
+    pm &= pm - 1;
+    const float lb = point_box_lb(g.qx, g.qy, g.qz, __shfl_sync(kFullMask, a.x, bi), __shfl_sync(kFullMask, a.y, bi),
+                                  __shfl_sync(kFullMask, a.z, bi), __shfl_sync(kFullMask, b.x, bi),
+                                  __shfl_sync(kFullMask, b.y, bi), __shfl_sync(kFullMask, b.z, bi));
+    if (__any_sync(kFullMask, g.valid && (lb < g.top))) keep |= 1u << bi;
+  }
+  return keep;
+}
+
 // This lane's child box of the node whose children are [base, base+count) on `level` (zeros beyond count).
 __device__ __forceinline__ void load_child_box(const TreeView& t, int level, int base, int count, float4& a, float4& b) {
   a = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -475,8 +502,12 @@ __device__ __forceinline__ void frontier_expand(int level, int base, int count, 
   const int lane = lane_id();
   const bool have = lane < count;
   const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
-  const bool pass = have && (key < g.maxR2) && !(level == 1 && base + lane == seed_l1);
-  const unsigned mask = __ballot_sync(kFullMask, pass);
+  bool pass = have && (key < g.maxR2) && !(level == 1 && base + lane == seed_l1);
+  unsigned mask = __ballot_sync(kFullMask, pass);
+  if (mask != 0u && group_is_loose(g)) {
+    mask = confirm_children(g, mask, a, b);
+    pass = (mask >> lane) & 1u;
+  }
   const int np = __popc(mask);
   if (np == 0) return;
   const unsigned lt = (1u << lane) - 1u;
@@ -568,7 +599,12 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
   auto run_start = [&](int base, int count, const float4& a, const float4& b) {
     run_a = a; run_b = b; run_base = base;
     const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
-    run_key = (lane < count && key < g.maxR2) ? __float_as_uint(key) : 0xffffffffu;
+    bool pass = lane < count && key < g.maxR2;
+    if (group_is_loose(g)) {
+      const unsigned pm = __ballot_sync(kFullMask, pass);
+      if (pm != 0u) pass = (confirm_children(g, pm, a, b) >> lane) & 1u;
+    }
+    run_key = pass ? __float_as_uint(key) : 0xffffffffu;
     run_select();
   };
 
@@ -600,6 +636,8 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       const int child = B + who;
       __syncwarp();
       if (lane == 0) fr[depth * 4 + 3] = pm & ~(1u << who);
+      // a loose group confirms the chosen child with the exact test (one child per visit, not all of them)
+      if (group_is_loose(g) && confirm_children(g, 1u << who, a, b) == 0u) { __syncwarp(); continue; }
       if (L != 0) {
         ++g.n_inner;
         ++depth;
@@ -770,8 +808,8 @@ __device__ __forceinline__ void group_bounds(GroupCtx& g) {
 // group-level test and the lanes on the far side keep a huge radius until the random walk happens to
 // reach their real neighbourhood — measured: one such group runs for tens of milliseconds and, if it
 // is claimed late, the whole GPU waits for it (local phase of one rank 188 ms instead of 131 ms).
-// Fix: before traversing, cut the lane set at the largest gap along the widest axis whenever that gap
-// is more than two thirds of the extent, recursively, and traverse each coherent sub-group on its own
+// Fix: before traversing, cut the lane set at the largest gap along an axis whenever that gap is more
+// than two thirds of the extent along that axis, recursively, and traverse each coherent sub-group on its own
 // (the other lanes are simply not valid during that pass). Exactness is unaffected.
 // fill_leaves: see traverse(); pass k / 32 for a group whose heaps are all fresh, else 0.
 template <class LeafOp>
@@ -788,24 +826,39 @@ __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, i
     __syncwarp();
     g.valid = (m >> lane) & 1u;
     group_bounds(g);
-    // widest axis of this lane set, largest gap between consecutive coordinates along it
+    // Largest gap between consecutive coordinates along each axis: cut where a gap takes up more than two
+    // thirds of the set's extent along its axis (and is not negligible next to the widest extent) — the
+    // widest such gap if several axes qualify. 32 evenly spread points never qualify, nor do the mildly
+    // two-lobed leaves at the joints of a Morton run (cutting those costs a second walk over nearly the
+    // same leaves: tried, +13 % on uniform data); what qualifies is a set in two places, whose second
+    // place would otherwise start with a useless radius — the distance to the first.
     const float ex = g.ghx - g.glx, ey = g.ghy - g.gly, ez = g.ghz - g.glz;
-    const int axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
-    const float extent = axis == 0 ? ex : (axis == 1 ? ey : ez);
-    const float c = g.valid ? (axis == 0 ? g.qx : (axis == 1 ? g.qy : g.qz)) : INFINITY;
-    float succ = INFINITY;
+    const float emax = fmaxf(ex, fmaxf(ey, ez));
+    float best_gap = 0.f, best_c = 0.f;
+    int best_wl = -1;
+#pragma unroll
+    for (int axis = 0; axis < 3; ++axis) {
+      const float c = g.valid ? (axis == 0 ? g.qx : (axis == 1 ? g.qy : g.qz)) : INFINITY;
+      const float extent = axis == 0 ? ex : (axis == 1 ? ey : ez);
+      float succ = INFINITY;
 #pragma unroll 8
-    for (int j = 0; j < 32; ++j) {
-      const float cj = __shfl_sync(kFullMask, c, j);
-      if (cj > c) succ = fminf(succ, cj);
+      for (int j = 0; j < 32; ++j) {
+        const float cj = __shfl_sync(kFullMask, c, j);
+        if (cj > c) succ = fminf(succ, cj);
+      }
+      const float gap = (g.valid && succ < INFINITY) ? succ - c : 0.f;
+      const unsigned gbits = __float_as_uint(gap);
+      const unsigned gmax = __reduce_max_sync(kFullMask, gbits);
+      const float gm = __uint_as_float(gmax);
+      if (gm > best_gap && gm > 0.66f * extent && gm > 0.33f * emax) {     // warp-uniform
+        best_gap = gm;
+        best_wl = __ffs(__ballot_sync(kFullMask, gbits == gmax)) - 1;
+        best_c = c;
+      }
     }
-    const float gap = (g.valid && succ < INFINITY) ? succ - c : 0.f;
-    const unsigned gbits = __float_as_uint(gap);
-    const unsigned gmax = __reduce_max_sync(kFullMask, gbits);
-    if (__popc(m) >= 2 && nwork <= 6 && __uint_as_float(gmax) > 0.66f * extent) {
-      const int wl = __ffs(__ballot_sync(kFullMask, gbits == gmax)) - 1;
-      const float cut = __shfl_sync(kFullMask, c, wl);
-      const unsigned left = __ballot_sync(kFullMask, g.valid && c <= cut);
+    if (__popc(m) >= 2 && nwork <= 6 && best_wl >= 0) {
+      const float cut = __shfl_sync(kFullMask, best_c, best_wl);
+      const unsigned left = __ballot_sync(kFullMask, g.valid && best_c <= cut);
       const unsigned right = m & ~left;
       if (left != 0u && right != 0u) {
         if (lane == 0) { g.work[nwork] = right; g.work[nwork + 1] = left; }

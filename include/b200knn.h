@@ -110,6 +110,11 @@ int64_t b200knn_noalloc_scratch_bytes(void);
  * [3] inner nodes opened, [4] frontier overflows handled depth-first, [5] frontier purges. Role of CUKD_ENABLE_STATS (cukd/common.h:349-361). */
 int b200knn_index_stats(b200knn_index* idx, uint64_t out8[8]);
 int b200knn_index_enable_stats(b200knn_index* idx, int on);
+/* Diagnostics of the last query with stats enabled: out8[7] of b200knn_index_stats is the slowest query group as
+   (kilo-cycles << 32) | group index; this returns what that one group did: leaves swept, inner nodes opened,
+   list flushes, depth-first fallbacks, frontier purges, candidates accepted by its first lane, 0, 0.
+   (No counterpart in the reference; its CUKD_STATS counts traversal steps only, cukd/common.h:349-361.) */
+int b200knn_index_stats_slowest(b200knn_index* idx, uint64_t out8[8]);
 
 /* ---- multi-GPU fused ring ----------------------------------------------------------------------
  * One process per GPU. Query groups and their k-candidate heaps travel rank -> rank+1; every GPU's

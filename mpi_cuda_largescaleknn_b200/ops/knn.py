@@ -102,7 +102,18 @@ class KnnIndex:
         check(lib().b200knn_index_stats(self._h, out.ctypes.data))
         return {"leaves_visited": int(out[0]), "candidates": int(out[1]),
                 "heap_inserts": int(out[2]), "inner_nodes": int(out[3]),
-                "dfs_fallbacks": int(out[4]), "purges": int(out[5])}
+                "dfs_fallbacks": int(out[4]), "purges": int(out[5]), "list_flushes": int(out[6]),
+                "slowest_group_kcycles": int(out[7]) >> 32, "slowest_group": int(out[7]) & 0xffffffff,
+                "slowest_group_did": self._slowest()}
+
+    def _slowest(self) -> dict:
+        out = np.zeros(8, np.uint64)
+        fn = lib().b200knn_index_stats_slowest
+        fn.argtypes = [C.c_void_p, C.c_void_p]
+        fn.restype = C.c_int
+        check(fn(self._h, out.ctypes.data))
+        return {"leaves": int(out[0]), "inner": int(out[1]), "flushes": int(out[2]), "fallbacks": int(out[3]),
+                "purges": int(out[4]), "lane0_candidates": int(out[5])}
 
     def knn_self(self, k: int, max_radius: float = math.inf, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """k-th-neighbour distance of every indexed point, in the caller's original order."""

@@ -12,9 +12,14 @@ ap.add_argument("--n", type=int, default=4_000_000)
 ap.add_argument("--k", type=int, default=100)
 ap.add_argument("--reps", type=int, default=2)
 ap.add_argument("--stats", action="store_true")
+ap.add_argument("--kind", default="uniform", choices=["uniform", "clustered"])
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
-x = torch_uniform(a.n, dev, seed=1)
+if a.kind == "uniform":
+    x = torch_uniform(a.n, dev, seed=1)
+else:
+    from tools.run_configs import clustered_surface
+    x = clustered_surface(a.n, dev, 300)
 out = torch.empty(a.n, device=dev)
 ev = lambda: torch.cuda.Event(enable_timing=True)
 for rep in range(a.reps):
