@@ -469,19 +469,26 @@ __device__ __forceinline__ int find_seed_l1(const TreeView& t, const GroupCtx& g
 // bounding box covers.
 __device__ __forceinline__ bool group_is_loose(const GroupCtx& g) {
   const float e = fmaxf(g.ghx - g.glx, fmaxf(g.ghy - g.gly, g.ghz - g.glz));
-  return e * e > 4.f * g.maxR2;          // wider than two radii; never while the radius is still +inf
+  return e * e > 4.f * g.maxR2;          // wider than two radii (a compact leaf-sized group is about one to two
+                                         // radii wide for k >= 32); never while the radius is still +inf
 }
-__device__ __forceinline__ unsigned confirm_children(const GroupCtx& g, unsigned pm, const float4& a, const float4& b) {
+// Not inlined: it is the rare path, and three inlined copies of it made the kernel's hot loop a quarter longer
+// (instruction cache). All arguments travel in registers.
+__device__ __noinline__ unsigned confirm_children_call(float qx, float qy, float qz, float top, bool valid, unsigned pm,
+                                                       float ax, float ay, float az, float bx, float by, float bz) {
   unsigned keep = 0u;
   while (pm != 0u) {
     const int bi = __ffs(pm) - 1;
     pm &= pm - 1;
-    const float lb = point_box_lb(g.qx, g.qy, g.qz, __shfl_sync(kFullMask, a.x, bi), __shfl_sync(kFullMask, a.y, bi),
-                                  __shfl_sync(kFullMask, a.z, bi), __shfl_sync(kFullMask, b.x, bi),
-                                  __shfl_sync(kFullMask, b.y, bi), __shfl_sync(kFullMask, b.z, bi));
-    if (__any_sync(kFullMask, g.valid && (lb < g.top))) keep |= 1u << bi;
+    const float lb = point_box_lb(qx, qy, qz, __shfl_sync(kFullMask, ax, bi), __shfl_sync(kFullMask, ay, bi),
+                                  __shfl_sync(kFullMask, az, bi), __shfl_sync(kFullMask, bx, bi),
+                                  __shfl_sync(kFullMask, by, bi), __shfl_sync(kFullMask, bz, bi));
+    if (__any_sync(kFullMask, valid && (lb < top))) keep |= 1u << bi;
   }
   return keep;
+}
+__device__ __forceinline__ unsigned confirm_children(const GroupCtx& g, unsigned pm, const float4& a, const float4& b) {
+  return confirm_children_call(g.qx, g.qy, g.qz, g.top, g.valid, pm, a.x, a.y, a.z, b.x, b.y, b.z);
 }
 
 // This lane's child box of the node whose children are [base, base+count) on `level` (zeros beyond count).
@@ -836,12 +843,12 @@ __device__ __forceinline__ void traverse_group(const TreeView& t, GroupCtx& g, i
     const float emax = fmaxf(ex, fmaxf(ey, ez));
     float best_gap = 0.f, best_c = 0.f;
     int best_wl = -1;
-#pragma unroll
+#pragma unroll 1
     for (int axis = 0; axis < 3; ++axis) {
       const float c = g.valid ? (axis == 0 ? g.qx : (axis == 1 ? g.qy : g.qz)) : INFINITY;
       const float extent = axis == 0 ? ex : (axis == 1 ? ey : ez);
       float succ = INFINITY;
-#pragma unroll 8
+#pragma unroll 4
       for (int j = 0; j < 32; ++j) {
         const float cj = __shfl_sync(kFullMask, c, j);
         if (cj > c) succ = fminf(succ, cj);

@@ -27,6 +27,9 @@
 
 #define __CUDACC__ 1
 #define B200KNN_SIMT_HOST 1
+#ifndef __noinline__
+#define __noinline__ __attribute__((noinline))
+#endif
 #define __global__
 #define __device__
 #define __host__
