@@ -11,7 +11,9 @@ CXXFLAGS  := -O2 -std=c++17 -fPIC -ffp-contract=off -mfma -pthread -Iinclude -Ic
 BUILD     := build
 
 CU_SRCS   := csrc/radix_sort.cu csrc/build.cu csrc/query.cu csrc/pv.cu csrc/redist.cu csrc/api.cu csrc/dist.cu csrc/noalloc.cu csrc/neighbors.cu csrc/verify.cu
-CU_OBJS   := $(patsubst csrc/%.cu,$(BUILD)/%.o,$(CU_SRCS))
+# tcgen05 / TMA code: GPU library only (the host emulation below has no tensor cores to emulate)
+TC_SRCS   := csrc/brute_tile.cu
+CU_OBJS   := $(patsubst csrc/%.cu,$(BUILD)/%.o,$(CU_SRCS) $(TC_SRCS))
 CPP_OBJS  := $(BUILD)/cpu_engine.o
 
 LIB       := $(BUILD)/libb200knn.so

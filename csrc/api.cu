@@ -446,6 +446,18 @@ int b200knn_index_stats(b200knn_index* idx, uint64_t out8[8]) {
   return 0;
 }
 
+int b200knn_mempool_usage(int64_t* reserved_now, int64_t* used_high, int reset_high) {
+  int dev = 0;
+  KNN_CUDA_TRY(cudaGetDevice(&dev));
+  cudaMemPool_t pool;
+  KNN_CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, dev));
+  uint64_t v = 0;
+  if (reserved_now) { KNN_CUDA_TRY(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &v)); *reserved_now = (int64_t)v; }
+  if (used_high) { KNN_CUDA_TRY(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemHigh, &v)); *used_high = (int64_t)v; }
+  if (reset_high) { v = 0; KNN_CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrUsedMemHigh, &v)); }
+  return 0;
+}
+
 int b200knn_index_stats_slowest(b200knn_index* idx, uint64_t out8[8]) {
   KNN_REQUIRE(idx && out8, "index_stats_slowest: NULL argument");
   unsigned long long h[8];
@@ -512,6 +524,7 @@ int b200knn_ring_create(b200knn_index* idx, int rank, int world, int k, int64_t 
   r->mine = make_layout(k, world > 1 ? r->Gc : 1, max_groups * kGroup);
   KNN_CUDA_TRY(cudaMalloc(&r->base, r->mine.bytes));
   KNN_CUDA_TRY(cudaMemset(r->base, 0, r->mine.bytes));
+  KNN_CUDA_TRY(cudaDeviceSynchronize());   // zeroed before the handle is exported or a kernel on another stream polls a flag
   return 0;
 }
 

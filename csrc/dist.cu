@@ -104,7 +104,10 @@ int ensure_heap(b200knn_dist* d, size_t need) {
   close_heap(d);
   const size_t grow = need + need / 8;
   KNN_CUDA_TRY(cudaMalloc(&d->base, grow));
+  // the zeroing runs on the legacy default stream, the kernels that use the flags run on the caller's
+  // (possibly non-blocking) stream and on other GPUs: make it complete before anybody can see the heap
   KNN_CUDA_TRY(cudaMemset(d->base, 0, grow));
+  KNN_CUDA_TRY(cudaDeviceSynchronize());
   d->bytes = grow;
   d->peer[d->rank] = d->base;
   if (d->world > 1) {
@@ -139,8 +142,11 @@ constexpr size_t kHeapReserved = kCollDataOff + 2 * (size_t)kMaxRanks * kCollWor
 static_assert(2 * kMaxRanks * sizeof(unsigned) <= kCollDataOff - kCollFlagsOff, "collective flags overflow their area");
 static_assert(kHeapReserved % 256 == 0, "reserved area keeps the 256-byte alignment of what follows");
 
+// Exchange slots (pending + inbox) exist only when there is somebody to exchange with.
+inline int64_t pv_slots(int Gc, int R) { return R > 1 ? Gc : 1; }
+
 size_t pv_heap_need(int k, int Gc, int64_t max_groups, int R) {
-  return kHeapReserved + 2 * align256((size_t)Gc * pv_slot_bytes(k)) + 6 * 256 +
+  return kHeapReserved + 2 * align256((size_t)pv_slots(Gc, R) * pv_slot_bytes(k)) + 6 * 256 +
          align256((size_t)R * tops_capacity(max_groups) * sizeof(Box)) + align256((size_t)kMaxRanks * sizeof(TopHead));
 }
 
@@ -240,8 +246,8 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   }
 
   const size_t slot = pv_slot_bytes(k);
-  const size_t off_pending = d->alloc((size_t)pl.Gc * slot);
-  const size_t off_inbox = d->alloc((size_t)pl.Gc * slot);
+  const size_t off_pending = d->alloc((size_t)pv_slots(pl.Gc, R) * slot);
+  const size_t off_inbox = d->alloc((size_t)pv_slots(pl.Gc, R) * slot);
   const size_t off_pcount = d->alloc(4);
   const size_t off_icount = d->alloc(4);
   const size_t off_ocount = d->alloc(4);

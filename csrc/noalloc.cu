@@ -17,7 +17,9 @@
 //
 // Limits and rules
 //   * n <= B200KNN_NOALLOC_MAX_POINTS (262144). Larger inputs are rejected with an error, never
-//     truncated. k is limited as in the normal path (shared-memory heap, k <= 1790).
+//     truncated. k must fit the shared-memory candidate lists (k <= 1729); the normal path's fallback for
+//     larger k keeps its lists in a global scratch buffer that it allocates, so it is refused here — before
+//     anything is launched.
 //   * The array (about 11.9 MB) is held by every GPU that loads the library, until the process exits.
 //   * The first call on each device looks up the array's device address with cudaGetSymbolAddress
 //     (the name g_scratch in host code is only a stand-in and must never be handed to a kernel).
@@ -30,6 +32,7 @@
 //
 // This entry point has no counterpart in the reference.
 #include <string.h>
+#include <atomic>
 #include "common.cuh"
 #include "kernels.h"
 #include "../include/b200knn.h"
@@ -64,20 +67,24 @@ constexpr size_t kScratchBytes = kOffBox2 + a256(kLvl2 * sizeof(Box));
 static __device__ __align__(256) unsigned char g_scratch[kScratchBytes];
 
 constexpr int kMaxDevices = 64;
-unsigned char* g_scratch_addr[kMaxDevices] = {};   // device address of g_scratch, per device
+// device address of g_scratch, per device. Several host threads may make their first call at once: they all
+// look up the same address, so the race is benign, and the slot is atomic so that it is also well defined.
+std::atomic<unsigned char*> g_scratch_addr[kMaxDevices];
 
 // Set-up, once per device, with that device current.
 int scratch_address(unsigned char** out) {
   int dev = 0;
   KNN_CUDA_TRY(cudaGetDevice(&dev));
   KNN_REQUIRE(dev >= 0 && dev < kMaxDevices, "knn_self_noalloc: device ordinal out of range");
-  if (g_scratch_addr[dev] == nullptr) {
+  unsigned char* known = g_scratch_addr[dev].load(std::memory_order_acquire);
+  if (known == nullptr) {
     void* ptr = nullptr;
     KNN_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_scratch));
     KNN_REQUIRE(ptr != nullptr, "knn_self_noalloc: cudaGetSymbolAddress returned a null address");
-    g_scratch_addr[dev] = static_cast<unsigned char*>(ptr);
+    known = static_cast<unsigned char*>(ptr);
+    g_scratch_addr[dev].store(known, std::memory_order_release);
   }
-  *out = g_scratch_addr[dev];
+  *out = known;
   return 0;
 }
 
@@ -96,6 +103,9 @@ int b200knn_knn_self_noalloc(const float* d_xyz, int64_t n, int k, float max_rad
               "knn_self_noalloc: n exceeds B200KNN_NOALLOC_MAX_POINTS (262144); use b200knn_index_create + "
               "b200knn_knn_self for larger inputs");
   KNN_REQUIRE(k >= 1, "knn_self_noalloc: k must be >= 1");
+  KNN_REQUIRE(ring_pick_warps_per_cta(k) >= 1,
+              "knn_self_noalloc: k does not fit the shared-memory candidate lists (k <= 1729); larger k needs a "
+              "scratch allocation, use b200knn_index_create + b200knn_knn_self");
   if (n == 0) return 0;
   KNN_REQUIRE(d_xyz != nullptr && d_out != nullptr, "knn_self_noalloc: NULL point or output buffer");
 

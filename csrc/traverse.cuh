@@ -474,7 +474,12 @@ __device__ __forceinline__ bool group_is_loose(const GroupCtx& g) {
 }
 // Not inlined: it is the rare path, and three inlined copies of it made the kernel's hot loop a quarter longer
 // (instruction cache). All arguments travel in registers.
-__device__ __noinline__ unsigned confirm_children_call(float qx, float qy, float qz, float top, bool valid, unsigned pm,
+#if defined(B200KNN_SIMT_HOST)
+#define KNN_NOINLINE __attribute__((noinline))
+#else
+#define KNN_NOINLINE __noinline__
+#endif
+__device__ KNN_NOINLINE unsigned confirm_children_call(float qx, float qy, float qz, float top, bool valid, unsigned pm,
                                                        float ax, float ay, float az, float bx, float by, float bz) {
   unsigned keep = 0u;
   while (pm != 0u) {

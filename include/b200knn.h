@@ -115,6 +115,23 @@ int b200knn_index_enable_stats(b200knn_index* idx, int on);
    list flushes, depth-first fallbacks, frontier purges, candidates accepted by its first lane, 0, 0.
    (No counterpart in the reference; its CUKD_STATS counts traversal steps only, cukd/common.h:349-361.) */
 int b200knn_index_stats_slowest(b200knn_index* idx, uint64_t out8[8]);
+/* Leaf tiles on the tensor cores, as a measured experiment (csrc/brute_tile.cu; no
+   counterpart in the reference): for nq queries and np points, how many points lie below each query's threshold
+   (squared distance), and optionally which (masks: [nq][ceil(np/32)] words, bit j of word l = point 32 l + j).
+   _cuda is the product's exact CUDA-core sweep; _tc is TMA + tcgen05.mma kind::tf32 + TMEM with a conservative error
+   bound: its masks are supersets of the exact ones. _prep turns xyz into the [n][8] operand rows (re-centred on
+   `centre`) and norms that _tc takes. */
+int b200knn_brute_tile_prep(const float* d_xyz, int64_t n, const float centre[3], int is_query, float* d_rows8,
+                            float* d_norm, void* stream);
+int b200knn_brute_tile_cuda(const float* d_q_xyz, int64_t nq, const float* d_p_xyz, int np, const float* d_thr,
+                            unsigned* d_counts, unsigned* d_masks_or_null, void* stream);
+int b200knn_brute_tile_tc(float* d_q_rows8, const float* d_q_norm, int64_t nq, float* d_p_rows8, int np, float p_norm_max,
+                          const float* d_thr, unsigned* d_counts, unsigned* d_masks_or_null, int num_ctas, void* stream);
+/* The stream-ordered pool this library allocates from (the current device's default pool): bytes reserved right
+   now and the high-water mark of bytes in use; reset_high != 0 restarts the high-water mark at zero afterwards.
+   Lets a caller (and tests/test_zz_no_alloc.py) see whether a call allocated. Role of the reference's
+   GpuMemoryResource bookkeeping, cukd/helpers.h:31-71, which has no such query. */
+int b200knn_mempool_usage(int64_t* reserved_now, int64_t* used_high, int reset_high);
 
 /* ---- multi-GPU fused ring ----------------------------------------------------------------------
  * One process per GPU. Query groups and their k-candidate heaps travel rank -> rank+1; every GPU's

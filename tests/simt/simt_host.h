@@ -27,9 +27,6 @@
 
 #define __CUDACC__ 1
 #define B200KNN_SIMT_HOST 1
-#ifndef __noinline__
-#define __noinline__ __attribute__((noinline))
-#endif
 #define __global__
 #define __device__
 #define __host__
@@ -195,7 +192,7 @@ typedef void* cudaMemPool_t;
 enum cudaMemcpyKind { cudaMemcpyHostToHost, cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice, cudaMemcpyDefault };
 enum cudaDeviceAttr { cudaDevAttrMultiProcessorCount = 16 };
 enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize = 8 };
-enum cudaMemPoolAttr { cudaMemPoolAttrReleaseThreshold = 4 };
+enum cudaMemPoolAttr { cudaMemPoolAttrReleaseThreshold = 4, cudaMemPoolAttrReservedMemCurrent = 5, cudaMemPoolAttrUsedMemHigh = 8 };
 constexpr unsigned cudaIpcMemLazyEnablePeerAccess = 1;
 struct cudaIpcMemHandle_t { char reserved[64]; };
 struct cudaFuncAttributes { int numRegs = 0; size_t sharedSizeBytes = 0; int maxThreadsPerBlock = 1024; };
@@ -228,6 +225,7 @@ inline cudaError_t cudaSetDevice(int) { return cudaSuccess; }
 inline cudaError_t cudaDeviceGetAttribute(int* v, cudaDeviceAttr, int) { *v = 2; return cudaSuccess; }   // "2 SMs": small grids
 inline cudaError_t cudaDeviceGetDefaultMemPool(cudaMemPool_t* p, int) { *p = nullptr; return cudaSuccess; }
 inline cudaError_t cudaMemPoolSetAttribute(cudaMemPool_t, cudaMemPoolAttr, void*) { return cudaSuccess; }
+inline cudaError_t cudaMemPoolGetAttribute(cudaMemPool_t, cudaMemPoolAttr, void* v) { *static_cast<uint64_t*>(v) = 0; return cudaSuccess; }
 template <class F> inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute, int) { return cudaSuccess; }
 template <class F> inline cudaError_t cudaFuncGetAttributes(cudaFuncAttributes* a, F) { *a = cudaFuncAttributes(); return cudaSuccess; }
 template <class F> inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, F, int, size_t) { *n = 1; return cudaSuccess; }

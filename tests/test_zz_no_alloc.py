@@ -89,11 +89,28 @@ def test_noalloc_rejects_oversized_input_and_does_not_allocate():
     rc = L.b200knn_knn_self_noalloc(big.data_ptr(), 262145, 4, math.inf, out.data_ptr(), None)
     assert rc != 0
     assert b"B200KNN_NOALLOC_MAX_POINTS" in L.b200knn_last_error()
-    # warm call (first use may load kernels), then free memory must stay put across a call
+    # k beyond the shared-memory lists would need the allocating fallback: refused, and before anything runs
+    small = torch.from_numpy(gen.uniform(5_000, seed=5)).to(dev)
+    out_small = torch.zeros(5_000, dtype=torch.float32, device=dev)
+    rc = L.b200knn_knn_self_noalloc(small.data_ptr(), 5_000, 2000, math.inf, out_small.data_ptr(), None)
+    assert rc != 0 and b"does not fit" in L.b200knn_last_error()
+    # warm call (first use may load kernels), then neither the driver's free memory nor the library's
+    # stream-ordered pool may move across a call: the pool keeps freed blocks, so a cudaMallocAsync would
+    # not show in mem_get_info — it shows in the pool's high-water mark of bytes in use
+    L.b200knn_mempool_usage.argtypes = [C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_int]
+    L.b200knn_mempool_usage.restype = C.c_int
     x = torch.from_numpy(gen.uniform(100_000, seed=4)).to(dev)
     _noalloc(L, x, 10, math.inf)
     torch.cuda.synchronize()
+    reserved0, high0 = C.c_int64(), C.c_int64()
+    assert L.b200knn_mempool_usage(C.byref(reserved0), C.byref(high0), 1) == 0
     free_before, _ = torch.cuda.mem_get_info(dev)
     _noalloc(L, x, 10, math.inf)
+    rc = L.b200knn_knn_self_noalloc(small.data_ptr(), 5_000, 2000, math.inf, out_small.data_ptr(), None)
+    assert rc != 0
     free_after, _ = torch.cuda.mem_get_info(dev)
+    reserved1, high1 = C.c_int64(), C.c_int64()
+    assert L.b200knn_mempool_usage(C.byref(reserved1), C.byref(high1), 0) == 0
     assert free_after == free_before
+    assert reserved1.value == reserved0.value
+    assert high1.value == 0, "the call used the stream-ordered pool"
