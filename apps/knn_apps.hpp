@@ -214,6 +214,10 @@ bool gpu_available();
 // GPU path: points -> device, b200knn_dist_knn, results -> host.
 std::vector<float> run_gpu(Bootstrap& bs, const std::vector<float>& pts, int64_t global_begin, const Options& o,
                            int mode);
+// The same, reading the rank's slice [begin, begin + n) of a raw float3 file straight into device memory through
+// pinned double buffers (no pageable copy of the input).
+std::vector<float> run_gpu_from_file(Bootstrap& bs, const std::string& path, int64_t begin, int64_t n,
+                                     const Options& o, int mode);
 // CPU path (B200KNN_BACKEND=cpu or no CUDA device): every rank gathers all points through the
 // bootstrap and answers its own queries with the host mirror engine. For plumbing tests.
 std::vector<float> run_cpu(Bootstrap& bs, const std::vector<float>& pts, const Options& o);

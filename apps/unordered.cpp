@@ -14,14 +14,18 @@ int main(int ac, char** av) {
     const Options o = parse_args(ac, av, "input file name", "output file name");
     Bootstrap bs;
     int64_t begin = 0, total = 0;
-    std::vector<float> pts = read_points(o.input, bs.rank(), bs.size(), &begin, &total);
-    std::cout << "#" << bs.rank() << "/" << bs.size() << ": got " << pts.size() / 3 << " points to work on" << std::endl;
     std::vector<float> result;
     if (gpu_available()) {
+      total = count_points(o.input);
+      begin = total * bs.rank() / bs.size();
+      const int64_t n = total * (bs.rank() + 1) / bs.size() - begin;
+      std::cout << "#" << bs.rank() << "/" << bs.size() << ": got " << n << " points to work on" << std::endl;
       select_gpu(bs, o);
       const int mode = o.mode >= 0 ? o.mode : B200KNN_MODE_REDISTRIBUTE;
-      result = run_gpu(bs, pts, begin, o, mode);
+      result = run_gpu_from_file(bs, o.input, begin, n, o, mode);
     } else {
+      std::vector<float> pts = read_points(o.input, bs.rank(), bs.size(), &begin, &total);
+      std::cout << "#" << bs.rank() << "/" << bs.size() << ": got " << pts.size() / 3 << " points to work on" << std::endl;
       result = run_cpu(bs, pts, o);
     }
     if (bs.rank() == 0) std::cout << "done all queries..." << std::endl;

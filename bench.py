@@ -87,6 +87,49 @@ def run_reference(args) -> int:
     return bench_reference(args)
 
 
+def cli_file_to_file(rank: int, world: int, N: int, k: int, n_local: int, out_dev, dev):
+    """Wall clock of `knnrun -n world cudaMpiKNN_unorderedData in.float3 -o out.float -k K` (second of two runs,
+    page cache warm), with the output file compared against this process's own results. Rank 0 only."""
+    import subprocess
+    import numpy as np
+    import torch
+    from mpi_cuda_largescaleknn_b200.utils.generators import torch_uniform
+    if rank != 0:
+        return None
+    exe, run = ROOT / "build" / "cudaMpiKNN_unorderedData", ROOT / "build" / "knnrun"
+    if not exe.exists() or not run.exists():
+        return {"error": "build/knnrun or build/cudaMpiKNN_unorderedData missing (make apps)"}
+    tmp = Path("/dev/shm") if Path("/dev/shm").is_dir() else Path("/tmp")
+    inp, outp = tmp / f"b200knn_bench_{os.getpid()}.float3", tmp / f"b200knn_bench_{os.getpid()}.float"
+    try:
+        with open(inp, "wb") as f:
+            for r in range(world):
+                n_r = N * (r + 1) // world - N * r // world
+                f.write(torch_uniform(n_r, dev, seed=1234 + r).cpu().numpy().tobytes())
+        cmd = [str(run), "-n", str(world), str(exe), str(inp), "-o", str(outp), "-k", str(k)]
+        env = {kk: v for kk, v in os.environ.items() if kk not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_PORT")}
+        walls = []
+        for _ in range(2):
+            t0 = time.perf_counter()
+            p = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+            walls.append(time.perf_counter() - t0)
+            if p.returncode != 0:
+                return {"error": f"exit {p.returncode}: {p.stdout[-300:]}"}
+        got = np.fromfile(outp, dtype=np.float32, count=n_local)
+        same = bool(np.array_equal(got.view(np.uint32), out_dev.cpu().numpy().view(np.uint32)))
+        wall = walls[-1]
+        return {"value": N / wall, "unit": "queries/s", "wall_s": wall, "first_run_wall_s": walls[0],
+                "scope": "process start -> output file closed; input read from /dev/shm",
+                "output_equals_api_result": same,
+                "bytes_in": int(N) * 12, "bytes_out": int(N) * 4}
+    finally:
+        for f in (inp, outp):
+            try:
+                f.unlink()
+            except OSError:
+                pass
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -102,6 +145,8 @@ def main() -> int:
                     help="multi-GPU strategy (auto = redistribute: scatter to spatial owners + bbox-culled exchange)")
     ap.add_argument("--chunk-groups", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cli-e2e", action="store_true",
+                    help="skip the file -> file run of the command-line program (knnrun + cudaMpiKNN_unorderedData)")
     ap.add_argument("--verify", action="store_true", help="kept for old command lines: the check always runs")
     args = ap.parse_args()
 
@@ -124,6 +169,7 @@ def main() -> int:
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)
+    host_group = dist.new_group(backend="gloo") if world > 1 else None   # waits that must not occupy the GPUs
 
     from mpi_cuda_largescaleknn_b200.ops._lib import lib
     from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
@@ -228,6 +274,20 @@ def main() -> int:
                 e2e["prefetch_ms_per_step"] = pf_ms
         except Exception as e:  # noqa: BLE001
             e2e["prefetch_error"] = repr(e)[:200]
+
+    # The same work the way the reference is used: the command-line program, from process start to output file
+    # closed, input in /dev/shm (what `--impl reference` times as its e2e). Rank 0 writes the input and launches
+    # `knnrun -n <gpus> cudaMpiKNN_unorderedData`; the torchrun ranks wait at a barrier meanwhile.
+    cli = None
+    if e2e is not None and not args.no_cli_e2e:
+        try:
+            cli = cli_file_to_file(rank, world, N, k, n_local, out_dev, dev)
+        except Exception as e:  # noqa: BLE001
+            cli = {"error": repr(e)[:300]}
+        if world > 1:
+            dist.barrier(group=host_group)
+        if cli is not None:
+            e2e["cli_file_to_file"] = cli
 
     # Outside every timed region, at every GPU count: check 64 sampled results of the last step against ALL
     # points of all ranks with one counting pass (independent of index, lists and traversal). Collective:
