@@ -120,6 +120,13 @@ int b200knn_index_create_xyzw(const float* d_xyzw, int64_t n, uint32_t id_offset
   return index_create_impl(d_xyzw, 4, n, nullptr, id_offset, (cudaStream_t)stream_, out);
 }
 
+int b200knn_index_create_xy(const float* d_xy, int64_t n, const uint32_t* d_ids, uint32_t id_offset, void* stream_,
+                            b200knn_index** out) {
+  const int rc = index_create_impl(d_xy, 2, n, d_ids, id_offset, (cudaStream_t)stream_, out);
+  if (out && *out) (*out)->dims = 2;
+  return rc;
+}
+
 static int index_create_impl(const float* d_xyz, int stride, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
                              cudaStream_t stream, b200knn_index** out) {
   NvtxRange range("b200knn:index_build");
@@ -287,10 +294,10 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   KNN_CUDA_TRY(rsorted.alloc_bytes(groups * kGroup * sizeof(float)));
   int rc;
   // Order queries along the index's own Morton grid (queries outside its box clamp to the faces).
-  if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
+  if ((rc = morton_keys(d_queries, idx->dims == 2 ? 2 : 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
-  if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
+  if ((rc = gather_points(d_queries, idx->dims == 2 ? 2 : 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
   if ((rc = refine_runs(qsorted, nq, stream))) return rc;   // compact query groups, same as leaves
   RingParams p;
   fill_local_only(p, idx, k, max_radius);
@@ -339,10 +346,10 @@ int b200knn_knn_neighbors(b200knn_index* idx, const float* d_queries, int64_t nq
     KNN_CUDA_TRY(vals_tmp.alloc_bytes(nq * sizeof(uint32_t)));
     KNN_CUDA_TRY(scratch.alloc_bytes(radix_sort_scratch_bytes(nq)));
     KNN_CUDA_TRY(qsorted.alloc_bytes(groups * kGroup * sizeof(Float4)));
-    if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
+    if ((rc = morton_keys(d_queries, idx->dims == 2 ? 2 : 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
     int in_tmp = 0;
     if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
-    if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
+    if ((rc = gather_points(d_queries, idx->dims == 2 ? 2 : 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
     if ((rc = refine_runs(qsorted, nq, stream))) return rc;
   }
   RingParams p;
@@ -385,7 +392,20 @@ int b200knn_knn_neighbors(b200knn_index* idx, const float* d_queries, int64_t nq
 // Role of cukd::stackFree::fcp (cudaKDTree/cukd/fcp.h:210-254).
 int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, float max_radius, int32_t* d_out_ids,
                       float* d_out_dist, void* stream_) {
+  b200knn_fcp_params prm;
+  prm.max_radius = max_radius;
+  prm.eps = 0.f;
+  prm.far_node_inspect_budget = -1;
+  return b200knn_fcp_query_ex(idx, d_queries, nq, &prm, d_out_ids, d_out_dist, stream_);
+}
+
+// The same with the reference's FcpSearchParams (cukd/fcp.h:35-52): cutOffRadius, eps, far_node_inspect_budget.
+int b200knn_fcp_query_ex(b200knn_index* idx, const float* d_queries, int64_t nq, const b200knn_fcp_params* prm,
+                         int32_t* d_out_ids, float* d_out_dist, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
+  KNN_REQUIRE(prm, "fcp_query_ex: NULL parameters");
+  KNN_REQUIRE(prm->eps >= 0.f, "fcp_query_ex: eps must be >= 0");
+  const float max_radius = prm->max_radius;
   KNN_REQUIRE(idx && d_out_ids, "fcp_query: NULL argument");
   KNN_REQUIRE(nq >= 0 && nq < (int64_t)0x7fffffff - 64, "fcp_query: nq out of range");
   if (nq == 0) return 0;
@@ -403,10 +423,10 @@ int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, fl
   KNN_CUDA_TRY(rsorted.alloc_bytes(groups * kGroup * sizeof(float)));
   KNN_CUDA_TRY(ids_sorted.alloc_bytes(groups * kGroup * sizeof(uint32_t)));
   int rc;
-  if ((rc = morton_keys(d_queries, 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
+  if ((rc = morton_keys(d_queries, idx->dims == 2 ? 2 : 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
   if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
-  if ((rc = gather_points(d_queries, 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
+  if ((rc = gather_points(d_queries, idx->dims == 2 ? 2 : 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
   if ((rc = refine_runs(qsorted, nq, stream))) return rc;
   RingParams p;
   fill_local_only(p, idx, 1, max_radius);
@@ -415,6 +435,8 @@ int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, fl
   p.home_n = nq;
   p.result_sorted = rsorted;
   p.result_ids = ids_sorted;
+  p.tree.cull_scale = 1.f + prm->eps;
+  p.tree.node_budget = prm->far_node_inspect_budget;
   if ((rc = ring_launch(p, idx->num_sms, stream))) return rc;
   // ids are 32-bit payloads: the float scatter moves them unchanged
   if ((rc = scatter_results(qsorted, reinterpret_cast<const float*>(ids_sorted.get()), nq, 0,

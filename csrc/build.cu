@@ -24,7 +24,7 @@ k_bounds(const float* __restrict__ xyz, int fstride, int64_t n, unsigned* __rest
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
-      const float v = xyz[(size_t)fstride * i + a];
+      const float v = a < fstride ? xyz[(size_t)fstride * i + a] : 0.f;      // stride 2: planar points, z = 0
       lo[a] = fminf(lo[a], v);
       hi[a] = fmaxf(hi[a], v);
     }
@@ -64,7 +64,7 @@ k_morton(const float* __restrict__ xyz, int stride, int64_t n, const float* __re
   const float ivy = ey > 0.f ? 1.f / ey : 0.f;
   const float ivz = ez > 0.f ? 1.f / ez : 0.f;
   const size_t o = (size_t)stride * i;
-  keys[i] = morton63(xyz[o], xyz[o + 1], xyz[o + 2], lox, loy, loz, ivx, ivy, ivz);
+  keys[i] = morton63(xyz[o], xyz[o + 1], stride >= 3 ? xyz[o + 2] : 0.f, lox, loy, loz, ivx, ivy, ivz);
   vals[i] = (uint32_t)i;
 }
 
@@ -78,7 +78,7 @@ k_gather(const float* __restrict__ xyz, int stride, const uint32_t* __restrict__
   const size_t o = (size_t)stride * src;
   p.x = xyz[o];
   p.y = xyz[o + 1];
-  p.z = xyz[o + 2];
+  p.z = stride >= 3 ? xyz[o + 2] : 0.f;
   // stride 4: the id travels in .w of the input (redistributed points); else explicit ids or position
   p.w = stride == 4 ? xyz[o + 3] : __uint_as_float(ids ? ids[src] : src + id_offset);
   reinterpret_cast<float4*>(sorted)[i] = p;

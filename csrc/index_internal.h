@@ -9,6 +9,7 @@ namespace b200knn { int frontier_capacity(); }   // api.cu: 128, or B200KNN_QUEU
 
 struct b200knn_index {
   int device = 0;
+  int dims = 3;                            // 2: the index was built from [n][2] points (z = 0) and takes [nq][2] queries
   int num_sms = 148;
   int64_t n = 0;
   uint32_t id_offset = 0;
@@ -32,6 +33,8 @@ struct b200knn_index {
     t.levels = levels;
     t.n = (int)n;
     t.queue_cap = frontier_capacity();
+    t.cull_scale = 1.f;
+    t.node_budget = -1;
     return t;
   }
   int64_t groups() const { return div_up(n, kGroup); }

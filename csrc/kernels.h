@@ -28,6 +28,11 @@ struct TreeView {
   int levels;                   // number of levels in use (top level has <= 32 boxes)
   int n;                        // number of points
   int queue_cap;                // frontier entries a warp may use (<= 128; smaller only to test the overflow paths)
+  // Approximate search, role of FcpSearchParams::eps / far_node_inspect_budget and of the traversal's eps
+  // (cukd/fcp.h:35-52, cukd/traverse-stack-free.h:32,85). Exact search: 1.0f and -1.
+  float cull_scale;             // 1 + eps: a node is skipped when lower_bound * (1 + eps) >= current k-th distance
+  int node_budget;              // heap kernels (find-closest-point): after the seed neighbourhood, at most this many
+                                // further nodes (inner or leaf) are inspected per query group; < 0 = no limit
 };
 
 struct Bounds { float lo[3]; float hi[3]; };

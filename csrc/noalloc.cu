@@ -153,6 +153,8 @@ int b200knn_knn_self_noalloc(const float* d_xyz, int64_t n, int k, float max_rad
   }
   tree.levels = levels;
   tree.queue_cap = 128;
+  tree.cull_scale = 1.f;
+  tree.node_budget = -1;
   if ((rc = build_leaf_boxes(pts, n, box_level[0], stream))) return rc;
   for (int l = 1; l < levels; ++l)
     if ((rc = build_upper_boxes(box_level[l - 1], tree.count[l - 1], box_level[l], stream))) return rc;

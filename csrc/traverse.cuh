@@ -43,6 +43,7 @@ struct GroupCtx {
   int cnt;              // sorted mode: candidates in this lane's buffer
   int live;             // sorted mode: upper bound of the list entries that are not the sentinel any more
   bool flush_pending;   // sorted mode, warp-uniform: some lane's buffer cannot take another leaf
+  float cull_scale;     // 1 + eps of an approximate search (1 for the exact one), see TreeView
   int kp;               // rows of the candidate structure: padded heap size, or k + 1 in sorted mode
   bool valid;
   unsigned last_id;     // id of the most recently accepted candidate (find-closest-point uses it, k == 1)
@@ -386,7 +387,7 @@ __device__ __forceinline__ void append_leaf(const float4& p, GroupCtx& g) {
 // Exact per-query test against the leaf box; skip the leaf if no lane can improve.
 __device__ __forceinline__ void maybe_leaf(const float4& p, float lx, float ly, float lz,
                                            float hx, float hy, float hz, GroupCtx& g) {
-  const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
+  const float lb = g.cull_scale * point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
   if (__any_sync(kFullMask, g.valid && (lb < g.top))) process_leaf(p, g);
 }
 
@@ -409,7 +410,7 @@ struct SortedLeafOp {
   __device__ __forceinline__ void flush(GroupCtx& g) const { sorted_flush(g, k); }
   __device__ __forceinline__ void operator()(const float4& p, float lx, float ly, float lz, float hx,
                                              float hy, float hz, GroupCtx& g) const {
-    const float lb = point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
+    const float lb = g.cull_scale * point_box_lb(g.qx, g.qy, g.qz, lx, ly, lz, hx, hy, hz);
     if (__any_sync(kFullMask, g.valid && (lb < g.top))) append_leaf(p, g);
   }
 };
@@ -510,10 +511,12 @@ __device__ __forceinline__ void load_child_box(const TreeView& t, int level, int
 // (a, b) = this lane's child box, loaded by the caller (load_child_box) — early, so that the latency is
 // behind other work by the time the keys are needed.
 __device__ __forceinline__ void frontier_expand(int level, int base, int count, const float4& a, const float4& b,
-                                                int seed_l1, int qcap, int& qcount, int& depth, GroupCtx& g) {
+                                                int seed_l1, int qcap, float cull_scale, int& qcount, int& depth,
+                                                GroupCtx& g) {
   const int lane = lane_id();
   const bool have = lane < count;
-  const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
+  // keys are stored already multiplied by (1 + eps): every later comparison with the radius inherits it
+  const float key = cull_scale * box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
   bool pass = have && (key < g.maxR2) && !(level == 1 && base + lane == seed_l1);
   unsigned mask = __ballot_sync(kFullMask, pass);
   if (mask != 0u && group_is_loose(g)) {
@@ -603,6 +606,8 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
   unsigned run_key = 0xffffffffu;
   int run_base = 0, run_who = -1;              // run_who < 0: no run
 
+  g.cull_scale = t.cull_scale;
+  int budget = t.node_budget;                  // only consulted by unbuffered leaf ops (find-closest-point)
   auto run_select = [&]() {                    // nearest remaining leaf of the run; request its points
     const unsigned m = __reduce_min_sync(kFullMask, run_key);
     run_who = m == 0xffffffffu ? -1 : __ffs(__ballot_sync(kFullMask, run_key == m)) - 1;
@@ -610,7 +615,7 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
   };
   auto run_start = [&](int base, int count, const float4& a, const float4& b) {
     run_a = a; run_b = b; run_base = base;
-    const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
+    const float key = t.cull_scale * box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
     bool pass = lane < count && key < g.maxR2;
     if (group_is_loose(g)) {
       const unsigned pm = __ballot_sync(kFullMask, pass);
@@ -637,7 +642,7 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       const unsigned todo_in = fr[depth * 4 + 3];
       float4 a, b;
       load_child_box(t, L, B, Cn, a, b);
-      const float key = box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
+      const float key = t.cull_scale * box_box_lb(g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz, a.x, a.y, a.z, b.x, b.y, b.z);
       const bool pass = lane < Cn && ((todo_in >> lane) & 1u) && (key < g.maxR2) &&
                         !(L == 1 && B + lane == seed_l1);
       const unsigned pm = __ballot_sync(kFullMask, pass);
@@ -682,6 +687,9 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
       const float lz = __shfl_sync(kFullMask, run_a.z, who), hx = __shfl_sync(kFullMask, run_b.x, who);
       const float hy = __shfl_sync(kFullMask, run_b.y, who), hz = __shfl_sync(kFullMask, run_b.z, who);
       if (!(kw < __float_as_uint(g.maxR2))) { run_who = -1; continue; }   // nearest first: the rest is farther still
+      if constexpr (!LeafOp::kBuffered) {
+        if (started && t.node_budget >= 0 && --budget < 0) break;          // approximate search: inspection budget spent
+      }
       if (lane == who) run_key = 0xffffffffu;
       run_select();
       if (fill_leaves > 0) {
@@ -726,6 +734,9 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
 
     // ---- process the inner node selected one iteration ago
     if (cur_node != kNoNode) {
+      if constexpr (!LeafOp::kBuffered) {
+        if (t.node_budget >= 0 && --budget < 0) break;    // approximate search: inspection budget spent
+      }
       if (cur_key < __float_as_uint(g.maxR2)) {          // the radius may have shrunk since it was popped
         const int level = (int)(cur_node >> kNodeIdxBits);
         const int idx = (int)(cur_node & ((1u << kNodeIdxBits) - 1u));
@@ -733,7 +744,7 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         const int rem = t.count[level - 1] - idx * kFanout;
         const int count = rem < kFanout ? rem : kFanout;
         if (level == 1) run_start(idx * kFanout, count, cur_a, cur_b);
-        else frontier_expand(level - 1, idx * kFanout, count, cur_a, cur_b, seed_l1, t.queue_cap, qcount, depth, g);
+        else frontier_expand(level - 1, idx * kFanout, count, cur_a, cur_b, seed_l1, t.queue_cap, t.cull_scale, qcount, depth, g);
       }
     } else if (nx_node == kNoNode) {
       // nothing in flight and nothing left inside the radius
@@ -745,7 +756,7 @@ __device__ __forceinline__ void traverse(const TreeView& t, GroupCtx& g, int see
         float4 a, b;
         load_child_box(t, top_level, 0, t.count[top_level], a, b);
         if (top_level == 0) { if (seed_l1 < 0) run_start(0, t.count[0], a, b); }
-        else frontier_expand(top_level, 0, t.count[top_level], a, b, seed_l1, t.queue_cap, qcount, depth, g);
+        else frontier_expand(top_level, 0, t.count[top_level], a, b, seed_l1, t.queue_cap, t.cull_scale, qcount, depth, g);
         continue;
       }
       if constexpr (LeafOp::kBuffered) {
@@ -790,6 +801,7 @@ __device__ __forceinline__ void group_ctx_init(GroupCtx& g, float* smem, int war
   g.soa = reinterpret_cast<float*>(g.frames + 32);
   g.work = reinterpret_cast<unsigned*>(g.soa + 96);
   g.kp = kp;
+  g.cull_scale = 1.f;
   g.cnt = 0;
   g.live = k;
   g.flush_pending = false;

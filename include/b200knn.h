@@ -45,6 +45,12 @@ int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, u
  * the layout redistributed points arrive in. */
 int b200knn_index_create_xyzw(const float* d_xyzw, int64_t n, uint32_t id_offset, void* stream,
                               b200knn_index** out);
+
+/* Planar points: d_xy is [n][2] floats (the reference library's float2 trees, cukd/cukd-math.h:61-85,298-331). The
+ * index treats them as z = 0 — fmaf(0,0, fmaf(dx,dx, dy*dy)) is bit for bit the 2-D squared distance — and every
+ * query entry point of this index then takes [nq][2] queries. */
+int b200knn_index_create_xy(const float* d_xy, int64_t n, const uint32_t* d_ids_or_null, uint32_t id_offset,
+                            void* stream, b200knn_index** out);
 void b200knn_index_destroy(b200knn_index* idx);
 int64_t b200knn_index_num_points(const b200knn_index* idx);
 int b200knn_index_num_levels(const b200knn_index* idx);
@@ -70,6 +76,22 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
  * (cudaKDTree/cukd/fcp.h:210-254). Synchronises `stream`. */
 int b200knn_fcp_query(b200knn_index* idx, const float* d_queries, int64_t nq, float max_radius,
                       int32_t* d_out_ids, float* d_out_dist_or_null, void* stream);
+
+/* Find-closest-point with the reference's search parameters (cukd/fcp.h:35-52, FcpSearchParams):
+ *   max_radius               cutOffRadius: points farther than this are ignored (+inf: none)
+ *   eps                      approximate search: a subtree is skipped when its lower bound times (1 + eps) is not
+ *                            below the best distance so far, so the reported distance is at most (1 + eps)^(1/2)
+ *                            times the true one (0 = exact; role of the eps of cukd/traverse-stack-free.h:32,85)
+ *   far_node_inspect_budget  after the leaves next to the query, at most this many further tree nodes are
+ *                            inspected per group of 32 queries (< 0 = no limit; the reference counts "far"
+ *                            subtrees of its binary tree, here a node is a 32-ary box-tree node or a leaf) */
+typedef struct b200knn_fcp_params {
+  float max_radius;
+  float eps;
+  int32_t far_node_inspect_budget;
+} b200knn_fcp_params;
+int b200knn_fcp_query_ex(b200knn_index* idx, const float* d_queries, int64_t nq, const b200knn_fcp_params* params,
+                         int32_t* d_out_ids, float* d_out_dist, void* stream);
 /* knn_neighbors: the k nearest indexed points of every query — their ids (as fcp_query reports them)
  * and distances — in d_out_ids / d_out_dist, both [nq][k] row-major. Rows are NOT ordered by distance
  * (like the reference's heap-ordered candidate lists, cukd/knn.h:311-326); slots beyond the points

@@ -22,15 +22,18 @@ def _stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
-def _as_xyz(points: torch.Tensor) -> torch.Tensor:
-    """[N,3] float32 contiguous. [N,2] input (the reference library's float2 trees) gets z = 0: the squared
-    distance fmaf(0,0, fmaf(dx,dx, dy*dy)) is bit for bit the 2-D expression."""
+def _as_xyz(points: torch.Tensor, dims: int = 0) -> torch.Tensor:
+    """[N,3] (or, for a planar index, [N,2]) float32 contiguous. With ``dims`` = 0 an [N,2] input is padded with
+    z = 0 (entry points that only take float3); with ``dims`` = 2 or 3 the shape must match the index."""
     if points.dim() != 2 or points.shape[1] not in (2, 3):
         raise ValueError("points must have shape [N, 3] (or [N, 2])")
     if not points.is_cuda:
         raise ValueError("points must be a CUDA tensor (use utils.oracle for CPU work)")
     points = points.detach().to(torch.float32)
-    if points.shape[1] == 2:
+    if dims in (2, 3):
+        if points.shape[1] != dims:
+            raise ValueError(f"this index holds {dims}-D points; got [N, {points.shape[1]}]")
+    elif points.shape[1] == 2:
         points = torch.cat([points, points.new_zeros((points.shape[0], 1))], dim=1)
     return points.contiguous()
 
@@ -43,7 +46,8 @@ class KnnIndex:
     """
 
     def __init__(self, points: torch.Tensor, ids: Optional[torch.Tensor] = None, id_offset: int = 0):
-        xyz = _as_xyz(points)
+        self.dims = int(points.shape[1]) if points.dim() == 2 and points.shape[1] in (2, 3) else 3
+        xyz = _as_xyz(points, self.dims)          # [N,2] stays [N,2]: the C ABI indexes planar points natively
         self.device = xyz.device
         self.n = int(xyz.shape[0])
         self.id_offset = int(id_offset)
@@ -53,8 +57,13 @@ class KnnIndex:
             ids = ids.to(device=self.device, dtype=torch.int32).contiguous()
             ids_ptr = ids.data_ptr()
         with torch.cuda.device(self.device):
-            check(lib().b200knn_index_create(xyz.data_ptr() if self.n else None, self.n, ids_ptr,
-                                             self.id_offset, _stream_ptr(), C.byref(self._h)),
+            create = lib().b200knn_index_create
+            if self.dims == 2:
+                create = lib().b200knn_index_create_xy
+                create.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+                create.restype = C.c_int
+            check(create(xyz.data_ptr() if self.n else None, self.n, ids_ptr,
+                         self.id_offset, _stream_ptr(), C.byref(self._h)),
                   "index_create")
 
     def close(self) -> None:
@@ -126,7 +135,7 @@ class KnnIndex:
 
     def knn_query(self, queries: torch.Tensor, k: int, max_radius: float = math.inf) -> torch.Tensor:
         """k-th-neighbour distance of arbitrary query points against the indexed points."""
-        q = _as_xyz(queries)
+        q = _as_xyz(queries, self.dims)
         out = torch.empty(q.shape[0], dtype=torch.float32, device=self.device)
         with torch.cuda.device(self.device):
             check(lib().b200knn_knn_query(self._h, q.data_ptr() if q.shape[0] else None, int(q.shape[0]),
@@ -147,7 +156,7 @@ def neighbors(index: "KnnIndex", queries: Optional[torch.Tensor], k: int, max_ra
     if queries is None:
         nq, qptr = index.n, None
     else:
-        q = _as_xyz(queries)
+        q = _as_xyz(queries, index.dims)
         nq, qptr = int(q.shape[0]), (q.data_ptr() if q.shape[0] else None)
         if nq == 0:
             return (torch.empty((0, k), dtype=torch.int32, device=index.device),
@@ -230,15 +239,26 @@ def verify_sample(points: torch.Tensor, result: torch.Tensor, k: int, samples: i
     return {"queries": nq, "violations": int(bad.sum().item())}
 
 
-def fcp(index: "KnnIndex", queries: torch.Tensor, max_radius: float = math.inf):
+class _FcpParams(C.Structure):
+    _fields_ = [("max_radius", C.c_float), ("eps", C.c_float), ("far_node_inspect_budget", C.c_int32)]
+
+
+def fcp(index: "KnnIndex", queries: torch.Tensor, max_radius: float = math.inf, eps: float = 0.0,
+        far_node_inspect_budget: int = -1):
     """Find-closest-point: (ids int32 [nq], distances float32 [nq]) of the nearest indexed point of
-    every query; id -1 where nothing lies within ``max_radius``. Role of ``cukd::fcp``."""
-    q = _as_xyz(queries)
+    every query; id -1 where nothing lies within ``max_radius``. ``eps`` > 0 and ``far_node_inspect_budget`` >= 0
+    make the search approximate (the reported point is a real point, possibly not the nearest). Role of
+    ``cukd::fcp`` with ``FcpSearchParams`` (cukd/fcp.h:35-52)."""
+    q = _as_xyz(queries, index.dims)
     ids = torch.empty(q.shape[0], dtype=torch.int32, device=index.device)
     dist = torch.empty(q.shape[0], dtype=torch.float32, device=index.device)
+    prm = _FcpParams(float(max_radius), float(eps), int(far_node_inspect_budget))
+    fn = lib().b200knn_fcp_query_ex
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(_FcpParams), C.c_void_p, C.c_void_p, C.c_void_p]
+    fn.restype = C.c_int
     with torch.cuda.device(index.device):
-        check(lib().b200knn_fcp_query(index.handle, q.data_ptr() if q.shape[0] else None, int(q.shape[0]),
-                                      float(max_radius), ids.data_ptr(), dist.data_ptr(), _stream_ptr()), "fcp_query")
+        check(fn(index.handle, q.data_ptr() if q.shape[0] else None, int(q.shape[0]), C.byref(prm), ids.data_ptr(),
+                 dist.data_ptr(), _stream_ptr()), "fcp_query_ex")
     return ids, dist
 
 

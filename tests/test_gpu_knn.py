@@ -236,6 +236,53 @@ def test_ring_world1_and_baseline_world1_equal_self():
     idx.close()
 
 
+def test_planar_points_are_indexed_natively():
+    """[N,2] points through b200knn_index_create_xy (no padding on the Python side): self kNN, external queries and
+    find-closest-point equal the oracle run on the same points with z = 0."""
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex, fcp
+    xy = gen.uniform(40_000, seed=41)[:, :2].copy()
+    qy = gen.uniform(3_000, seed=42)[:, :2].copy()
+    pad = lambda a: np.concatenate([a, np.zeros((len(a), 1), np.float32)], axis=1)
+    idx = KnnIndex(torch.from_numpy(xy).to(_dev()))
+    assert idx.dims == 2
+    assert bit_equal(idx.knn_self(10).cpu().numpy(), bruteforce(pad(xy), k=10))
+    assert bit_equal(idx.knn_query(torch.from_numpy(qy).to(_dev()), 7).cpu().numpy(), bruteforce(pad(xy), queries=pad(qy), k=7))
+    ids, d = fcp(idx, torch.from_numpy(qy).to(_dev()))
+    assert bit_equal(d.cpu().numpy(), bruteforce(pad(xy), queries=pad(qy), k=1))
+    with pytest.raises(ValueError):
+        idx.knn_query(torch.from_numpy(gen.uniform(10, seed=1)).to(_dev()), 3)      # 3-D queries against a planar index
+    idx.close()
+
+
+def test_fcp_search_params_eps_and_inspection_budget():
+    """FcpSearchParams (cukd/fcp.h:35-52): eps > 0 may return a point up to sqrt(1 + eps) times farther than the
+    nearest, never nearer; a finite inspection budget returns real points whose distance is an upper bound; with
+    eps = 0 and no budget the result is the exact one."""
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex, fcp
+    x = gen.clustered_surface(60_000, seed=31)
+    q = gen.uniform(8_000, seed=32)
+    xd, qd = torch.from_numpy(x).to(_dev()), torch.from_numpy(q).to(_dev())
+    idx = KnnIndex(xd)
+    want = bruteforce(x, queries=q, k=1)
+    ids0, d0 = fcp(idx, qd, eps=0.0, far_node_inspect_budget=-1)
+    assert bit_equal(d0.cpu().numpy(), want)
+    for eps in (0.1, 1.0):
+        ids, d = fcp(idx, qd, eps=eps)
+        d, ids = d.cpu().numpy(), ids.cpu().numpy()
+        assert np.all(d >= want) and np.all(d <= want * np.float32(math.sqrt(1.0 + eps)) * np.float32(1.0001))
+        assert ids.min() >= 0
+        real = np.linalg.norm(x[ids[:500]].astype(np.float64) - q[:500].astype(np.float64), axis=1)
+        assert np.allclose(real, d[:500], rtol=1e-5, atol=1e-7)          # the reported point is at the reported distance
+    for budget in (0, 4):
+        ids, d = fcp(idx, qd, far_node_inspect_budget=budget)
+        d, ids = d.cpu().numpy(), ids.cpu().numpy()
+        found = ids >= 0
+        assert np.all(d[found] >= want[found])
+        real = np.linalg.norm(x[ids[found][:500]].astype(np.float64) - q[found][:500].astype(np.float64), axis=1)
+        assert np.allclose(real, d[found][:500], rtol=1e-5, atol=1e-7)
+    idx.close()
+
+
 def test_fcp_returns_closest_point_id_and_distance():
     """find-closest-point (cukd/fcp.h): id of the nearest indexed point + its distance, cut-off radius."""
     from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex, fcp
