@@ -80,13 +80,13 @@ void keep_pool_memory(int device) {
 
 // Convergent fill of fresh heaps (traverse.cuh::fill_leaf): on by default (measured 58.4 -> 54.5 ms for
 // 16 M points, k = 100); B200KNN_FILL=0 switches back to sifting every candidate.
-// Frontier entries per warp: all 128, unless B200KNN_QUEUE_CAP (32..128) shrinks it so that tests reach the
+// Frontier entries per warp: all 128, unless B200KNN_QUEUE_CAP (8..128) shrinks it so that tests reach the
 // purge and depth-first fallback paths with small inputs.
 int frontier_capacity() {
   static const int cap = [] {
     const char* e = getenv("B200KNN_QUEUE_CAP");
     const int v = e ? atoi(e) : 128;
-    return v < 32 ? 32 : (v > 128 ? 128 : v);
+    return v < 8 ? 8 : (v > 128 ? 128 : v);
   }();
   return cap;
 }
