@@ -112,7 +112,9 @@ def run_once(exe: Path, in_arg: str, out_arg: str, k: int, ranks: int, gpus: int
         shutil.rmtree(shim_dir, ignore_errors=True)
 
 
-def bench_reference(args) -> int:
+def bench_reference(args, variant: str = "unmodified") -> int:
+    """variant "unmodified": the reference as it is (what `--impl reference` runs, oversubscribed if n*k needs it).
+    variant "i64": the three-expression size_t patch (baseline/ref_i64.patch) at exactly one rank per GPU."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0      # the reference launch is driven by one process; torchrun's other ranks have nothing to do
@@ -125,7 +127,17 @@ def bench_reference(args) -> int:
     err = ensure_built()
     if err:
         return emit({"impl": "reference", "unavailable": err})
+    exe = EXE_UNORDERED
     ranks, n_rank, per_gpu = plan_ranks(n, k, gpus)
+    if variant == "i64":
+        exe = ROOT / "baseline" / "_ref" / "cudaMpiKNN_unorderedData_i64"
+        if not exe.exists():
+            out = subprocess.run(["bash", str(ROOT / "baseline" / "build_ref_i64.sh")], stdout=subprocess.PIPE,
+                                 stderr=subprocess.STDOUT, text=True, timeout=900)
+            if out.returncode != 0 or not exe.exists():
+                return emit({"impl": "reference-i64", "unavailable": "build failed: " + out.stdout[-300:].replace("\n", " ")})
+        ranks, n_rank = gpus, math.ceil(n / gpus)
+        per_gpu = n_rank * k * 8 + n_rank * 12 * 3 + n_rank * 24 + n_rank * 4 + (600 << 20)
     if per_gpu > GPU_BYTES:
         return emit({"impl": "reference", "n_gpus": gpus,
                      "unavailable": f"unmodified reference needs {ranks} ranks (int32 limit n*k<2^31) = "
@@ -141,13 +153,13 @@ def bench_reference(args) -> int:
     # A full reference run at the headline size takes minutes, so: run once; if that run was short
     # (< 60 s) treat it as the warm-up and time `steps` more runs, otherwise it IS the timed step.
     runs, steps_done, warm_done = [], 0, 0
-    first, why = run_once(EXE_UNORDERED, str(in_path), str(out_path), k, ranks, gpus, budget)
+    first, why = run_once(exe, str(in_path), str(out_path), k, ranks, gpus, budget)
     if first is None:
         return emit({"impl": "reference", "n_gpus": gpus, "unavailable": why})
     if first["wall_s"] < 60.0 and int(args.warmup) > 0:
         warm_done = 1
         for _ in range(max(1, int(args.steps))):
-            res, why = run_once(EXE_UNORDERED, str(in_path), str(out_path), k, ranks, gpus, budget)
+            res, why = run_once(exe, str(in_path), str(out_path), k, ranks, gpus, budget)
             if res is None:
                 return emit({"impl": "reference", "n_gpus": gpus, "unavailable": why})
             runs.append(res)
@@ -163,9 +175,11 @@ def bench_reference(args) -> int:
         "value": n / dev_s, "unit": "queries/s", "n_gpus": gpus, "steps": steps_done, "warmup": warm_done,
         "ms_per_step": dev_s * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "fp32", "data": "synthetic uniform-random float3 in the unit cube (file in /dev/shm)",
-        "impl": "reference",
+        "impl": "reference" if variant == "unmodified" else "reference-i64",
         "config": {"model": "unorderedDataVariant", "n_points": n, "k": k, "global_batch": n, "seq_len": k,
-                   "parallelism": f"mpi-shim ranks={ranks} (-g {gpus}; {ranks // gpus} per GPU, int32 limit n*k<2^31)",
+                   "parallelism": (f"mpi-shim ranks={ranks} (-g {gpus}; {ranks // gpus} per GPU, int32 limit n*k<2^31)"
+                                   if variant == "unmodified" else
+                                   f"mpi-shim ranks={ranks} (one per GPU; reference with baseline/ref_i64.patch)"),
                    "step": "file read + H2D + cukd::buildTree + all rounds of runQuery + extractFinalResult "
                            "(first MPI_Comm_size .. first MPI_Barrier, wall clock, max over ranks)",
                    "timing": "host wall clock marks in the MPI shim; the reference has no device timers"},

@@ -84,7 +84,7 @@ class ClockSampler(threading.Thread):
 
 def run_reference(args) -> int:
     from baseline.run_reference import bench_reference
-    return bench_reference(args)
+    return bench_reference(args, "i64" if args.impl == "reference-i64" else "unmodified")
 
 
 def cli_file_to_file(rank: int, world: int, N: int, k: int, n_local: int, out_dev, dev):
@@ -135,7 +135,8 @@ def main() -> int:
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-i64"],
+                    help="reference = the unmodified reference; reference-i64 = with baseline/ref_i64.patch, one rank per GPU")
     ap.add_argument("--num-points", dest="n", type=int, default=int(os.environ.get("B200KNN_BENCH_N", BASELINE_N)),
                     help="TOTAL number of points over all GPUs")
     ap.add_argument("--k", type=int, default=BASELINE_K)
@@ -150,7 +151,7 @@ def main() -> int:
     ap.add_argument("--verify", action="store_true", help="kept for old command lines: the check always runs")
     args = ap.parse_args()
 
-    if args.impl == "reference":
+    if args.impl in ("reference", "reference-i64"):
         return run_reference(args)
 
     import torch
