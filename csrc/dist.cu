@@ -145,9 +145,21 @@ static_assert(kHeapReserved % 256 == 0, "reserved area keeps the 256-byte alignm
 // Exchange slots (pending + inbox) exist only when there is somebody to exchange with.
 inline int64_t pv_slots(int Gc, int R) { return R > 1 ? Gc : 1; }
 
+// The one-round exchange (requests out, candidates back; pv.cu SERVE_FRESH / MERGE) runs whenever the lists are
+// sorted columns and a chunk's requests fit the areas below; otherwise that chunk takes the R - 1 sequential rounds.
+inline bool pv_one_round(int k, int R) { return R > 1 && pv_one_round_capable(k) && getenv("B200KNN_SEQ_EXCHANGE") == nullptr; }
+inline int64_t pv_cap_req(int Gc) {                                             // per (source, destination) pair
+  if (const char* e = getenv("B200KNN_REQ_CAP")) return std::max<int64_t>(1, atoll(e));   // tests: force the fallback
+  return std::max<int64_t>(256, Gc / 4);
+}
+inline int64_t pv_cap_ret(int Gc) { return std::max<int64_t>(256, Gc / 2); }    // per home rank
+
 size_t pv_heap_need(int k, int Gc, int64_t max_groups, int R) {
-  return kHeapReserved + 2 * align256((size_t)pv_slots(Gc, R) * pv_slot_bytes(k)) + 6 * 256 +
-         align256((size_t)R * tops_capacity(max_groups) * sizeof(Box)) + align256((size_t)kMaxRanks * sizeof(TopHead));
+  size_t need = kHeapReserved + 2 * align256((size_t)pv_slots(Gc, R) * pv_slot_bytes(k)) + 6 * 256 +
+                align256((size_t)R * tops_capacity(max_groups) * sizeof(Box)) + align256((size_t)kMaxRanks * sizeof(TopHead));
+  if (pv_one_round(k, R))
+    need += align256((size_t)R * pv_cap_req(Gc) * pv_request_bytes()) + align256((size_t)pv_cap_ret(Gc) * pv_return_bytes(k)) + 256;
+  return need;
 }
 
 // Device-side barrier over all ranks, enqueued on `stream` (replaces MPI_Barrier,
@@ -248,9 +260,17 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   const size_t slot = pv_slot_bytes(k);
   const size_t off_pending = d->alloc((size_t)pv_slots(pl.Gc, R) * slot);
   const size_t off_inbox = d->alloc((size_t)pv_slots(pl.Gc, R) * slot);
-  const size_t off_pcount = d->alloc(4);
+  const size_t off_pcount = d->alloc((1 + kMaxRanks) * sizeof(int));   // pending count, then requests posted per rank
   const size_t off_icount = d->alloc(4);
   const size_t off_ocount = d->alloc(4);
+  const bool one_round = pv_one_round(k, R);
+  const int64_t cap_req = pv_cap_req(pl.Gc), cap_ret = pv_cap_ret(pl.Gc);
+  size_t off_req = 0, off_ret = 0, off_retcount = 0;
+  if (one_round) {
+    off_req = d->alloc((size_t)R * cap_req * pv_request_bytes());
+    off_ret = d->alloc((size_t)cap_ret * pv_return_bytes(k));
+    off_retcount = d->alloc(4);
+  }
   KNN_REQUIRE(d->bump <= d->bytes, "symmetric heap too small (internal sizing error)");
 
   PvMainParams p;
@@ -274,6 +294,21 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   p.inbox_count = reinterpret_cast<const int*>(d->base + off_icount);
   p.task_counter = d->task_counter;
   p.stats = idx->stats_on ? idx->stats : nullptr;
+  if (one_round) {
+    p.fused = 1;
+    p.cap_req = cap_req;
+    p.cap_ret = cap_ret;
+    p.req_out_count = p.pending_count + 1;
+    p.my_req_inbox = d->base + off_req;
+    p.my_ret_area = d->base + off_ret;
+    p.my_ret_count = reinterpret_cast<const int*>(d->base + off_retcount);
+    for (int r = 0; r < R; ++r) {
+      p.req_inbox[r] = d->peer[r] + off_req;
+      p.ret_area[r] = d->peer[r] + off_ret;
+      p.ret_count[r] = reinterpret_cast<int*>(d->peer[r] + off_retcount);
+    }
+  }
+  const int vote_words = one_round ? 1 + R : 1;
   int* out_count = reinterpret_cast<int*>(d->base + off_ocount);
   const int64_t my_groups = idx->groups();
   if (idx->stats_on) KNN_CUDA_TRY(cudaMemsetAsync(idx->stats, 0, 16 * sizeof(unsigned long long), stream));
@@ -282,11 +317,13 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
   // the pending counters (B200KNN_HOST_VOTE=1: through the bootstrap, as a cross-check)
   const bool host_vote = getenv("B200KNN_HOST_VOTE") != nullptr;
   StreamBuf<int> d_votes(stream);
-  if (R > 1 && !host_vote) KNN_CUDA_TRY(d_votes.alloc_bytes((size_t)R * sizeof(int)));
+  if (R > 1 && !host_vote) KNN_CUDA_TRY(d_votes.alloc_bytes((size_t)R * vote_words * sizeof(int)));
 
   int rc;
   for (int c = 0; c < pl.C; ++c) {
-    KNN_CUDA_TRY(cudaMemsetAsync(p.pending_count, 0, sizeof(int), stream));
+    KNN_CUDA_TRY(cudaMemsetAsync(p.pending_count, 0, (size_t)vote_words * sizeof(int), stream));
+    // nobody adds to this counter before the vote below has seen every rank finish its local phase
+    if (one_round) KNN_CUDA_TRY(cudaMemsetAsync(d->base + off_retcount, 0, sizeof(int), stream));
     p.phase = 0;
     p.group_begin = (int64_t)c * pl.Gc;
     int64_t gc = my_groups - p.group_begin;
@@ -296,29 +333,57 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     if ((rc = pv_main_launch(p, p.group_count, idx->num_sms, stream))) return rc;
     if (R == 1) continue;
     // any work for the exchange at all? (one tiny allgather per chunk saves 2(R-1) fences when not)
-    int my_pending = 0;
-    std::vector<int> all_pending(R);
+    // votes[r * vote_words]: rank r's pending groups; [+ 1 + s]: requests rank r posted to rank s
+    std::vector<int> votes((size_t)R * vote_words), mine(vote_words);
     double tl1;
     if (host_vote) {
-      KNN_CUDA_TRY(cudaMemcpyAsync(&my_pending, p.pending_count, sizeof(int), cudaMemcpyDeviceToHost, stream));
+      KNN_CUDA_TRY(cudaMemcpyAsync(mine.data(), p.pending_count, (size_t)vote_words * sizeof(int), cudaMemcpyDeviceToHost, stream));
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
       tl1 = now_ms();
-      if (d->allgather(&my_pending, all_pending.data(), sizeof(int))) { set_last_error("bootstrap allgather failed"); return -3; }
+      if (d->allgather(mine.data(), votes.data(), (int64_t)vote_words * sizeof(int))) { set_last_error("bootstrap allgather failed"); return -3; }
+      // the device-side vote doubles as the fence that makes the posted requests visible; this one does not
+      if (one_round && (rc = device_barrier(d, stream))) return rc;
     } else {
-      if ((rc = device_collective(d, p.pending_count, 1, kCollGather, d_votes, stream))) return rc;
-      KNN_CUDA_TRY(cudaMemcpyAsync(all_pending.data(), d_votes, (size_t)R * sizeof(int), cudaMemcpyDeviceToHost, stream));
+      if ((rc = device_collective(d, p.pending_count, vote_words, kCollGather, d_votes, stream))) return rc;
+      KNN_CUDA_TRY(cudaMemcpyAsync(votes.data(), d_votes, votes.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
       tl1 = now_ms();
-      my_pending = all_pending[me];
     }
+    const int my_pending = votes[(size_t)me * vote_words];
     if (rep) rep->ms_local_phase += tl1 - tl0;
     trace.mark("exchange: local phase + vote");
     int64_t total_pending = 0;
-    for (int v : all_pending) total_pending += v;
+    for (int r = 0; r < R; ++r) total_pending += votes[(size_t)r * vote_words];
     if (rep) { rep->pending_groups += my_pending; rep->chunks += 1; }
     if (rep) rep->ms_host_collectives += now_ms() - tl1;
     if (total_pending == 0) continue;
     const double tr0 = now_ms();
+    // one round if every rank's requests fitted their areas (every host sees the same counts, so all agree)
+    bool fits = one_round;
+    for (int r = 0; r < R && fits; ++r) {
+      int64_t sent = 0;
+      for (int s = 0; s < R; ++s) {
+        const int v = votes[(size_t)r * vote_words + 1 + s];
+        if (v > cap_req) fits = false;
+        sent += v;
+      }
+      if (sent > cap_ret) fits = false;       // at most one return record per request
+    }
+    if (fits) {
+      int64_t to_serve = 0, sent = 0;
+      for (int s = 0; s < R; ++s) {
+        p.req_in[s] = votes[(size_t)s * vote_words + 1 + me];
+        to_serve += p.req_in[s];
+        sent += votes[(size_t)me * vote_words + 1 + s];
+      }
+      if ((rc = pv_fused_launch(p, 2, (int)to_serve, idx->num_sms, stream))) return rc;
+      if ((rc = device_barrier(d, stream))) return rc;
+      if ((rc = pv_fused_launch(p, 3, (int)sent, idx->num_sms, stream))) return rc;
+      if ((rc = pv_final_launch(p.pending, p.pending_count, k, idx->result_sorted, idx->num_sms, stream))) return rc;
+      if (rep) { rep->rounds += 1; KNN_CUDA_TRY(cudaStreamSynchronize(stream)); rep->ms_rounds += now_ms() - tr0; }
+      trace.mark("exchange: one round (serve, merge, final)");
+      continue;
+    }
     for (int j = 1; j < R; ++j) {
       const int dst = (me + j) % R, src = (me - j + R) % R;
       if ((rc = pv_push_launch(p.pending, p.pending_count, k, tops, territory, territory_count, dst,

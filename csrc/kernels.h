@@ -170,7 +170,24 @@ struct PvMainParams {
   char* src_pending;           // the visiting groups' home GPU's pending slots (peer pointer)
   unsigned long long* task_counter;
   unsigned long long* stats;
+  // One-round exchange (phases LOCAL with fused != 0, SERVE_FRESH, MERGE; sorted-list kernels only):
+  // LOCAL posts a REQUEST (32 queries with their current k-th distances, 528 bytes) to every rank a pending group
+  // reaches; every rank serves all requests it received in one pass, starting each from an empty list cut off at the
+  // lanes' k-th distances, and sends back only the candidates it found (RETURN record); home merges the returns.
+  int fused;
+  int64_t cap_req;              // requests per (source, destination) region
+  int64_t cap_ret;              // return records a rank can receive
+  char* req_inbox[kMaxRanks];   // rank s's request area [R][cap_req] (peer pointers); this rank writes region [rank]
+  int* req_out_count;           // [R] local: requests posted to each rank so far
+  const char* my_req_inbox;     // SERVE_FRESH: this rank's request area
+  int req_in[kMaxRanks];        // SERVE_FRESH: requests received from each rank (known to every host from the vote)
+  char* ret_area[kMaxRanks];    // rank h's return area [cap_ret] (peer pointers)
+  int* ret_count[kMaxRanks];    // rank h's return counter (incremented over NVLink by the servers)
+  const char* my_ret_area;      // MERGE
+  const int* my_ret_count;
 };
+KNN_HD size_t pv_request_bytes() { return 512 + 16; }
+KNN_HD size_t pv_return_bytes(int k) { return (size_t)k * 128 + 16; }
 int pv_main_launch(const PvMainParams& p, int max_tasks, int num_sms, cudaStream_t stream);
 int pv_push_launch(const char* pending, const int* pending_count, int k, const TopsView& tops, const Box* territory,
                    const int* territory_count, int dst, char* peer_inbox, int* out_count, int num_sms, cudaStream_t stream);
@@ -184,6 +201,8 @@ struct TopsPublishParams {
 };
 int64_t tops_capacity(int64_t max_groups);      // boxes a rank with at most max_groups leaves publishes (upper bound)
 int tops_publish_launch(const TopsPublishParams& p, int num_sms, cudaStream_t stream);
+bool pv_one_round_capable(int k);     // the sorted-list kernels serve this k (one-round exchange possible)
+int pv_fused_launch(const PvMainParams& p, int phase, int max_tasks, int num_sms, cudaStream_t stream);   // 2 = SERVE_FRESH, 3 = MERGE
 int pv_publish_launch(const int* out_count, int* peer_inbox_count, cudaStream_t stream);
 int pv_final_launch(const char* pending, const int* pending_count, int k, float* result_sorted, int num_sms,
                     cudaStream_t stream);

@@ -192,16 +192,19 @@ pv_main_kernel_t(const PvMainParams p) {
         if (g.valid) p.result_sorted[home_group * kGroup + lane] = finalize_kth(g.top);
         // does the group's ball still reach another rank's region? lane = one of that rank's boxes
         group_bounds(g);
-        bool need = false;
-        for (int s = 0; s < p.R && !need; ++s) {
+        // which ranks? (the sequential exchange only needs to know whether there is one)
+        unsigned reach = 0u;
+        for (int s = 0; s < p.R && (p.fused || reach == 0u); ++s) {
           if (s == p.rank) continue;
           if (p.territory != nullptr &&
               !reaches_territory(p.territory, p.territory_count, s, g.qx, g.qy, g.qz, g.top, g.valid, g.glx, g.gly, g.glz,
                                  g.ghx, g.ghy, g.ghz, g.maxR2))
             continue;
-          need = reaches_rank(p.tops, s, g.qx, g.qy, g.qz, g.top, g.valid, g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz,
-                              g.maxR2, g.qnode);
+          if (reaches_rank(p.tops, s, g.qx, g.qy, g.qz, g.top, g.valid, g.glx, g.gly, g.glz, g.ghx, g.ghy, g.ghz,
+                           g.maxR2, g.qnode))
+            reach |= 1u << s;
         }
+        const bool need = reach != 0u;
         if (need) {
           int slot_idx = 0;
           if (lane == 0) slot_idx = atomicAdd(p.pending_count, 1);
@@ -215,7 +218,22 @@ pv_main_kernel_t(const PvMainParams p) {
             meta[0] = (int)(home_group & 0xffffffffll);
             meta[1] = cnt;
             meta[2] = (int)(home_group >> 32);
-            meta[3] = 0;
+            meta[3] = 0;            // MERGE's lock word
+          }
+          // one-round exchange: a request to every rank the ball reaches — queries + their k-th distances
+          for (unsigned todo = p.fused ? reach : 0u; todo != 0u; todo &= todo - 1) {
+            const int dst = __ffs(todo) - 1;
+            int r_idx = 0;
+            if (lane == 0) r_idx = atomicAdd(p.req_out_count + dst, 1);
+            r_idx = __shfl_sync(kFullMask, r_idx, 0);
+            if (r_idx < p.cap_req) {
+              char* req = p.req_inbox[dst] + ((size_t)p.rank * p.cap_req + r_idx) * pv_request_bytes();
+              reinterpret_cast<float4*>(req)[lane] = make_float4(g.qx, g.qy, g.qz, g.top);
+              if (lane == 0) {
+                int* rmeta = reinterpret_cast<int*>(req + 512);
+                rmeta[0] = slot_idx; rmeta[1] = cnt; rmeta[2] = 0; rmeta[3] = 0;
+              }
+            }
           }
         }
       }
@@ -223,6 +241,109 @@ pv_main_kernel_t(const PvMainParams p) {
       // merge-back: improved heaps go straight into the home GPU's pending slot
       float* dst = slot_heap(p.src_pending + (size_t)home_slot * slot_bytes) + lane;
       for (int i = 0; i < k; ++i) dst[(size_t)i * 32] = g.heap[i * 32];
+    }
+    __syncwarp();
+  }
+  flush_stats(g, p.stats);
+}
+
+// ---- one-round exchange: SERVE_FRESH (PHASE 2) and MERGE (PHASE 3) --------------------------------------
+// SERVE_FRESH: every request received from any rank, in one pass (one tail instead of R - 1): the 32 queries start
+// from an EMPTY list whose sentinel is each lane's k-th distance at home — nothing at or beyond it can matter —
+// and walk the local tree; what they find (rows [k - found, k) of the sorted lists) goes back to the home GPU as a
+// RETURN record, the slot reserved by one atomic on the home GPU's counter over NVLink. A request that finds
+// nothing sends nothing.
+// MERGE: home appends every returned value that still beats the lane's k-th distance to the lane's buffer and
+// flushes — the same code path as a leaf. Several servers may answer the same group; a spin lock in the pending
+// slot's meta word serialises them (one to three returns per group, the holder never waits for anything).
+template <int PHASE>
+__global__ void __launch_bounds__(Q_MAX_WARPS * 32, 1)
+pv_fused_kernel_t(const PvMainParams p) {
+  extern __shared__ __align__(16) float q_smem[];
+  const int lane = lane_id();
+  const int k = p.k;
+  GroupCtx g;
+  group_ctx_init(g, q_smem, threadIdx.x >> 5, lane, k, nullptr, true);
+  const size_t slot_bytes = pv_slot_bytes(k);
+  int total = 0;
+  auto capped = [](int v, int64_t cap) { return v < (int)cap ? v : (int)cap; };
+  if (PHASE == 2) { for (int s = 0; s < p.R; ++s) total += capped(p.req_in[s], p.cap_req); }
+  else total = capped(ldcg_i(p.my_ret_count), p.cap_ret);
+
+  for (;;) {
+    unsigned long long t = 0;
+    if (lane == 0) t = atomicAdd(p.task_counter, 1ull);
+    t = __shfl_sync(kFullMask, t, 0);
+    if (t >= (unsigned long long)total) break;
+
+    if (PHASE == 2) {
+      int src = 0, idx = (int)t;
+      for (;; ++src) {                                    // which source's region does task t fall into
+        const int c = capped(p.req_in[src], p.cap_req);
+        if (idx < c) break;
+        idx -= c;
+      }
+      const char* req = p.my_req_inbox + ((size_t)src * p.cap_req + idx) * pv_request_bytes();
+      const float4 q = ldcg_f4(reinterpret_cast<const float4*>(req) + lane);
+      const int home_slot = ldcg_i(reinterpret_cast<const int*>(req + 512));
+      const int cnt = ldcg_i(reinterpret_cast<const int*>(req + 512) + 1);
+      g.qx = q.x; g.qy = q.y; g.qz = q.z;
+      g.valid = lane < cnt;
+      const float thr = g.valid ? q.w : -INFINITY;
+      for (int i = 0; i < k; ++i) g.heap[i * 32] = thr;
+      g.heap[k * 32] = -INFINITY;
+      g.top = thr;
+      g.live = 0;
+      if (cnt > 0 && p.tree.n > 0) traverse_group_knn<true>(p.tree, g, cnt, -2, k, 0);
+      const int found = (int)__reduce_max_sync(kFullMask, (unsigned)(g.valid ? g.live : 0));
+      if (found > 0) {
+        int r_idx = 0;
+        if (lane == 0) r_idx = atomicAdd_system(p.ret_count[src], 1);
+        r_idx = __shfl_sync(kFullMask, r_idx, 0);
+        if (r_idx < p.cap_ret) {
+          char* rec = p.ret_area[src] + (size_t)r_idx * pv_return_bytes(k);
+          float* dst = reinterpret_cast<float*>(rec) + lane;
+          for (int i = 0; i < found; ++i) dst[(size_t)i * 32] = g.heap[(k - found + i) * 32];
+          if (lane == 0) {
+            int* meta = reinterpret_cast<int*>(rec + (size_t)k * 128);
+            meta[0] = home_slot; meta[1] = found; meta[2] = p.rank; meta[3] = 0;
+          }
+        }
+      }
+    } else {
+      const char* rec = p.my_ret_area + (size_t)t * pv_return_bytes(k);
+      const int* rmeta = reinterpret_cast<const int*>(rec + (size_t)k * 128);
+      const int home_slot = ldcg_i(rmeta), found = ldcg_i(rmeta + 1);
+      char* slot = p.pending + (size_t)home_slot * slot_bytes;
+      int* lock = slot_meta(slot, k) + 3;
+      if (lane == 0) {
+        unsigned ns = 32;
+        while (atomicCAS(lock, 0, 1) != 0) { __nanosleep(ns); if (ns < 1024) ns <<= 1; }
+        __threadfence();
+      }
+      __syncwarp();
+      const int cnt = slot_meta(slot, k)[1];
+      g.valid = lane < cnt;
+      float* list = slot_heap(slot) + lane;
+      for (int i = 0; i < k; ++i) g.heap[i * 32] = __ldcg(list + (size_t)i * 32);
+      g.heap[k * 32] = -INFINITY;
+      g.top = g.heap[0];
+      g.live = k;
+      g.cnt = 0;
+      g.maxR2 = 0.f;
+      const float* src = reinterpret_cast<const float*>(rec) + lane;
+      const float top0 = g.valid ? g.top : -INFINITY;
+      for (int i = 0; i < found; ++i) {
+        const float v = ldcg_f(src + (size_t)i * 32);
+        if (v < top0) { g.buf[g.cnt * 32] = v; ++g.cnt; }      // sentinel rows of the server's list equal top0: dropped
+        if ((i & 31) == 31 || i == found - 1) {
+          __syncwarp();
+          if (__any_sync(kFullMask, g.cnt > 0)) sorted_flush(g, k);
+        }
+      }
+      for (int i = 0; i < k; ++i) list[(size_t)i * 32] = g.heap[i * 32];
+      __syncwarp();
+      if (lane == 0) { __threadfence(); atomicExch(lock, 0); }
     }
     __syncwarp();
   }
@@ -528,6 +649,29 @@ int pv_main_launch(const PvMainParams& p_in, int max_tasks, int num_sms, cudaStr
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   KNN_CUDA_TRY(cudaFreeAsync(heaps, stream));
+  return 0;
+}
+
+bool pv_one_round_capable(int k) { return use_sorted_list(k); }
+
+int pv_fused_launch(const PvMainParams& p_in, int phase, int max_tasks, int num_sms, cudaStream_t stream) {
+  PvMainParams p = p_in;
+  KNN_REQUIRE(use_sorted_list(p.k), "one-round exchange needs the sorted-list kernels");
+  KNN_REQUIRE(phase == 2 || phase == 3, "pv_fused_launch: phase must be 2 or 3");
+  auto kernel = phase == 2 ? pv_fused_kernel_t<2> : pv_fused_kernel_t<3>;
+  const int warps = group_pick_warps(p.k, (const void*)kernel, true);
+  KNN_REQUIRE(warps >= 1, "pv fused kernel: k does not fit in shared memory");
+  const size_t smem = group_smem_bytes(p.k, warps, true);
+  KNN_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  KNN_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, warps * 32, smem));
+  KNN_REQUIRE(occ >= 1, "pv fused kernel does not fit on an SM");
+  if (max_tasks <= 0) return 0;
+  const long long want = ((long long)max_tasks + warps - 1) / warps, cap = (long long)num_sms * occ;
+  KNN_CUDA_TRY(cudaMemsetAsync(p.task_counter, 0, sizeof(unsigned long long), stream));
+  kernel<<<(int)(want < cap ? want : cap), warps * 32, smem, stream>>>(p);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
   return 0;
 }
 

@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 import sys
 import threading
 from pathlib import Path
@@ -132,6 +133,12 @@ def main() -> int:
                 if not bit_equal(out, ref):
                     bad = int((out.view(np.uint32) != ref.view(np.uint32)).sum())
                     fail(f"[rank {rank}] {name}/{mode}: {bad} of {len(x)} results differ from the oracle")
+                # which exchange ran: one round per chunk, or world - 1 sequential rounds (B200KNN_EXPECT_ROUNDS)
+                expect = os.environ.get("B200KNN_EXPECT_ROUNDS")
+                if expect and mode in ("prepartitioned", "redistribute") and rep.chunks == 1:
+                    want = 1 if expect == "one" else world - 1
+                    if rep.rounds != want:
+                        fail(f"[rank {rank}] {name}/{mode}: {rep.rounds} exchange rounds, expected {want}")
             if rank == 0:
                 print(f"case {name}: N={N} k={k} r={r} gc={gc} done", flush=True)
         lib.b200knn_dist_destroy(eng)

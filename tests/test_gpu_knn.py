@@ -236,6 +236,25 @@ def test_ring_world1_and_baseline_world1_equal_self():
     idx.close()
 
 
+def test_against_plain_torch_fp32_brute_force():
+    """An oracle that shares no code with the library (not even knn_math.h): squared distances from plain torch fp32
+    elementwise arithmetic, k-th smallest by torch.topk. torch rounds x*x + y*y + z*z differently from the library's
+    fmaf chain, so the comparison uses the tolerance of the reference's own verifyKNN
+    (cudaKDTree/testing/floatN-knn-and-fcp.cu:315-323): relative 1e-6."""
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
+    for n, k, kind in ((6000, 10, "uniform"), (5000, 100, "uniform"), (7000, 32, "clustered")):
+        x = gen.uniform(n, seed=n) if kind == "uniform" else gen.clustered_surface(n, seed=n)
+        xd = torch.from_numpy(x).to(_dev())
+        diff = xd[:, None, :] - xd[None, :, :]
+        d2 = (diff * diff).sum(dim=2)
+        want = torch.sqrt(torch.topk(d2, k, dim=1, largest=False).values[:, k - 1])
+        idx = KnnIndex(xd)
+        got = idx.knn_self(k)
+        idx.close()
+        rel = (got - want).abs() / torch.maximum(want, torch.tensor(1e-30, device=_dev()))
+        assert float(rel.max().item()) <= 1e-6 or float((got - want).abs().max().item()) <= 1e-9, (n, k, float(rel.max().item()))
+
+
 def test_planar_points_are_indexed_natively():
     """[N,2] points through b200knn_index_create_xy (no padding on the Python side): self kNN, external queries and
     find-closest-point equal the oracle run on the same points with z = 0."""

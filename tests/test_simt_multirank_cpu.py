@@ -28,6 +28,19 @@ def test_emulated_ranks_every_mode_equals_oracle(built, world, cases):
     assert out.returncode == 0 and "MULTIRANK_OK" in out.stdout, out.stdout[-4000:]
 
 
+@pytest.mark.parametrize("env,expect", [({}, "one"), ({"B200KNN_SEQ_EXCHANGE": "1"}, "sequential"),
+                                        ({"B200KNN_REQ_CAP": "1"}, "sequential")])
+def test_emulated_one_round_exchange_and_its_fallbacks(built, env, expect):
+    """The culled exchange normally takes ONE round per chunk (requests out, candidates back, merged at home);
+    it falls back to world - 1 sequential rounds when switched off or when a chunk's requests do not fit their
+    area. All three must give the oracle's bits, and the report must show which one ran."""
+    import os
+    out = subprocess.run([sys.executable, str(ROOT / "tests" / "simt" / "multirank_worker.py"), "3", "radius", "clustered"],
+                         cwd=str(ROOT), env=dict(os.environ, B200KNN_EXPECT_ROUNDS=expect, **env),
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert out.returncode == 0 and "MULTIRANK_OK" in out.stdout, out.stdout[-4000:]
+
+
 def test_emulated_ranks_are_race_free_under_thread_sanitizer(built):
     """Race detection for the protocols BETWEEN ranks (ring flags and credits, device barriers, device
     collectives, peer stores ordered by host barriers): the emulated library is compiled with
