@@ -289,7 +289,8 @@ pv_fused_kernel_t(const PvMainParams p) {
       const int cnt = ldcg_i(reinterpret_cast<const int*>(req + 512) + 1);
       g.qx = q.x; g.qy = q.y; g.qz = q.z;
       g.valid = lane < cnt;
-      const float thr = g.valid ? q.w : -INFINITY;
+      // idle lanes: a list of zeros takes nothing and, unlike -inf, cannot be mistaken for the column's terminator
+      const float thr = g.valid ? q.w : 0.f;
       for (int i = 0; i < k; ++i) g.heap[i * 32] = thr;
       g.heap[k * 32] = -INFINITY;
       g.top = thr;
@@ -342,8 +343,9 @@ pv_fused_kernel_t(const PvMainParams p) {
         }
       }
       for (int i = 0; i < k; ++i) list[(size_t)i * 32] = g.heap[i * 32];
+      __threadfence();                       // every lane's column is out before lane 0 opens the lock
       __syncwarp();
-      if (lane == 0) { __threadfence(); atomicExch(lock, 0); }
+      if (lane == 0) atomicExch(lock, 0);
     }
     __syncwarp();
   }

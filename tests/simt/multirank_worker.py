@@ -89,8 +89,9 @@ def main() -> int:
              ("radius", 1800 * world, 32, 0.08, 0, "uniform"),
              ("clustered", 2000 * world, 10, math.inf, 0, "clustered"),
              ("tiny", world * 3 + 1, 5, math.inf, 0, "uniform"),
-             ("hugek", 1300 * world, 1900, math.inf, 0, "uniform")]     # heaps in global memory, every group travels
-    cases = [c for c in cases if (c[0] in wanted if wanted else c[0] != "hugek")]
+             ("hugek", 1300 * world, 1900, math.inf, 0, "uniform"),     # heaps in global memory, every group travels
+             ("manyreturns", 3000 * world + 1, 100, math.inf, 16, "uniform")]   # unpartitioned: every group asks every rank
+    cases = [c for c in cases if (c[0] in wanted if wanted else c[0] not in ("hugek", "manyreturns"))]
 
     def rank_main(rank):
         bs, keep = w.bootstrap(rank)

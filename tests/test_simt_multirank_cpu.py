@@ -20,7 +20,7 @@ def built():
     assert out.returncode == 0, out.stdout[-3000:]
 
 
-@pytest.mark.parametrize("world,cases", [(2, ["chunks", "tiny", "hugek"]), (3, ["radius", "clustered"]), (8, ["uniform"]),
+@pytest.mark.parametrize("world,cases", [(2, ["chunks", "tiny", "hugek"]), (3, ["radius", "clustered", "manyreturns"]), (8, ["uniform"]),
                                          (16, ["tiny"])])      # 16 = B200KNN_MAX_RANKS, more than any box has GPUs
 def test_emulated_ranks_every_mode_equals_oracle(built, world, cases):
     out = subprocess.run([sys.executable, str(ROOT / "tests" / "simt" / "multirank_worker.py"), str(world), *cases],
