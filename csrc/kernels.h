@@ -235,36 +235,7 @@ struct DevCollParams {
 };
 int dev_collective_launch(const DevCollParams& p, cudaStream_t stream);
 
-struct RedistributeParams {
-  const float* xyz;            // local points, caller order
-  const uint32_t* order;       // order[i] = caller index of the i-th point in global Morton order
-  int64_t n;
-  int64_t global_begin;        // global index of local point 0
-  int R;
-  int64_t cut[kMaxRanks + 1];  // destination d takes sorted positions [cut[d], cut[d+1])
-  Float4* recv[kMaxRanks];     // destination receive buffers (peer pointers)
-  int64_t recv_offset[kMaxRanks];   // where this rank's run starts inside recv[d]
-};
-int redistribute_launch(const RedistributeParams& p, cudaStream_t stream);
-
-struct PushPairsParams {
-  const uint32_t* ids;         // local results sorted by global id
-  const uint32_t* vals;        // float bits
-  int64_t n;
-  int R;
-  int64_t cut[kMaxRanks + 1];  // owner o takes sorted positions [cut[o], cut[o+1])
-  uint2* dst[kMaxRanks];       // owners' staging areas (peer pointers)
-  int64_t dst_offset[kMaxRanks];    // where this rank's run starts inside dst[o]
-};
-int extract_pairs_launch(const Float4* pts, const float* res, int64_t n, uint32_t* ids, uint32_t* vals,
-                         cudaStream_t stream);
-int lower_bounds32_launch(const uint32_t* sorted_ids, int64_t n, const int64_t* d_begins, int count, int64_t* out,
-                          cudaStream_t stream);
-int push_pairs_launch(const PushPairsParams& p, cudaStream_t stream);
 int scatter_pairs_launch(const void* pairs, int64_t n, int64_t begin, float* out, cudaStream_t stream);
-int sample_keys_launch(const uint64_t* sorted_keys, int64_t n, int samples, uint64_t* out, cudaStream_t stream);
-int lower_bounds_launch(const uint64_t* sorted_keys, int64_t n, const uint64_t* splitters, int count,
-                        int64_t* out, cudaStream_t stream);
 
 // ---------------- sort-free redistribution (redist.cu) ----------------
 constexpr int kRdInfoWords = 10;   // per rank: bounds (6 order-preserving uints), n (2 words), global begin (2 words)

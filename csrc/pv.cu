@@ -479,61 +479,7 @@ pv_final_kernel(const char* __restrict__ pending, const int* __restrict__ pendin
   }
 }
 
-// ---- redistribution ---------------------------------------------------------------------------
-// Local points are already ordered by global Morton key, so each destination's share is one
-// contiguous run [cut[d], cut[d+1]). Thread i writes point order[i] (with its global id) into the
-// destination GPU's receive buffer: coalesced 16-byte peer stores within each run.
-__global__ void __launch_bounds__(256)
-redistribute_kernel(const RedistributeParams p) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= p.n) return;
-  int d = 0;
-  while (d + 1 < p.R && i >= p.cut[d + 1]) ++d;
-  const uint32_t src = p.order[i];
-  float4 v;
-  v.x = p.xyz[3 * (size_t)src];
-  v.y = p.xyz[3 * (size_t)src + 1];
-  v.z = p.xyz[3 * (size_t)src + 2];
-  v.w = __uint_as_float((uint32_t)(p.global_begin + src));
-  reinterpret_cast<float4*>(p.recv[d])[p.recv_offset[d] + (i - p.cut[d])] = v;
-}
-
 // ---- result return ------------------------------------------------------------------------------
-// Results are (global id, value) pairs. Scattering them one by one into the owners' arrays is 4-byte
-// random peer stores (measured: 1.0 s for 125 M results per GPU). Instead: sort the pairs by id (the
-// owners' id ranges are contiguous, so each owner's share becomes one run), push every run as
-// contiguous 8-byte pairs into the owner's staging area, and let the owner scatter locally.
-__global__ void __launch_bounds__(256)
-extract_pairs_kernel(const Float4* __restrict__ pts, const float* __restrict__ res, int64_t n,
-                     uint32_t* __restrict__ ids, uint32_t* __restrict__ vals) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  ids[i] = __float_as_uint(pts[i].w);
-  vals[i] = __float_as_uint(res[i]);
-}
-
-__global__ void lower_bounds32_kernel(const uint32_t* __restrict__ sorted_ids, int64_t n,
-                                      const int64_t* __restrict__ begins, int count, int64_t* __restrict__ out) {
-  const int j = threadIdx.x;
-  if (j >= count) return;
-  const int64_t s = begins[j];
-  int64_t lo = 0, hi = n;
-  while (lo < hi) {
-    const int64_t mid = (lo + hi) >> 1;
-    if ((int64_t)sorted_ids[mid] < s) lo = mid + 1; else hi = mid;
-  }
-  out[j] = lo;
-}
-
-__global__ void __launch_bounds__(256)
-push_pairs_kernel(const PushPairsParams p) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= p.n) return;
-  int o = 0;
-  while (o + 1 < p.R && i >= p.cut[o + 1]) ++o;
-  p.dst[o][p.dst_offset[o] + (i - p.cut[o])] = make_uint2(p.ids[i], p.vals[i]);
-}
-
 // The pairs arrive in no particular order, so this is a random permutation of 4-byte values: written in
 // one go, every store would be a read-modify-write of a 32-byte DRAM sector (measured 5.2 ms for 134 M
 // pairs). Instead the output is covered in windows small enough to stay in L2; every window re-reads the
@@ -547,27 +493,6 @@ scatter_pairs_kernel(const uint2* __restrict__ pairs, int64_t n, int64_t begin, 
     const int64_t o = (int64_t)pr.x - begin;
     if (o >= window_lo && o < window_hi) out[o] = __uint_as_float(pr.y);
   }
-}
-
-__global__ void __launch_bounds__(256)
-sample_keys_kernel(const uint64_t* __restrict__ sorted_keys, int64_t n, int samples, uint64_t* __restrict__ out) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= samples) return;
-  // evenly spaced order statistics of the local key distribution
-  out[j] = n > 0 ? sorted_keys[(int64_t)(((double)j + 0.5) * (double)n / (double)samples)] : ~0ull;
-}
-
-__global__ void lower_bounds_kernel(const uint64_t* __restrict__ sorted_keys, int64_t n,
-                                    const uint64_t* __restrict__ splitters, int count, int64_t* __restrict__ out) {
-  const int j = threadIdx.x;
-  if (j >= count) return;
-  const uint64_t s = splitters[j];
-  int64_t lo = 0, hi = n;
-  while (lo < hi) {
-    const int64_t mid = (lo + hi) >> 1;
-    if (sorted_keys[mid] < s) lo = mid + 1; else hi = mid;
-  }
-  out[j] = lo;
 }
 
 // ---- publishing the upper tree levels ---------------------------------------------------------------------
@@ -733,41 +658,6 @@ int pv_final_launch(const char* pending, const int* pending_count, int k, float*
   return 0;
 }
 
-int redistribute_launch(const RedistributeParams& p, cudaStream_t stream) {
-  if (p.n <= 0) return 0;
-  redistribute_kernel<<<blocks_for(p.n, 256), 256, 0, stream>>>(p);
-  note_launch();
-  KNN_CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-int extract_pairs_launch(const Float4* pts, const float* res, int64_t n, uint32_t* ids, uint32_t* vals,
-                         cudaStream_t stream) {
-  if (n <= 0) return 0;
-  extract_pairs_kernel<<<blocks_for(n, 256), 256, 0, stream>>>(pts, res, n, ids, vals);
-  note_launch();
-  KNN_CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-int lower_bounds32_launch(const uint32_t* sorted_ids, int64_t n, const int64_t* d_begins, int count, int64_t* out,
-                          cudaStream_t stream) {
-  KNN_REQUIRE(count <= 32, "lower_bounds32: too many boundaries");
-  if (count <= 0) return 0;
-  lower_bounds32_kernel<<<1, 32, 0, stream>>>(sorted_ids, n, d_begins, count, out);
-  note_launch();
-  KNN_CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-int push_pairs_launch(const PushPairsParams& p, cudaStream_t stream) {
-  if (p.n <= 0) return 0;
-  push_pairs_kernel<<<blocks_for(p.n, 256), 256, 0, stream>>>(p);
-  note_launch();
-  KNN_CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
 int scatter_pairs_launch(const void* pairs, int64_t n, int64_t begin, float* out, cudaStream_t stream) {
   if (n <= 0) return 0;
   const int64_t window = (int64_t)20 << 20;             // 20 Mi results = 80 MB of output per window (L2: 126 MB)
@@ -782,21 +672,5 @@ int scatter_pairs_launch(const void* pairs, int64_t n, int64_t begin, float* out
   return 0;
 }
 
-int sample_keys_launch(const uint64_t* sorted_keys, int64_t n, int samples, uint64_t* out, cudaStream_t stream) {
-  sample_keys_kernel<<<blocks_for(samples, 256), 256, 0, stream>>>(sorted_keys, n, samples, out);
-  note_launch();
-  KNN_CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-int lower_bounds_launch(const uint64_t* sorted_keys, int64_t n, const uint64_t* splitters, int count,
-                        int64_t* out, cudaStream_t stream) {
-  KNN_REQUIRE(count <= 32, "lower_bounds: too many splitters");
-  if (count <= 0) return 0;
-  lower_bounds_kernel<<<1, 32, 0, stream>>>(sorted_keys, n, splitters, count, out);
-  note_launch();
-  KNN_CUDA_TRY(cudaGetLastError());
-  return 0;
-}
 
 }  // namespace b200knn
