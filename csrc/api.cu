@@ -6,6 +6,7 @@
 // (peer mapping, flow control).
 #include <string.h>
 #include <atomic>
+#include <mutex>
 #include <vector>
 #include "../include/b200knn.h"
 #include "common.cuh"
@@ -18,6 +19,68 @@ void set_last_error(const std::string& msg) { g_last_error = msg; }
 const char* last_error_cstr() { return g_last_error.c_str(); }
 static std::atomic<unsigned long long> g_launches{0};
 void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// ---- SmallRead (index_internal.h): mapped page-locked mailbox slots ------------------------------------
+namespace {
+constexpr int kMailSlots = 64;
+constexpr size_t kMailSlotBytes = 2048;
+std::mutex g_mail_mutex;
+char* g_mail_host = nullptr;       // kMailSlots * kMailSlotBytes, cudaHostAllocMapped | Portable, never freed
+char* g_mail_dev = nullptr;
+bool g_mail_failed = false;
+unsigned long long g_mail_used = 0;
+
+__global__ void small_read_kernel(const unsigned* __restrict__ src, unsigned* __restrict__ dst, int words) {
+  for (int i = threadIdx.x; i < words; i += blockDim.x) dst[i] = src[i];
+  __threadfence_system();
+}
+}  // namespace
+
+int SmallRead::begin(const void* d_src, size_t bytes, void* h_dst, cudaStream_t stream) {
+  release();
+  dst_ = h_dst;
+  bytes_ = bytes;
+  if (bytes == 0) return 0;
+  if (bytes <= kMailSlotBytes && bytes % 4 == 0) {
+    std::lock_guard<std::mutex> lock(g_mail_mutex);
+    if (g_mail_host == nullptr && !g_mail_failed) {
+      void *h = nullptr, *dv = nullptr;
+      if (cudaHostAlloc(&h, kMailSlots * kMailSlotBytes, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess &&
+          cudaHostGetDevicePointer(&dv, h, 0) == cudaSuccess) {
+        g_mail_host = static_cast<char*>(h);
+        g_mail_dev = static_cast<char*>(dv);
+      } else {
+        cudaGetLastError();
+        g_mail_failed = true;
+      }
+    }
+    if (g_mail_host != nullptr)
+      for (int i = 0; i < kMailSlots; ++i)
+        if (!(g_mail_used >> i & 1ull)) { g_mail_used |= 1ull << i; slot_ = i; break; }
+  }
+  if (slot_ >= 0) {
+    small_read_kernel<<<1, 128, 0, stream>>>(static_cast<const unsigned*>(d_src),
+                                             reinterpret_cast<unsigned*>(g_mail_dev + (size_t)slot_ * kMailSlotBytes),
+                                             (int)(bytes / 4));
+    note_launch();
+    KNN_CUDA_TRY(cudaGetLastError());
+  } else {
+    KNN_CUDA_TRY(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, stream));
+  }
+  return 0;
+}
+
+void SmallRead::end() {
+  if (slot_ >= 0) memcpy(dst_, g_mail_host + (size_t)slot_ * kMailSlotBytes, bytes_);
+  release();
+}
+
+void SmallRead::release() {
+  if (slot_ < 0) return;
+  std::lock_guard<std::mutex> lock(g_mail_mutex);
+  g_mail_used &= ~(1ull << slot_);
+  slot_ = -1;
+}
 }  // namespace b200knn
 
 namespace {
@@ -149,9 +212,11 @@ static int index_create_impl(const float* d_xyz, int stride, int64_t n, const ui
   if ((rc = bounds_init(idx->d_bounds_ord, stream))) return rc;
   if ((rc = bounds_accumulate(d_xyz, stride, n, idx->d_bounds_ord, stream))) return rc;
   if ((rc = bounds_decode(idx->d_bounds_ord, idx->d_bounds6, stream))) return rc;
-  KNN_CUDA_TRY(cudaMemcpyAsync(idx->h_bounds, idx->d_bounds6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  SmallRead bounds_read;
+  if ((rc = bounds_read.begin(idx->d_bounds6, 6 * sizeof(float), idx->h_bounds, stream))) return rc;
   if (n == 0) {
     KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    bounds_read.end();
     return 0;
   }
   const int64_t groups = idx->groups();
@@ -194,6 +259,7 @@ static int index_create_impl(const float* d_xyz, int stride, int64_t n, const ui
   vals_tmp.release();
   scratch.release();
   KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  bounds_read.end();
   return 0;
 }
 

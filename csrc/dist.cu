@@ -337,16 +337,20 @@ int run_pv(b200knn_dist* d, b200knn_index* idx, int k, float max_radius, const P
     std::vector<int> votes((size_t)R * vote_words), mine(vote_words);
     double tl1;
     if (host_vote) {
-      KNN_CUDA_TRY(cudaMemcpyAsync(mine.data(), p.pending_count, (size_t)vote_words * sizeof(int), cudaMemcpyDeviceToHost, stream));
+      SmallRead vote_read;
+      if ((rc = vote_read.begin(p.pending_count, (size_t)vote_words * sizeof(int), mine.data(), stream))) return rc;
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      vote_read.end();
       tl1 = now_ms();
       if (d->allgather(mine.data(), votes.data(), (int64_t)vote_words * sizeof(int))) { set_last_error("bootstrap allgather failed"); return -3; }
       // the device-side vote doubles as the fence that makes the posted requests visible; this one does not
       if (one_round && (rc = device_barrier(d, stream))) return rc;
     } else {
       if ((rc = device_collective(d, p.pending_count, vote_words, kCollGather, d_votes, stream))) return rc;
-      KNN_CUDA_TRY(cudaMemcpyAsync(votes.data(), d_votes, votes.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
+      SmallRead vote_read;
+      if ((rc = vote_read.begin(d_votes, votes.size() * sizeof(int), votes.data(), stream))) return rc;
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      vote_read.end();
       tl1 = now_ms();
     }
     const int my_pending = votes[(size_t)me * vote_words];
@@ -522,9 +526,14 @@ int knn_redistribute(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
   // ---- the one host synchronisation: sizes
   RdPlan plan;
   std::vector<unsigned> info((size_t)R * kRdInfoWords);
-  KNN_CUDA_TRY(cudaMemcpyAsync(&plan, d_plan, sizeof(RdPlan), cudaMemcpyDeviceToHost, stream));
-  KNN_CUDA_TRY(cudaMemcpyAsync(info.data(), d_info_all, info.size() * sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
-  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+  {
+    SmallRead plan_read, info_read;      // no copy engine: see index_internal.h
+    if ((rc = plan_read.begin(d_plan, sizeof(RdPlan), &plan, stream))) return rc;
+    if ((rc = info_read.begin(d_info_all, info.size() * sizeof(unsigned), info.data(), stream))) return rc;
+    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    plan_read.end();
+    info_read.end();
+  }
   trace.mark("redistribute: bounds, histograms, splitters, plan");
   std::vector<long long> begins(R + 1);
   int64_t max_local = 0, total = 0;
@@ -745,10 +754,12 @@ int b200knn_dist_knn(b200knn_dist* d, const float* d_xyz, int64_t n_local, int64
       if ((rc = bounds_init(d_bord, stream))) return rc;
       if ((rc = bounds_accumulate(d_xyz, 3, n_local, d_bord, stream))) return rc;
       if ((rc = bounds_decode(d_bord, d_box6, stream))) return rc;
-      KNN_CUDA_TRY(cudaMemcpyAsync(mine.box, d_box6, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+      SmallRead box_read;
+      if ((rc = box_read.begin(d_box6, 6 * sizeof(float), mine.box, stream))) return rc;
       d_bord.release();
       d_box6.release();
       KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+      box_read.end();
       std::vector<Info> info(d->world);
       if (d->allgather(&mine, info.data(), sizeof(Info))) { set_last_error("bootstrap allgather failed"); return -3; }
       double worst = 0.0;

@@ -5,7 +5,30 @@
 
 using namespace b200knn;
 
-namespace b200knn { int frontier_capacity(); }   // api.cu: 128, or B200KNN_QUEUE_CAP (a test knob)
+namespace b200knn {
+int frontier_capacity();   // api.cu: 128, or B200KNN_QUEUE_CAP (a test knob)
+
+// A few words from device memory to the host WITHOUT a copy engine: a one-warp kernel stores them into a slot of
+// page-locked host memory that the GPU has mapped. An in-stream cudaMemcpyAsync of 24 bytes looks harmless, but it
+// queues on the device-to-host copy engine behind whatever a caller's other stream is downloading — a 1 GB result
+// array of the previous step holds the next step's bounds (and with them its whole build) back by 19 ms.
+// begin() enqueues on `stream`; after the caller has synchronised that stream, end() copies slot -> h_dst and
+// frees the slot (the destructor frees it on error paths). Falls back to cudaMemcpyAsync when no slot is free.
+class SmallRead {
+ public:
+  SmallRead() = default;
+  SmallRead(const SmallRead&) = delete;
+  SmallRead& operator=(const SmallRead&) = delete;
+  ~SmallRead() { release(); }
+  int begin(const void* d_src, size_t bytes, void* h_dst, cudaStream_t stream);
+  void end();
+ private:
+  void release();
+  int slot_ = -1;
+  void* dst_ = nullptr;
+  size_t bytes_ = 0;
+};
+}  // namespace b200knn
 
 struct b200knn_index {
   int device = 0;

@@ -205,6 +205,9 @@ inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 inline cudaError_t cudaMalloc(void** p, size_t n) { *p = nullptr; return posix_memalign(p, 256, n ? n : 1) == 0 ? cudaSuccess : 2; }
 template <class T> inline cudaError_t cudaMalloc(T** p, size_t n) { return cudaMalloc((void**)p, n); }
 inline cudaError_t cudaFree(void* p) { free(p); return cudaSuccess; }
+constexpr unsigned cudaHostAllocDefault = 0, cudaHostAllocPortable = 1, cudaHostAllocMapped = 2;
+inline cudaError_t cudaHostAlloc(void** p, size_t n, unsigned) { *p = nullptr; return posix_memalign(p, 256, n ? n : 1) == 0 ? cudaSuccess : 2; }
+inline cudaError_t cudaHostGetDevicePointer(void** d, void* h, unsigned) { *d = h; return cudaSuccess; }
 template <class T> inline cudaError_t cudaMallocAsync(T** p, size_t n, cudaStream_t) { return cudaMalloc((void**)p, n); }
 inline cudaError_t cudaFreeAsync(void* p, cudaStream_t) { free(p); return cudaSuccess; }
 inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, cudaMemcpyKind) { if (n) memmove(d, s, n); return cudaSuccess; }

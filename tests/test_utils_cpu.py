@@ -106,3 +106,68 @@ def test_host_prefetcher_schedule_with_fake_streams(monkeypatch):
     assert trace.index(("copy waits", "free0")) < trace.index(("compute", 0))          # first use: nothing to wait for yet
     second_wait = [j for j, t in enumerate(trace) if t == ("copy waits", "free0")][1]
     assert trace.index(("record", "free0")) < second_wait < trace.index(("compute", 1))
+
+
+def test_result_drain_schedule_with_fake_streams(monkeypatch):
+    """Control flow of ops.pipeline.ResultDrain without a GPU: step i writes slot i % 2, its download waits for the
+    step, the next step that writes the same slot waits for that download, and submit() hands back the result of the
+    step before, after waiting for ITS download only."""
+    import types
+
+    import torch
+
+    import mpi_cuda_largescaleknn_b200.ops.pipeline as pl
+    trace = []
+
+    class Event:
+        def __init__(self):
+            self.name = None
+
+        def record(self, stream=None):
+            trace.append(("record", self.name))
+
+        def synchronize(self):
+            trace.append(("host waits", self.name))
+
+    class Stream:
+        def __init__(self, device=None, name="copy"):
+            self.name = name
+
+        def wait_event(self, e):
+            trace.append((self.name + " waits", e.name))
+
+    class Ctx:
+        def __init__(self, s):
+            pass
+
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *a):
+            return False
+
+    fake_cuda = types.SimpleNamespace(Stream=Stream, Event=Event, stream=Ctx, current_stream=lambda d=None: Stream(name="main"))
+    real_empty = torch.empty
+    monkeypatch.setattr(pl, "torch", types.SimpleNamespace(
+        cuda=fake_cuda, float32=torch.float32, device=torch.device, Tensor=torch.Tensor,
+        empty=lambda *a, pin_memory=False, **kw: real_empty(*a, **kw)))
+    d = pl.ResultDrain(4, "cpu")
+    for i in range(2):
+        d.filled[i].name, d.done[i].name = f"filled{i}", f"done{i}"
+    got = []
+    for i in range(4):
+        out = d.next_out()
+        out.fill_(float(i))                    # "the step"
+        trace.append(("compute", i))
+        prev = d.submit()
+        got.append(None if prev is None else float(prev[0]))
+    last = d.finish()
+    assert got == [None, 0.0, 1.0, 2.0] and float(last[0]) == 3.0
+    # step 2 reuses slot 0: the main stream waits for download 0 before computing, and the host waited only for done0
+    c2 = trace.index(("compute", 2))
+    waits0 = [j for j, t in enumerate(trace) if t == ("main waits", "done0")]
+    assert len(waits0) == 2 and trace.index(("record", "done0")) < waits0[1] < c2
+    assert trace.index(("copy waits", "filled0")) > trace.index(("compute", 0))
+    # handing in step 1 returns step 0 after waiting for done0 — never for done1, which is still in flight
+    s1 = trace.index(("compute", 1))
+    assert ("host waits", "done0") in trace[s1:c2] and ("host waits", "done1") not in trace[s1:c2]
