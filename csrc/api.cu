@@ -170,27 +170,42 @@ const char* b200knn_last_error(void) { return last_error_cstr(); }
 int b200knn_version(void) { return 100; }
 uint64_t b200knn_launch_count(void) { return g_launches.load(); }
 
-static int index_create_impl(const float* d_xyz, int stride, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
+static int index_create_impl(const float* d_xyz, PointLayout stride, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
                              cudaStream_t stream, b200knn_index** out);
 
 int b200knn_index_create(const float* d_xyz, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
                          void* stream_, b200knn_index** out) {
-  return index_create_impl(d_xyz, 3, n, d_ids, id_offset, (cudaStream_t)stream_, out);
+  return index_create_impl(d_xyz, layout_of(3), n, d_ids, id_offset, (cudaStream_t)stream_, out);
 }
 
 int b200knn_index_create_xyzw(const float* d_xyzw, int64_t n, uint32_t id_offset, void* stream_,
                               b200knn_index** out) {
-  return index_create_impl(d_xyzw, 4, n, nullptr, id_offset, (cudaStream_t)stream_, out);
+  return index_create_impl(d_xyzw, layout_of(4), n, nullptr, id_offset, (cudaStream_t)stream_, out);
 }
 
 int b200knn_index_create_xy(const float* d_xy, int64_t n, const uint32_t* d_ids, uint32_t id_offset, void* stream_,
                             b200knn_index** out) {
-  const int rc = index_create_impl(d_xy, 2, n, d_ids, id_offset, (cudaStream_t)stream_, out);
+  const int rc = index_create_impl(d_xy, layout_of(2), n, d_ids, id_offset, (cudaStream_t)stream_, out);
   if (out && *out) (*out)->dims = 2;
   return rc;
 }
 
-static int index_create_impl(const float* d_xyz, int stride, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
+int b200knn_index_create_records(const void* d_records, int64_t n, size_t record_bytes, size_t position_offset,
+                                 int dims, const uint32_t* d_ids, uint32_t id_offset, void* stream_,
+                                 b200knn_index** out) {
+  KNN_REQUIRE(dims == 2 || dims == 3, "index_create_records: dims must be 2 or 3");
+  KNN_REQUIRE(record_bytes % 4 == 0 && position_offset % 4 == 0, "index_create_records: record size and position offset must be multiples of 4 bytes");
+  KNN_REQUIRE(position_offset + (size_t)dims * 4 <= record_bytes, "index_create_records: the position does not fit inside a record");
+  KNN_REQUIRE(record_bytes / 4 <= 0x7fffffff, "index_create_records: record too large");
+  KNN_REQUIRE(n == 0 || (reinterpret_cast<uintptr_t>(d_records) & 3u) == 0, "index_create_records: records must be 4-byte aligned");
+  const float* first = reinterpret_cast<const float*>(static_cast<const char*>(d_records) + position_offset);
+  const int rc = index_create_impl(first, PointLayout{(int)(record_bytes / 4), dims, 0}, n, d_ids, id_offset,
+                                   (cudaStream_t)stream_, out);
+  if (out && *out) (*out)->dims = dims;
+  return rc;
+}
+
+static int index_create_impl(const float* d_xyz, PointLayout stride, int64_t n, const uint32_t* d_ids, uint32_t id_offset,
                              cudaStream_t stream, b200knn_index** out) {
   NvtxRange range("b200knn:index_build");
   KNN_REQUIRE(out != nullptr, "index_create: out is NULL");

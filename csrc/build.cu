@@ -18,13 +18,13 @@ __global__ void k_bounds_init(unsigned* b) {
 }
 
 __global__ void __launch_bounds__(256)
-k_bounds(const float* __restrict__ xyz, int fstride, int64_t n, unsigned* __restrict__ b) {
+k_bounds(const float* __restrict__ xyz, const PointLayout lay, int64_t n, unsigned* __restrict__ b) {
   float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
-      const float v = a < fstride ? xyz[(size_t)fstride * i + a] : 0.f;      // stride 2: planar points, z = 0
+      const float v = a < lay.dims ? xyz[(size_t)lay.stride * i + a] : 0.f;      // planar points: z = 0
       lo[a] = fminf(lo[a], v);
       hi[a] = fmaxf(hi[a], v);
     }
@@ -54,7 +54,7 @@ __global__ void k_bounds_decode(const unsigned* __restrict__ b, float* __restric
 }
 
 __global__ void __launch_bounds__(256)
-k_morton(const float* __restrict__ xyz, int stride, int64_t n, const float* __restrict__ bounds6,
+k_morton(const float* __restrict__ xyz, const PointLayout lay, int64_t n, const float* __restrict__ bounds6,
          uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -63,24 +63,24 @@ k_morton(const float* __restrict__ xyz, int stride, int64_t n, const float* __re
   const float ivx = ex > 0.f ? 1.f / ex : 0.f;
   const float ivy = ey > 0.f ? 1.f / ey : 0.f;
   const float ivz = ez > 0.f ? 1.f / ez : 0.f;
-  const size_t o = (size_t)stride * i;
-  keys[i] = morton63(xyz[o], xyz[o + 1], stride >= 3 ? xyz[o + 2] : 0.f, lox, loy, loz, ivx, ivy, ivz);
+  const size_t o = (size_t)lay.stride * i;
+  keys[i] = morton63(xyz[o], xyz[o + 1], lay.dims >= 3 ? xyz[o + 2] : 0.f, lox, loy, loz, ivx, ivy, ivz);
   vals[i] = (uint32_t)i;
 }
 
 __global__ void __launch_bounds__(256)
-k_gather(const float* __restrict__ xyz, int stride, const uint32_t* __restrict__ order,
+k_gather(const float* __restrict__ xyz, const PointLayout lay, const uint32_t* __restrict__ order,
          const uint32_t* __restrict__ ids, uint32_t id_offset, int64_t n, Float4* __restrict__ sorted) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t src = order[i];
   float4 p;
-  const size_t o = (size_t)stride * src;
+  const size_t o = (size_t)lay.stride * src;
   p.x = xyz[o];
   p.y = xyz[o + 1];
-  p.z = stride >= 3 ? xyz[o + 2] : 0.f;
-  // stride 4: the id travels in .w of the input (redistributed points); else explicit ids or position
-  p.w = stride == 4 ? xyz[o + 3] : __uint_as_float(ids ? ids[src] : src + id_offset);
+  p.z = lay.dims >= 3 ? xyz[o + 2] : 0.f;
+  // the id travels in .w of the input (redistributed points); else explicit ids or position
+  p.w = lay.w_is_id ? xyz[o + 3] : __uint_as_float(ids ? ids[src] : src + id_offset);
   reinterpret_cast<float4*>(sorted)[i] = p;
 }
 
@@ -286,11 +286,11 @@ int bounds_init(unsigned* d_bounds_ord, cudaStream_t stream) {
   return 0;
 }
 
-int bounds_accumulate(const float* d_xyz, int stride, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream) {
+int bounds_accumulate(const float* d_xyz, PointLayout lay, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream) {
   if (n <= 0) return 0;
   int64_t blocks = div_up(n, 256 * 8);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  k_bounds<<<(int)blocks, 256, 0, stream>>>(d_xyz, stride, n, d_bounds_ord);
+  k_bounds<<<(int)blocks, 256, 0, stream>>>(d_xyz, lay, n, d_bounds_ord);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;
@@ -303,19 +303,19 @@ int bounds_decode(const unsigned* d_bounds_ord, float* d_bounds6, cudaStream_t s
   return 0;
 }
 
-int morton_keys(const float* d_xyz, int stride, int64_t n, const float* d_bounds6, uint64_t* keys,
+int morton_keys(const float* d_xyz, PointLayout lay, int64_t n, const float* d_bounds6, uint64_t* keys,
                 uint32_t* vals, cudaStream_t stream) {
   if (n <= 0) return 0;
-  k_morton<<<grid_for(n, 256), 256, 0, stream>>>(d_xyz, stride, n, d_bounds6, keys, vals);
+  k_morton<<<grid_for(n, 256), 256, 0, stream>>>(d_xyz, lay, n, d_bounds6, keys, vals);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;
 }
 
-int gather_points(const float* d_xyz, int stride, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
+int gather_points(const float* d_xyz, PointLayout lay, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
                   int64_t n, Float4* sorted, cudaStream_t stream) {
   if (n <= 0) return 0;
-  k_gather<<<grid_for(n, 256), 256, 0, stream>>>(d_xyz, stride, order, ids, id_offset, n, sorted);
+  k_gather<<<grid_for(n, 256), 256, 0, stream>>>(d_xyz, lay, order, ids, id_offset, n, sorted);
   note_launch();
   KNN_CUDA_TRY(cudaGetLastError());
   return 0;

@@ -39,15 +39,30 @@ struct Bounds { float lo[3]; float hi[3]; };
 
 // d_bounds_ord: 6 unsigned (order-preserving encoding), must be initialised by bounds_init.
 int bounds_init(unsigned* d_bounds_ord, cudaStream_t stream);
-int bounds_accumulate(const float* d_xyz, int stride, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream);
+// Where the coordinates of point i live: `dims` (2 or 3) floats at d_xyz + stride * i; a missing z is 0.
+// w_is_id: the float after z carries the point's id (points that arrive from another rank).
+struct PointLayout { int stride, dims, w_is_id; };
+KNN_HD PointLayout layout_of(int stride) { return PointLayout{stride, stride >= 3 ? 3 : 2, stride == 4 ? 1 : 0}; }
+int bounds_accumulate(const float* d_xyz, PointLayout lay, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream);
+inline int bounds_accumulate(const float* d_xyz, int stride, int64_t n, unsigned* d_bounds_ord, cudaStream_t stream) {
+  return bounds_accumulate(d_xyz, layout_of(stride), n, d_bounds_ord, stream);
+}
 int bounds_decode(const unsigned* d_bounds_ord, float* d_bounds6, cudaStream_t stream);
 // `stride` = floats per input point: 3 (xyz) or 4 (xyzw, id bits in w).
 // keys[i] = morton63(point i) relative to *d_bounds6 (device-resident lo[3],hi[3]); vals[i] = i.
-int morton_keys(const float* d_xyz, int stride, int64_t n, const float* d_bounds6, uint64_t* keys,
+int morton_keys(const float* d_xyz, PointLayout lay, int64_t n, const float* d_bounds6, uint64_t* keys,
                 uint32_t* vals, cudaStream_t stream);
+inline int morton_keys(const float* d_xyz, int stride, int64_t n, const float* d_bounds6, uint64_t* keys,
+                       uint32_t* vals, cudaStream_t stream) {
+  return morton_keys(d_xyz, layout_of(stride), n, d_bounds6, keys, vals, stream);
+}
 // sorted[i] = (xyz[order[i]], id = ids ? ids[order[i]] : order[i] + id_offset)
-int gather_points(const float* d_xyz, int stride, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
+int gather_points(const float* d_xyz, PointLayout lay, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
                   int64_t n, Float4* sorted, cudaStream_t stream);
+inline int gather_points(const float* d_xyz, int stride, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
+                         int64_t n, Float4* sorted, cudaStream_t stream) {
+  return gather_points(d_xyz, layout_of(stride), order, ids, id_offset, n, sorted, stream);
+}
 // Re-order every 1024-point Morton run into a balanced k-d tree with compact 32-point leaves.
 int refine_runs(Float4* sorted, int64_t n, cudaStream_t stream);
 int build_leaf_boxes(const Float4* sorted, int64_t n, Box* level0, cudaStream_t stream);

@@ -51,6 +51,15 @@ int b200knn_index_create_xyzw(const float* d_xyzw, int64_t n, uint32_t id_offset
  * query entry point of this index then takes [nq][2] queries. */
 int b200knn_index_create_xy(const float* d_xy, int64_t n, const uint32_t* d_ids_or_null, uint32_t id_offset,
                             void* stream, b200knn_index** out);
+/* Points embedded in caller records — the reference library's data traits (a struct with a position and any
+ * payload, cukd/data.h:56-112; testing/testPayloadSampleFromReadme.cu): record i starts at
+ * d_records + i * record_bytes and its position is `dims` (2 or 3) floats at byte offset position_offset. Nothing
+ * is copied besides the positions; the ids that fcp / neighbors return are record indices (+ id_offset, or
+ * d_ids[i]), so the payload of a hit is records[id]. Sizes and offsets must be multiples of 4 bytes. Queries are
+ * plain [nq][dims] floats. */
+int b200knn_index_create_records(const void* d_records, int64_t n, size_t record_bytes, size_t position_offset,
+                                 int dims, const uint32_t* d_ids_or_null, uint32_t id_offset, void* stream,
+                                 b200knn_index** out);
 void b200knn_index_destroy(b200knn_index* idx);
 int64_t b200knn_index_num_points(const b200knn_index* idx);
 int b200knn_index_num_levels(const b200knn_index* idx);

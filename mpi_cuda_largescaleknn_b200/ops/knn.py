@@ -66,6 +66,37 @@ class KnnIndex:
                          self.id_offset, _stream_ptr(), C.byref(self._h)),
                   "index_create")
 
+    @classmethod
+    def from_records(cls, records: torch.Tensor, first_column: int = 0, dims: int = 3,
+                     ids: Optional[torch.Tensor] = None, id_offset: int = 0) -> "KnnIndex":
+        """Index the positions embedded in caller records without copying them out first: ``records`` is a
+        contiguous float32 CUDA tensor ``[N, F]`` (position + any payload columns), the position is ``dims`` (2 or
+        3) columns starting at ``first_column``. Role of the reference's data traits
+        (cudaKDTree/cukd/data.h:56-112): ids returned by ``fcp`` / ``neighbors`` are row numbers, so the payload
+        of a hit is ``records[id]``. Queries are plain ``[nq, dims]`` tensors."""
+        if records.dim() != 2 or records.dtype != torch.float32 or not records.is_contiguous():
+            raise ValueError("from_records needs a contiguous float32 tensor [N, F]")
+        if dims not in (2, 3) or first_column < 0 or first_column + dims > records.shape[1]:
+            raise ValueError("the position columns do not fit inside a record")
+        self = cls.__new__(cls)
+        self.dims = int(dims)
+        self.device = records.device
+        self.n = int(records.shape[0])
+        self.id_offset = int(id_offset)
+        self._h = C.c_void_p()
+        ids_ptr = None
+        if ids is not None:
+            ids = ids.to(device=self.device, dtype=torch.int32).contiguous()
+            ids_ptr = ids.data_ptr()
+        create = lib().b200knn_index_create_records
+        create.argtypes = [C.c_void_p, C.c_int64, C.c_size_t, C.c_size_t, C.c_int, C.c_void_p, C.c_uint32, C.c_void_p,
+                           C.c_void_p]
+        create.restype = C.c_int
+        with torch.cuda.device(self.device):
+            check(create(records.data_ptr() if self.n else None, self.n, int(records.shape[1]) * 4, int(first_column) * 4,
+                         self.dims, ids_ptr, self.id_offset, _stream_ptr(), C.byref(self._h)), "index_create_records")
+        return self
+
     def close(self) -> None:
         if getattr(self, "_h", None) is not None and self._h.value:
             lib().b200knn_index_destroy(self._h)

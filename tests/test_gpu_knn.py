@@ -322,3 +322,27 @@ def test_fcp_returns_closest_point_id_and_distance():
     assert np.all(ids2.cpu().numpy() == -1)
     assert np.all(dist2.cpu().numpy() == np.float32(0.5))
     idx.close()
+
+
+def test_index_over_records_with_payload():
+    """b200knn_index_create_records: positions read in place out of [N, F] records (payload columns before and after
+    them). Self kNN, external queries and find-closest-point must give the bits of an index built on a contiguous
+    copy of the positions, and the ids returned must be record numbers — the handle to the payload."""
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex, fcp
+    for dims, first, width in ((3, 2, 7), (2, 1, 4), (3, 0, 3)):
+        n = 30_000
+        rec = torch.from_numpy(np.random.default_rng(dims * 10 + first).random((n, width), dtype=np.float32)).to(_dev())
+        pos = rec[:, first:first + dims].contiguous()
+        q = torch.from_numpy(np.random.default_rng(5).random((2_000, dims), dtype=np.float32)).to(_dev())
+        a, b = KnnIndex.from_records(rec, first_column=first, dims=dims), KnnIndex(pos)
+        assert torch.equal(a.knn_self(16), b.knn_self(16))
+        assert torch.equal(a.knn_query(q, 8), b.knn_query(q, 8))
+        ia, da = fcp(a, q)
+        ib, db = fcp(b, q)
+        assert torch.equal(ia, ib) and torch.equal(da, db)
+        # the id is the record number: the record's own position is the closest point that was reported
+        hit = rec[ia.long()][:, first:first + dims]
+        d = torch.sqrt(((hit - q) ** 2).sum(dim=1))
+        assert float((d - da).abs().max().item()) <= 1e-6
+        a.close()
+        b.close()

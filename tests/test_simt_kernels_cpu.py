@@ -125,6 +125,35 @@ def test_emulated_external_queries_and_fcp(sim):
     idx.close()
 
 
+def test_emulated_index_over_records_with_payload(sim):
+    """b200knn_index_create_records: positions read in place from records with payload around them; results equal
+    the oracle on the positions, ids are record numbers, bad layouts are refused."""
+    rng = np.random.default_rng(3)
+    for dims, first, width in ((3, 2, 7), (2, 1, 4)):
+        rec = rng.random((2600, width), dtype=np.float32)
+        pos = np.zeros((len(rec), 3), np.float32)
+        pos[:, :dims] = rec[:, first:first + dims]
+        q = rng.random((300, dims), dtype=np.float32)
+        q3 = np.zeros((len(q), 3), np.float32)
+        q3[:, :dims] = q
+        h = C.c_void_p()
+        sim.b200knn_index_create_records.argtypes = [C.c_void_p, C.c_int64, C.c_size_t, C.c_size_t, C.c_int, C.c_void_p,
+                                                     C.c_uint32, C.c_void_p, C.POINTER(C.c_void_p)]
+        ok(sim, sim.b200knn_index_create_records(rec.ctypes.data, len(rec), width * 4, first * 4, dims, None, 0, None, C.byref(h)))
+        out = np.empty(len(rec), np.float32)
+        ok(sim, sim.b200knn_knn_self(h, 20, math.inf, out.ctypes.data, None))
+        assert bit_equal(out, bruteforce(pos, k=20))
+        ids, dist = np.empty(len(q), np.int32), np.empty(len(q), np.float32)
+        ok(sim, sim.b200knn_fcp_query(h, q.ctypes.data, len(q), math.inf, ids.ctypes.data, dist.ctypes.data, None))
+        assert bit_equal(dist, bruteforce(pos, queries=q3, k=1))
+        assert np.allclose(np.sqrt(((rec[ids][:, first:first + dims] - q) ** 2).sum(1)), dist, rtol=1e-5, atol=1e-7)
+        sim.b200knn_index_destroy(h)
+    h = C.c_void_p()
+    assert sim.b200knn_index_create_records(rec.ctypes.data, len(rec), 16, 8, 3, None, 0, None, C.byref(h)) != 0   # 8 + 12 > 16
+    assert sim.b200knn_index_create_records(rec.ctypes.data, len(rec), 14, 0, 3, None, 0, None, C.byref(h)) != 0   # not a multiple of 4
+    assert sim.b200knn_index_create_records(rec.ctypes.data, len(rec), 16, 0, 4, None, 0, None, C.byref(h)) != 0   # dims
+
+
 def test_emulated_heap_in_global_memory(sim):
     x = gen.uniform(2300, seed=77)
     idx = Index(sim, x)
