@@ -215,9 +215,14 @@ bool gpu_available();
 std::vector<float> run_gpu(Bootstrap& bs, const std::vector<float>& pts, int64_t global_begin, const Options& o,
                            int mode);
 // The same, reading the rank's slice [begin, begin + n) of a raw float3 file straight into device memory through
-// pinned double buffers (no pageable copy of the input).
+// pinned double buffers (no pageable copy of the input). With `out_path` the results go from the pinned buffers
+// straight into that file at float offset `begin` (a file of `total` floats that rank 0 creates; collective: two
+// barriers) and the returned vector is empty; "done all queries..." is printed before the file is written.
 std::vector<float> run_gpu_from_file(Bootstrap& bs, const std::string& path, int64_t begin, int64_t n,
-                                     const Options& o, int mode);
+                                     const Options& o, int mode, const std::string& out_path = std::string(),
+                                     int64_t total = 0);
+void parallel_pread(int fd, char* dst, size_t len, int64_t off, const std::string& what);
+void parallel_pwrite(int fd, const char* src, size_t len, int64_t off, const std::string& what);
 // CPU path (B200KNN_BACKEND=cpu or no CUDA device): every rank gathers all points through the
 // bootstrap and answers its own queries with the host mirror engine. For plumbing tests.
 std::vector<float> run_cpu(Bootstrap& bs, const std::vector<float>& pts, const Options& o);

@@ -22,7 +22,9 @@ int main(int ac, char** av) {
       std::cout << "#" << bs.rank() << "/" << bs.size() << ": got " << n << " points to work on" << std::endl;
       select_gpu(bs, o);
       const int mode = o.mode >= 0 ? o.mode : B200KNN_MODE_REDISTRIBUTE;
-      result = run_gpu_from_file(bs, o.input, begin, n, o, mode);
+      // file -> device -> file; the results never exist as one host array
+      run_gpu_from_file(bs, o.input, begin, n, o, mode, o.output, total);
+      return 0;
     } else {
       std::vector<float> pts = read_points(o.input, bs.rank(), bs.size(), &begin, &total);
       std::cout << "#" << bs.rank() << "/" << bs.size() << ": got " << pts.size() / 3 << " points to work on" << std::endl;
