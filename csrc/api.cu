@@ -141,6 +141,19 @@ void keep_pool_memory(int device) {
   done.fetch_or(bit);
 }
 
+// Leading bits of the Morton key that the index build sorts by (see index_create_impl): 40, or B200KNN_SORT_BITS
+// (8..64, rounded up to whole 8-bit digits).
+int index_sort_bits() {
+  static const int bits = [] {
+    const char* e = getenv("B200KNN_SORT_BITS");
+    int b = e ? atoi(e) : 40;
+    if (b < 8) b = 8;
+    if (b > 64) b = 64;
+    return (b + 7) / 8 * 8;
+  }();
+  return bits;
+}
+
 // Convergent fill of fresh heaps (traverse.cuh::fill_leaf): on by default (measured 58.4 -> 54.5 ms for
 // 16 M points, k = 100); B200KNN_FILL=0 switches back to sifting every candidate.
 // Frontier entries per warp: all 128, unless B200KNN_QUEUE_CAP (8..128) shrinks it so that tests reach the
@@ -259,22 +272,41 @@ static int index_create_impl(const float* d_xyz, PointLayout stride, int64_t n, 
   KNN_CUDA_TRY(vals.alloc_bytes(n * sizeof(uint32_t)));
   KNN_CUDA_TRY(vals_tmp.alloc_bytes(n * sizeof(uint32_t)));
   KNN_CUDA_TRY(scratch.alloc_bytes(radix_sort_scratch_bytes(n)));
-  if ((rc = morton_keys(d_xyz, stride, n, idx->d_bounds6, keys, vals, stream))) return rc;
-  int in_tmp = 0;
-  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n, 0, 64, stream, &in_tmp))) return rc;
-  const uint32_t* order = in_tmp ? vals_tmp.get() : vals.get();
-  if ((rc = gather_points(d_xyz, stride, order, d_ids, id_offset, n, idx->pts, stream))) return rc;
-  if ((rc = refine_runs(idx->pts, n, stream))) return rc;
-  if ((rc = build_leaf_boxes(idx->pts, n, idx->boxes[0], stream))) return rc;
-  for (int l = 1; l < levels; ++l)
-    if ((rc = build_upper_boxes(idx->boxes[l - 1], idx->count[l - 1], idx->boxes[l], stream))) return rc;
+  StreamBuf<unsigned> heavy(stream);
+  KNN_CUDA_TRY(heavy.alloc_bytes(sizeof(unsigned)));
+  // The order only has to be spatial down to the 1024-point runs that refine_runs re-sorts anyway, so the sort
+  // looks at the leading kIndexSortBits of the 63-bit key: 5 digit passes instead of 8. That is enough unless more
+  // than 1024 points share one such cell (extent / 10321 per axis) — checked on the device, read back with the
+  // synchronisation below, and answered by building again on all 64 bits (B200KNN_SORT_BITS=64: always).
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    const int low_bit = attempt == 0 ? 64 - index_sort_bits() : 0;
+    if ((rc = morton_keys(d_xyz, stride, n, idx->d_bounds6, keys, vals, stream))) return rc;
+    int in_tmp = 0;
+    if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, n, low_bit, 64, stream, &in_tmp))) return rc;
+    const uint32_t* order = in_tmp ? vals_tmp.get() : vals.get();
+    unsigned h_heavy = 0;
+    SmallRead heavy_read;
+    if (low_bit > 0) {
+      if ((rc = heavy_cells(in_tmp ? keys_tmp.get() : keys.get(), n, low_bit, heavy, stream))) return rc;
+      if ((rc = heavy_read.begin(heavy, sizeof(unsigned), &h_heavy, stream))) return rc;
+    }
+    if ((rc = gather_points(d_xyz, stride, order, d_ids, id_offset, n, idx->pts, stream))) return rc;
+    if ((rc = refine_runs(idx->pts, n, stream))) return rc;
+    if ((rc = build_leaf_boxes(idx->pts, n, idx->boxes[0], stream))) return rc;
+    for (int l = 1; l < levels; ++l)
+      if ((rc = build_upper_boxes(idx->boxes[l - 1], idx->count[l - 1], idx->boxes[l], stream))) return rc;
+    KNN_CUDA_TRY(cudaStreamSynchronize(stream));
+    heavy_read.end();
+    if (attempt == 0) bounds_read.end();
+    idx->sort_bits = 64 - low_bit;
+    if (low_bit == 0 || h_heavy == 0) break;
+  }
   keys.release();
   keys_tmp.release();
   vals.release();
   vals_tmp.release();
   scratch.release();
-  KNN_CUDA_TRY(cudaStreamSynchronize(stream));
-  bounds_read.end();
+  heavy.release();
   return 0;
 }
 
@@ -293,6 +325,7 @@ void b200knn_index_destroy(b200knn_index* idx) {
 
 int64_t b200knn_index_num_points(const b200knn_index* idx) { return idx ? idx->n : 0; }
 int b200knn_index_num_levels(const b200knn_index* idx) { return idx ? idx->levels : 0; }
+int b200knn_index_sort_bits(const b200knn_index* idx) { return idx ? idx->sort_bits : 0; }
 
 int b200knn_index_bounds(const b200knn_index* idx, float* host_bounds6) {
   KNN_REQUIRE(idx && host_bounds6, "index_bounds: NULL argument");
@@ -377,7 +410,7 @@ int b200knn_knn_query(b200knn_index* idx, const float* d_queries, int64_t nq, in
   // Order queries along the index's own Morton grid (queries outside its box clamp to the faces).
   if ((rc = morton_keys(d_queries, idx->dims == 2 ? 2 : 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
-  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
+  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 64 - index_sort_bits(), 64, stream, &in_tmp))) return rc;
   if ((rc = gather_points(d_queries, idx->dims == 2 ? 2 : 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
   if ((rc = refine_runs(qsorted, nq, stream))) return rc;   // compact query groups, same as leaves
   RingParams p;
@@ -429,7 +462,7 @@ int b200knn_knn_neighbors(b200knn_index* idx, const float* d_queries, int64_t nq
     KNN_CUDA_TRY(qsorted.alloc_bytes(groups * kGroup * sizeof(Float4)));
     if ((rc = morton_keys(d_queries, idx->dims == 2 ? 2 : 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
     int in_tmp = 0;
-    if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
+    if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 64 - index_sort_bits(), 64, stream, &in_tmp))) return rc;
     if ((rc = gather_points(d_queries, idx->dims == 2 ? 2 : 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
     if ((rc = refine_runs(qsorted, nq, stream))) return rc;
   }
@@ -506,7 +539,7 @@ int b200knn_fcp_query_ex(b200knn_index* idx, const float* d_queries, int64_t nq,
   int rc;
   if ((rc = morton_keys(d_queries, idx->dims == 2 ? 2 : 3, nq, idx->d_bounds6, keys, vals, stream))) return rc;
   int in_tmp = 0;
-  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 0, 64, stream, &in_tmp))) return rc;
+  if ((rc = radix_sort_u64(keys, vals, keys_tmp, vals_tmp, scratch, nq, 64 - index_sort_bits(), 64, stream, &in_tmp))) return rc;
   if ((rc = gather_points(d_queries, idx->dims == 2 ? 2 : 3, in_tmp ? vals_tmp.get() : vals.get(), nullptr, 0, nq, qsorted, stream))) return rc;
   if ((rc = refine_runs(qsorted, nq, stream))) return rc;
   RingParams p;

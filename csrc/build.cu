@@ -312,6 +312,23 @@ int morton_keys(const float* d_xyz, PointLayout lay, int64_t n, const float* d_b
   return 0;
 }
 
+// Set *flag if any cell of the key's leading (64 - shift) bits holds more than 1024 points: in sorted order that is
+// the same prefix 1024 places apart.
+__global__ void __launch_bounds__(256)
+k_heavy_cells(const uint64_t* __restrict__ keys, int64_t n, int shift, unsigned* __restrict__ flag) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i + 1024 < n && (keys[i] >> shift) == (keys[i + 1024] >> shift)) *flag = 1u;
+}
+
+int heavy_cells(const uint64_t* sorted_keys, int64_t n, int shift, unsigned* d_flag, cudaStream_t stream) {
+  KNN_CUDA_TRY(cudaMemsetAsync(d_flag, 0, sizeof(unsigned), stream));
+  if (n <= 1024) return 0;
+  k_heavy_cells<<<grid_for(n - 1024, 256), 256, 0, stream>>>(sorted_keys, n, shift, d_flag);
+  note_launch();
+  KNN_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 int gather_points(const float* d_xyz, PointLayout lay, const uint32_t* order, const uint32_t* ids, uint32_t id_offset,
                   int64_t n, Float4* sorted, cudaStream_t stream) {
   if (n <= 0) return 0;

@@ -7,6 +7,7 @@ using namespace b200knn;
 
 namespace b200knn {
 int frontier_capacity();   // api.cu: 128, or B200KNN_QUEUE_CAP (a test knob)
+int index_sort_bits();     // api.cu: 40, or B200KNN_SORT_BITS
 
 // A few words from device memory to the host WITHOUT a copy engine: a one-warp kernel stores them into a slot of
 // page-locked host memory that the GPU has mapped. An in-stream cudaMemcpyAsync of 24 bytes looks harmless, but it
@@ -32,6 +33,7 @@ class SmallRead {
 
 struct b200knn_index {
   int device = 0;
+  int sort_bits = 64;                      // leading key bits the build sorted by (40, or 64 after the heavy-cell fallback)
   int dims = 3;                            // 2: the index was built from [n][2] points (z = 0) and takes [nq][2] queries
   int num_sms = 148;
   int64_t n = 0;

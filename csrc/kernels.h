@@ -63,6 +63,8 @@ inline int gather_points(const float* d_xyz, int stride, const uint32_t* order, 
                          int64_t n, Float4* sorted, cudaStream_t stream) {
   return gather_points(d_xyz, layout_of(stride), order, ids, id_offset, n, sorted, stream);
 }
+// *d_flag = 1 if more than 1024 points share the leading (64 - shift) bits of their key (keys sorted), else 0.
+int heavy_cells(const uint64_t* sorted_keys, int64_t n, int shift, unsigned* d_flag, cudaStream_t stream);
 // Re-order every 1024-point Morton run into a balanced k-d tree with compact 32-point leaves.
 int refine_runs(Float4* sorted, int64_t n, cudaStream_t stream);
 int build_leaf_boxes(const Float4* sorted, int64_t n, Box* level0, cudaStream_t stream);

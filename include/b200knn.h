@@ -63,6 +63,9 @@ int b200knn_index_create_records(const void* d_records, int64_t n, size_t record
 void b200knn_index_destroy(b200knn_index* idx);
 int64_t b200knn_index_num_points(const b200knn_index* idx);
 int b200knn_index_num_levels(const b200knn_index* idx);
+/* Leading bits of the Morton key the build sorted by: 40 normally, 64 when some 40-bit cell held more than 1024 points
+ * (the build then runs a second time on the full key) or B200KNN_SORT_BITS=64 is set. */
+int b200knn_index_sort_bits(const b200knn_index* idx);
 /* host float[6]: lo.xyz, hi.xyz of the indexed points (synchronous). */
 int b200knn_index_bounds(const b200knn_index* idx, float* host_bounds6);
 /* Debug/test helpers: copy the sorted points (x,y,z,id-bits as float4) or one level of boxes to

@@ -116,6 +116,14 @@ class KnnIndex:
     def num_levels(self) -> int:
         return int(lib().b200knn_index_num_levels(self._h))
 
+    @property
+    def sort_bits(self) -> int:
+        """Leading bits of the 63-bit Morton key the build sorted by (40; 64 after the heavy-cell fallback)."""
+        fn = lib().b200knn_index_sort_bits
+        fn.argtypes = [C.c_void_p]
+        fn.restype = C.c_int
+        return int(fn(self._h))
+
     def bounds(self) -> np.ndarray:
         out = np.zeros(6, np.float32)
         check(lib().b200knn_index_bounds(self._h, out.ctypes.data), "index_bounds")

@@ -59,14 +59,17 @@ def test_index_build_sort_and_boxes(n):
     ids = s[:, 3].copy().view(np.uint32)
     assert np.array_equal(np.sort(ids), np.arange(n, dtype=np.uint32))
     assert np.array_equal(s[:, :3], x[ids])
-    # Order: Morton across 1024-point runs (radix sort), k-d median order inside a run (refine).
-    keys = morton63_np(s[:, :3], b[:3], b[3:])
+    # Order: Morton across 1024-point runs (radix sort on the key's leading sort_bits), k-d median order inside a
+    # run (refine).
+    shift = np.uint64(64 - idx.sort_bits)
+    assert idx.sort_bits in (40, 64)
+    keys = morton63_np(s[:, :3], b[:3], b[3:]) >> shift
     nruns = (n + 1023) // 1024
     run_min = np.array([keys[r * 1024:(r + 1) * 1024].min() for r in range(nruns)])
     run_max = np.array([keys[r * 1024:(r + 1) * 1024].max() for r in range(nruns)])
     assert np.all(run_min[1:] >= run_max[:-1])
     # every run holds exactly the points a stable Morton sort of the input puts there
-    ref_order = np.argsort(morton63_np(x, b[:3], b[3:]), kind="stable").astype(np.uint32)
+    ref_order = np.argsort(morton63_np(x, b[:3], b[3:]) >> shift, kind="stable").astype(np.uint32)
     for r in range(0, nruns, max(1, nruns // 64)):
         assert np.array_equal(np.sort(ids[r * 1024:(r + 1) * 1024]), np.sort(ref_order[r * 1024:(r + 1) * 1024]))
     # inside a full run: first median split is exact (left half <= right half on the widest axis)
@@ -346,3 +349,21 @@ def test_index_over_records_with_payload():
         assert float((d - da).abs().max().item()) <= 1e-6
         a.close()
         b.close()
+
+
+def test_index_build_falls_back_to_full_keys_on_heavy_cells():
+    """More than 1024 points inside one cell of the key's leading 40 bits (here: 5000 points within 1e-6 of the
+    extent, next to a uniform cloud): the build notices on the device and sorts again by all 64 bits. Results are
+    exact either way; this checks that the switch happens and that ordinary clouds do not take it."""
+    from mpi_cuda_largescaleknn_b200.ops.knn import KnnIndex
+    x = gen.uniform(60_000, seed=5)
+    tight = (np.float32(0.5) + np.random.default_rng(6).random((5000, 3), dtype=np.float32) * np.float32(1e-6)).astype(np.float32)
+    both = np.concatenate([x, tight])
+    a = KnnIndex(torch.from_numpy(x).to(_dev()))
+    b = KnnIndex(torch.from_numpy(both).to(_dev()))
+    assert a.sort_bits == 40 and b.sort_bits == 64
+    sel = np.concatenate([np.arange(0, 60_000, 97), np.arange(60_000, 65_000, 41)])
+    got = b.knn_self(20).cpu().numpy()
+    assert bit_equal(got[sel], bruteforce(both, queries=both[sel], k=20))
+    a.close()
+    b.close()

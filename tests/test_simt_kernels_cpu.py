@@ -96,6 +96,24 @@ def test_emulated_index_is_sorted_and_boxes_are_exact(sim):
     idx.close()
 
 
+def test_emulated_index_sort_falls_back_to_full_keys_on_heavy_cells(sim):
+    """The build sorts by the leading 40 bits of the Morton key and, when more than 1024 points share one such cell,
+    again by all 64: exact results either way, and the switch must happen exactly when it should."""
+    sim.b200knn_index_sort_bits.argtypes = [C.c_void_p]
+    x = gen.uniform(3000, seed=5)
+    tight = (np.float32(0.5) + np.random.default_rng(6).random((1500, 3), dtype=np.float32) * np.float32(1e-6)).astype(np.float32)
+    both = np.ascontiguousarray(np.concatenate([x, tight]))
+    a, b = Index(sim, x), Index(sim, both)
+    assert sim.b200knn_index_sort_bits(a.h) == 40 and sim.b200knn_index_sort_bits(b.h) == 64
+    assert bit_equal(b.knn_self(12), bruteforce(both, k=12))
+    few = np.ascontiguousarray(np.concatenate([x, tight[:900]]))      # 900 in the cell: no need
+    c = Index(sim, few)
+    assert sim.b200knn_index_sort_bits(c.h) == 40
+    assert bit_equal(c.knn_self(12), bruteforce(few, k=12))
+    for i in (a, b, c):
+        i.close()
+
+
 def test_emulated_radius_duplicates_and_clusters(sim):
     x = np.concatenate([gen.clustered_surface(2000, seed=2), np.zeros((60, 3), np.float32),
                         np.full((40, 3), 0.25, np.float32)])
