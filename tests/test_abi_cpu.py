@@ -8,6 +8,8 @@ from pathlib import Path
 
 import pytest
 
+from conftest import run_make
+
 ROOT = Path(__file__).resolve().parents[1]
 HEADER = ROOT / "include" / "b200knn.h"
 
@@ -81,7 +83,7 @@ def test_header_constants_match_python():
 
 def test_c_example_builds_against_the_library():
     """examples/sample_knn.c is plain C99 against include/b200knn.h + libb200knn.so (run it on a GPU box)."""
-    out = subprocess.run(["make", "-C", str(ROOT), "examples"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    out = run_make("examples")
     assert out.returncode == 0, out.stdout[-2000:]
     assert (ROOT / "build" / "sample_knn").exists()
 

@@ -8,6 +8,8 @@ from pathlib import Path
 import numpy as np
 import pytest
 
+from conftest import run_make
+
 from mpi_cuda_largescaleknn_b200.utils import generators as gen
 from mpi_cuda_largescaleknn_b200.utils import io as kio
 from mpi_cuda_largescaleknn_b200.utils.oracle import bit_equal, bruteforce
@@ -22,7 +24,8 @@ RUN = str(BUILD / "knnrun")
 @pytest.fixture(scope="module", autouse=True)
 def _built():
     if not (Path(UV).exists() and Path(PV).exists() and Path(RUN).exists()):
-        subprocess.run(["make", "-C", str(ROOT), "all"], check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        out = run_make("all")
+        assert out.returncode == 0, out.stdout[-3000:]
 
 
 def run(cmd, **kw):

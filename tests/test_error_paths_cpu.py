@@ -12,6 +12,8 @@ from pathlib import Path
 import numpy as np
 import pytest
 
+from conftest import run_make
+
 from mpi_cuda_largescaleknn_b200.ops import _lib
 from mpi_cuda_largescaleknn_b200.utils import generators as gen
 from mpi_cuda_largescaleknn_b200.utils import io as kio
@@ -22,7 +24,7 @@ pytestmark = pytest.mark.skipif(platform.machine() != "x86_64", reason="the emul
 
 @pytest.fixture(scope="module")
 def sim():
-    out = subprocess.run(["make", "-C", str(ROOT), "simt", "all"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    out = run_make("simt", "all")
     assert out.returncode == 0, out.stdout[-3000:]
     lib = _lib._proto(C.CDLL(os.environ.get("B200KNN_SIMT_LIB", str(ROOT / "build" / "libb200knn_simt.so"))))
     return lib

@@ -13,6 +13,8 @@ from pathlib import Path
 import numpy as np
 import pytest
 
+from conftest import run_make
+
 from mpi_cuda_largescaleknn_b200.ops import _lib
 from mpi_cuda_largescaleknn_b200.utils import generators as gen
 from mpi_cuda_largescaleknn_b200.utils.oracle import bit_equal, bruteforce
@@ -23,7 +25,7 @@ pytestmark = pytest.mark.skipif(platform.machine() != "x86_64", reason="the emul
 
 @pytest.fixture(scope="module")
 def sim():
-    out = subprocess.run(["make", "-C", str(ROOT), "simt"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    out = run_make("simt")
     assert out.returncode == 0, out.stdout[-3000:]
     import os
     lib = _lib._proto(C.CDLL(os.environ.get("B200KNN_SIMT_LIB", str(ROOT / "build" / "libb200knn_simt.so"))))
@@ -281,7 +283,7 @@ def test_emulated_frontier_overflow_paths_are_exercised_and_exact():
         "sel = np.arange(0, len(x), 150)\n"
         "assert bit_equal(out[sel], bruteforce(x, queries=x[sel], k=200))\n"
         "print('OVERFLOW_OK', st[4], st[5])\n")
-    out = subprocess.run(["make", "-C", str(ROOT), "simt"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    out = run_make("simt")
     assert out.returncode == 0, out.stdout[-3000:]
     run = subprocess.run([sys.executable, "-c", code], cwd=str(ROOT), env=dict(os.environ, B200KNN_QUEUE_CAP="8"),
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500)

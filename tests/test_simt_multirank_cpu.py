@@ -10,13 +10,15 @@ from pathlib import Path
 
 import pytest
 
+from conftest import run_make
+
 ROOT = Path(__file__).resolve().parents[1]
 pytestmark = pytest.mark.skipif(platform.machine() != "x86_64", reason="the emulation's fiber switch is x86-64 assembly")
 
 
 @pytest.fixture(scope="module")
 def built():
-    out = subprocess.run(["make", "-C", str(ROOT), "simt"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    out = run_make("simt")
     assert out.returncode == 0, out.stdout[-3000:]
 
 
@@ -54,7 +56,7 @@ def test_emulated_ranks_are_race_free_under_thread_sanitizer(built):
         tsan = ""
     if not tsan or not os.path.isabs(tsan) or not os.path.exists(tsan) or not os.path.exists("/usr/bin/g++"):
         pytest.skip("no ThreadSanitizer runtime / system g++ on this machine")
-    out = subprocess.run(["make", "-C", str(ROOT), "simt-tsan"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    out = run_make("simt-tsan")
     assert out.returncode == 0, out.stdout[-3000:]
     env = dict(os.environ, LD_PRELOAD=tsan, B200KNN_SIMT_LIB=str(ROOT / "build" / "libb200knn_simt_tsan.so"),
                TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 history_size=4 exitcode=0")
