@@ -4,6 +4,8 @@
 // collectives (allgather of equal-sized blobs, barrier = allgather of zero bytes) over one unix
 // stream socket per rank. Bulk data never passes through here: GPUs exchange it over NVLink.
 // Exit code = first non-zero child exit code.
+// Role of `mpirun -n <ranks>` in the reference's command lines (/root/reference/README.md:31,39) and of
+// MPI_Init / MPI_Comm_rank / MPI_Comm_size / MPI_Finalize (/root/reference/unorderedDataVariant.cu:34-35,107,238).
 #include <errno.h>
 #include <poll.h>
 #include <signal.h>

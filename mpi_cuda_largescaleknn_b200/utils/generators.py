@@ -3,6 +3,11 @@
 uniform            config 1, 2, 4: uniform-random float3 in the unit cube
 gaussian_blobs     config 3: one Gaussian blob per rank, centres on a grid, ~10 % spatial overlap
 clustered_surface  config 5: strongly clustered + surface-sampled points (load imbalance)
+
+The reference ships no generator for its programs (inputs are raw float3 files, /root/reference/README.md:25-39); its
+library tests draw uniformly distributed coordinates (integers in [0, N] stored as floats,
+cudaKDTree/testing/floatN-knn-and-fcp.cu:73-94 `generatePoints`); `uniform` is the continuous version of that in the
+unit cube.
 """
 from __future__ import annotations
 
